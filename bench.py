@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""Benchmark of the hierarchical message-passing encoder hot path (BASELINE.json metric:
+"HierMPN encoder molecules/sec (fwd+bwd)").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg3|cfg1]
+
+One step = HierMPNEncoder forward + backward (loss = hroot.sum(), the only output the VAEs consume,
+ggpm/property_vae.py:50) over one synthetic batch.  Workload at N=1 is BASELINE config #2: the encoder of
+one vae_train.py pre-training step with configs/pretrained_w_tie_embedding_configs.json (LSTM, hidden =
+embed = 250, depthT = depthG = 20, dropout 0.1, train mode), batch 256 per GPU.  For N > 1 every rank
+encodes its own batches (weak scaling, no communication on the encoder path) and the encoder-weight
+gradients are all-reduced with NCCL as one flat bucket inside the step.
+
+Prints ONE JSON line (rank 0).  `value` is timed with inputs resident in HBM; `e2e` goes through the public
+module API from pinned HOST index tensors (H2D copy + loss read-back inside the timed region).
+`--impl reference` times the CPU oracle (oracle/encoder_oracle.py: the reference's padded PyTorch
+formulation; the reference itself is Python and cannot travel to the GPU box) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: hidden, depthT, depthG, dropout, batch per GPU
+    "cfg1": dict(hidden=250, depthT=20, depthG=20, dropout=0.0, batch=20,
+                 desc="configs/configs.json encoder, 20 synthetic molecules"),
+    "cfg2": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256,
+                 desc="encoder of one vae_train.py step, pretrained_w_tie_embedding_configs.json, batch 256"),
+    "cfg3": dict(hidden=500, depthT=20, depthG=20, dropout=0.0, batch=4096,
+                 desc="double-hidden encoder (hidden 500), batch 4096 synthetic graphs"),
+}
+METRIC = "HierMPN encoder molecules/sec (fwd+bwd)"
+UNIT = "molecules/s"
+PROF_CLASSES = ["gather_sum", "gemm_tcgen05_3xtf32", "gemm_fp32_simt", "gemm_wgrad_fp32_simt", "cell_fwd", "cell_bwd", "misc"]
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return dict(hbm=float(p["hbm_gbs"]), bf16=float(p.get("bf16_tflops_sustained", p["bf16_tflops"])), src="measured")
+    return dict(hbm=6650.0, bf16=1590.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_batches(workload, n_batches, seed):
+    from ggpm_b200 import synth
+    out = []
+    for i in range(n_batches):
+        mols = synth.random_batch(seed * 1000 + i, workload["batch"])
+        tree, graph = synth.tensorize(mols)
+        out.append((tree, graph, synth.batch_stats(tree, graph)))
+    return out
+
+
+def algorithmic_flops(stats, H, depthT, depthG, B):
+    """minimal-formulation FLOPs of one HierMPNEncoder forward (LSTM); fwd+bwd = 3x"""
+    def layer(E, N, IN, F, D):
+        return 2.0 * E * IN * 4 * H + D * 8.0 * E * H * H + 2.0 * N * (F + H) * H
+    f = layer(stats["Ea"], stats["Na"], 62, 38, depthG) + 2 * layer(stats["Et"], stats["Nt"], H + 20, H, depthT)
+    f += 2 * (2.0 * stats["Nt"] * 2 * H * H) + 2.0 * B * 2 * H * H
+    return f
+
+
+# --------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the oracle (reference's padded torch formulation) on the host cores
+# --------------------------------------------------------------------------------------------------
+def cpu_oracle_rate(workload, sample_mols, warmup, steps):
+    from ggpm_b200 import synth
+    from oracle import encoder_oracle as eo
+    torch.set_num_threads(os.cpu_count() or 1)
+    H = workload["hidden"]
+    mols = synth.random_batch(424242, sample_mols)
+    tree, graph = synth.tensorize(mols)
+    as_long = lambda ts: [torch.from_numpy(np.asarray(t)).long() if not isinstance(t, list) else t for t in ts]
+    tree, graph = as_long(tree), as_long(graph)
+    sd = {k: v.requires_grad_(True) for k, v in eo.random_state("hier", "LSTM", H, H, 0, bias_std=0.0).items()}
+
+    def step():
+        for v in sd.values():
+            v.grad = None
+        eo.hier_encoder(sd, "LSTM", workload["depthT"], workload["depthG"], tree, graph)[0].sum().backward()
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / max(steps, 1)
+    return sample_mols / dt, dt
+
+
+def run_reference(args, workload):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample = min(workload["batch"], 32)
+    rate, dt = cpu_oracle_rate(workload, sample, args.warmup, args.steps)
+    cores = os.cpu_count() or 1
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + workload["desc"], "hidden": workload["hidden"],
+                   "depthT": workload["depthT"], "depthG": workload["depthG"], "rnn_type": "LSTM",
+                   "batch_per_gpu": workload["batch"]},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "%d-molecule synthetic batch of the same generator per step (CPU time scales "
+                                   "linearly in molecules); oracle = reference's padded PyTorch formulation, fp32, "
+                                   "%d torch threads" % (sample, cores)},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------------
+def run_ours(args, workload):
+    import torch.distributed as dist
+    import ggpm_b200
+    from ggpm_b200 import _lib, nnutils, synth
+    from ggpm_b200.dist import GradBucket
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the encoder path has no CPU fallback (use --impl reference "
+                         "for the CPU oracle)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if args.gpus != world and rank == 0 and world > 1:
+        print("warning: --gpus %d but WORLD_SIZE %d" % (args.gpus, world), file=sys.stderr)
+
+    H = workload["hidden"]
+    torch.manual_seed(0)
+    model = ggpm_b200.HierMPNEncoder(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H,
+                                     workload["depthT"], workload["depthG"], workload["dropout"])
+    for p in model.parameters():          # vae_train.py:49-53
+        if p.dim() == 1:
+            torch.nn.init.constant_(p, 0)
+        else:
+            torch.nn.init.xavier_normal_(p)
+    model = model.to(dev).train()
+    bucket = GradBucket(model.parameters())
+
+    n_batches = 4
+    batches = make_batches(workload, n_batches, seed=rank + 1)
+    dev_batches = [nnutils.make_cuda((t, g)) for t, g, _ in batches]
+    stats = batches[0][2]
+
+    def step(tree, graph, read_loss=False):
+        model.zero_grad(set_to_none=True)
+        hroot = model(tree, graph)[0]
+        loss = hroot.sum()
+        loss.backward()
+        if world > 1:
+            bucket.all_reduce_mean()
+        return float(loss.item()) if read_loss else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, warmup, steps):
+        for i in range(warmup):
+            fn(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(warmup + i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # ---- device-resident throughput ("value") -------------------------------------------------------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = _lib.launch_count()
+    ms = timed(lambda i: step(*dev_batches[i % n_batches]), args.warmup, args.steps)
+    launches = (_lib.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    mols_per_step = workload["batch"] * world
+    value = mols_per_step * args.steps / (ms / 1e3)
+
+    # ---- end to end from pinned host buffers ("e2e") ------------------------------------------------
+    def pin(arrs):
+        return [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() if not isinstance(a, list) else a for a in arrs]
+    host_batches = [(pin(t), pin(g)) for t, g, _ in batches]
+    h2d = sum(a.numel() * a.element_size() for a in host_batches[0][0][:-1] + host_batches[0][1][:-1])
+
+    def e2e_step(i):
+        t, g = host_batches[i % n_batches]
+        tree = [a.to(dev, non_blocking=True).long() for a in t[:-1]] + [t[-1]]
+        graph = [a.to(dev, non_blocking=True).long() for a in g[:-1]] + [g[-1]]
+        step(tree, graph, read_loss=True)
+    e2e_ms = timed(e2e_step, min(args.warmup, 3), args.steps)
+    e2e_value = mols_per_step * args.steps / (e2e_ms / 1e3)
+
+    # ---- per-kernel-class timing for the roofline (separate instrumented pass, rank 0) --------------
+    roofline, kernels = None, None
+    peaks = load_peaks()
+    if rank == 0:
+        lib = _lib.backend()
+        _lib.call("ggpm_prof_enable", 1)
+        prof_steps = 2
+        for i in range(prof_steps):
+            model.zero_grad(set_to_none=True)
+            model(*dev_batches[i % n_batches])[0].sum().backward()
+        n = len(PROF_CLASSES)
+        ms_c, cnt_c, work_c = (ctypes.c_double * n)(), (ctypes.c_longlong * n)(), (ctypes.c_double * n)()
+        _lib.call("ggpm_prof_collect", ctypes.cast(ms_c, ctypes.c_void_p), ctypes.cast(cnt_c, ctypes.c_void_p),
+                  ctypes.cast(work_c, ctypes.c_void_p), n)
+        _lib.call("ggpm_prof_enable", 0)
+        total = sum(ms_c) or 1.0
+        kernels = {PROF_CLASSES[c]: {"ms_per_step": ms_c[c] / prof_steps, "launches_per_step": cnt_c[c] // prof_steps,
+                                     "share": ms_c[c] / total} for c in range(n) if cnt_c[c]}
+        gemm_classes = [c for c in (1, 2, 3) if cnt_c[c]]
+        top = max(range(n), key=lambda c: ms_c[c])
+        if top in gemm_classes:
+            tf = work_c[top] / (ms_c[top] * 1e-3) / 1e12
+            per_launch = work_c[top] / cnt_c[top]
+            roofline = {"kernel": PROF_CLASSES[top], "bound": "tensor", "achieved": tf, "peak": peaks["bf16"],
+                        "unit": "TFLOP/s", "frac": tf / peaks["bf16"], "traffic": None,
+                        "flops_per_launch": per_launch, "avg_launch_ms": ms_c[top] / cnt_c[top],
+                        "peak_kind": "dense bf16 cuBLAS, sustained, of " + peaks["src"]}
+        else:
+            # HBM-side classes: algorithmic bytes per step from SURVEY 8(d) (nnz-dependent part from the batch)
+            Hp = (H + 31) // 32 * 32
+            by = 0.0
+            for E, nnz, D in ((stats["Ea"], stats["nnz_bA"], workload["depthG"]),
+                              (stats["Et"], stats["nnz_bT"], workload["depthT"]),
+                              (stats["Et"], stats["nnz_bT"], workload["depthT"])):
+                by += D * (3.0 * nnz * Hp * 4 + 2.0 * E * Hp * 4 + 4.0 * nnz + 4.0 * E)
+            gbs = by * prof_steps / (ms_c[top] * 1e-3) / 1e9
+            roofline = {"kernel": PROF_CLASSES[top], "bound": "hbm", "achieved": gbs, "peak": peaks["hbm"],
+                        "unit": "GB/s", "frac": gbs / peaks["hbm"], "traffic": None,
+                        "avg_launch_ms": ms_c[top] / cnt_c[top], "peak_kind": "copy bandwidth, of " + peaks["src"]}
+
+    # ---- CPU baseline on the host cores (rank 0, N = 1 only) ----------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sample = min(workload["batch"], 32)
+        rate, dt = cpu_oracle_rate(workload, sample, 1, 3)
+        cores = os.cpu_count() or 1
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "%d-molecule batch x 3 timed fwd+bwd (%.2f s each) of the oracle (reference's padded "
+                         "PyTorch formulation, fp32, %d threads)" % (sample, dt, cores)}
+
+    if rank == 0:
+        flops = 3.0 * algorithmic_flops(stats, H, workload["depthT"], workload["depthG"], workload["batch"])
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload + ": " + workload["desc"], "hidden": H, "depthT": workload["depthT"],
+                       "depthG": workload["depthG"], "rnn_type": "LSTM", "dropout": workload["dropout"],
+                       "batch_per_gpu": workload["batch"], "parallelism": "dp%d" % world,
+                       "gemm_engine": {0: "auto", 1: "fp32-simt", 2: "tcgen05-3xtf32"}[lib.ggpm_get_gemm_engine()],
+                       "l2": "no explicit flush: %d distinct batches rotate and each step streams its saved "
+                             "activations (>> 126 MB L2) between forward and backward" % n_batches,
+                       "shape_per_batch": stats},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
+                    "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": roofline,
+            "kernels": kernels,
+            "algorithmic_tflops": flops * world / (ms / args.steps * 1e-3) / 1e12,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--engine", type=int, default=None, help="0 auto, 1 fp32 CUDA cores, 2 tcgen05 3xTF32")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    workload = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, workload)
+        return
+    if args.engine is not None:
+        from ggpm_b200 import _lib
+        _lib.set_gemm_engine(args.engine)
+    run_ours(args, workload)
+
+
+if __name__ == "__main__":
+    main()

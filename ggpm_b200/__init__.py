@@ -1,0 +1,11 @@
+"""ggpm_b200 — B200-native (sm_100a) implementation of ggpm's hierarchical message-passing encoder.
+
+Drop-in classes (same names / constructor / forward contract as ggpm/encoder.py and ggpm/rnn.py):
+    from ggpm_b200 import HierMPNEncoder, MotifEncoder, MPNEncoder, GRU, LSTM
+The CUDA library (libggpm_b200.so, C ABI in include/ggpm_b200.h) is loaded on first use; without it, or
+without a CUDA device, the modules raise — there is no CPU fallback.
+"""
+from .encoder import HierMPNEncoder, MotifEncoder, MPNEncoder      # noqa: F401
+from .rnn import GRU, LSTM                                         # noqa: F401
+
+__all__ = ["HierMPNEncoder", "MotifEncoder", "MPNEncoder", "GRU", "LSTM"]

@@ -1,0 +1,117 @@
+"""ctypes binding of libggpm_b200.so (the C ABI declared in include/ggpm_b200.h).
+
+There is NO CPU path: if the shared library is missing, or a tensor is not on a CUDA device, the
+calls below raise.  Build the library in-tree with ``python -m ggpm_b200.build``.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_void_p
+
+import torch
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libggpm_b200.so")
+
+ACT_NONE, ACT_RELU, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3
+ENGINE_AUTO, ENGINE_SIMT_FP32, ENGINE_TCGEN05_3XTF32 = 0, 1, 2
+
+P = c_void_p
+I = c_int
+# name -> (restype, argtypes); mirrors include/ggpm_b200.h one to one (checked by tests/test_cabi.py)
+SIGNATURES = {
+    "ggpm_last_error": (c_char_p, []),
+    "ggpm_abi_version": (I, []),
+    "ggpm_set_gemm_engine": (I, [I]),
+    "ggpm_get_gemm_engine": (I, []),
+    "ggpm_launch_count": (c_longlong, []),
+    "ggpm_prof_enable": (I, [I]),
+    "ggpm_prof_collect": (I, [P, P, P, I]),
+    "ggpm_csr_from_padded": (I, [P, I, I, I, I, P, P, P, P]),
+    "ggpm_csr_transpose": (I, [P, P, I, I, P, P, P, P, P]),
+    "ggpm_gather_sum": (I, [P, I, P, P, P, I, I, I, I, P]),
+    "ggpm_gemm": (I, [P, c_longlong, c_longlong, P, c_longlong, c_longlong, P, I, I, I, I, c_float, P, I, I, I, P]),
+    "ggpm_act_bwd": (I, [P, I, P, I, P, I, I, I, I, I, P]),
+    "ggpm_colsum": (I, [P, I, I, I, P, I, P]),
+    "ggpm_table_wgrad": (I, [P, I, I, I, P, P, P, I, I, P]),
+    "ggpm_lstm_fwd": (I, [I, I, I, I, P, P, P, P, P, P, P, P, P, P, P, P, P, I, P]),
+    "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 25),
+    "ggpm_gru_fwd": (I, [I, I, I, I] + [P] * 13 + [I, P]),
+    "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
+}
+
+_LIB = None
+_TEST_BACKEND = None      # tests/ may install an emulator of the C ABI; the product never does
+
+
+def _load():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "ggpm_b200: %s is missing — build it with `python -m ggpm_b200.build` "
+                "(there is no CPU or PyTorch fallback for this path)" % LIB_PATH)
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)        # AttributeError if the library lacks a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = lib
+    return _LIB
+
+
+def backend():
+    return _TEST_BACKEND if _TEST_BACKEND is not None else _load()
+
+
+def _install_test_backend(obj):
+    """TEST SEAM ONLY (tests/_emu_lib.py): route the C-ABI calls to a host emulator."""
+    global _TEST_BACKEND
+    _TEST_BACKEND = obj
+
+
+def call(name, *args):
+    """Invoke a C-ABI entry point; non-zero status -> RuntimeError with ggpm_last_error()."""
+    lib = backend()
+    status = getattr(lib, name)(*args)
+    if status != 0:
+        msg = lib.ggpm_last_error()
+        if isinstance(msg, bytes):
+            msg = msg.decode(errors="replace")
+        raise RuntimeError("%s failed (status %d): %s" % (name, status, msg))
+
+
+def require_device(t: torch.Tensor, what: str = "tensor"):
+    if _TEST_BACKEND is None and not t.is_cuda:
+        raise RuntimeError("ggpm_b200 runs on CUDA devices only (no CPU fallback): %s is on %s" % (what, t.device))
+
+
+def fptr(t: torch.Tensor, what: str = "tensor"):
+    """device pointer of an fp32 tensor whose last dimension is contiguous"""
+    require_device(t, what)
+    if t.dtype != torch.float32:
+        raise ValueError("%s must be float32, got %s" % (what, t.dtype))
+    if t.dim() >= 1 and t.shape[-1] > 1 and t.stride(-1) != 1:
+        raise ValueError("%s must be contiguous along its last dimension" % what)
+    return t.data_ptr()
+
+
+def iptr(t: torch.Tensor, what: str = "index"):
+    require_device(t, what)
+    if t.dtype != torch.int32 or not t.is_contiguous():
+        raise ValueError("%s must be a contiguous int32 tensor" % what)
+    return t.data_ptr()
+
+
+def stream_ptr(device=None):
+    if _TEST_BACKEND is not None:
+        return None
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def launch_count() -> int:
+    return int(backend().ggpm_launch_count())
+
+
+def set_gemm_engine(engine: int):
+    call("ggpm_set_gemm_engine", engine)

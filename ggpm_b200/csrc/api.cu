@@ -1,0 +1,300 @@
+// C-ABI entry points that orchestrate whole layers: the depth loops of the graph LSTM / GRU
+// (ggpm/rnn.py:41-50, 96-108) and their back-propagation through time, plus library-wide state.
+#include <stdarg.h>
+#include <string.h>
+
+#include <atomic>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ggpm {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+static std::atomic<int> g_engine{GGPM_ENGINE_AUTO};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int check_launch(const char* what, int n_kernels) {
+    g_launches.fetch_add(n_kernels, std::memory_order_relaxed);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return 3;
+    }
+    return 0;
+}
+
+int sm_count() {
+    static int cached = 0;
+    if (cached > 0) return cached;
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+        n = 148;
+    cached = n;
+    return n;
+}
+
+int gemm_engine() { return g_engine.load(std::memory_order_relaxed); }
+
+// ---- per-launch event timing -------------------------------------------------------------------------
+constexpr int kProfMax = 1 << 16;
+static bool g_prof_on = false;
+static int g_prof_n = 0;
+static cudaEvent_t* g_prof_ev = nullptr;        // 2 * kProfMax events, created on first enable
+static int g_prof_cls[kProfMax];
+static double g_prof_work[kProfMax];
+
+ProfScope::ProfScope(int cls, cudaStream_t stream, double work) : slot(-1), st(stream) {
+    if (!g_prof_on || g_prof_n >= kProfMax) return;
+    slot = g_prof_n++;
+    g_prof_cls[slot] = cls;
+    g_prof_work[slot] = work;
+    cudaEventRecord(g_prof_ev[2 * slot], st);
+}
+ProfScope::~ProfScope() {
+    if (slot >= 0) cudaEventRecord(g_prof_ev[2 * slot + 1], st);
+}
+
+// C = A[M,K] * W[N,K]^T with both operands K-contiguous
+static int gemm_nt(const float* A, int lda, const float* W, int ldw, float* C, int ldc, int M, int N, int K, float beta,
+                   const float* bias, int act, int zero_row0, cudaStream_t st) {
+    GemmArgs g;
+    g.A = A; g.sam = lda; g.sak = 1;
+    g.B = W; g.sbk = 1; g.sbn = ldw;
+    g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K; g.beta = beta; g.bias = bias; g.act = act; g.zero_row0 = zero_row0;
+    return launch_gemm_nt(g, st);
+}
+// C = A[M,K] * B[K,N] with B stored row-major [K, N]  (input gradients: dX = dY * W)
+static int gemm_nn(const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K, float beta,
+                   cudaStream_t st) {
+    GemmArgs g;
+    g.A = A; g.sam = lda; g.sak = 1;
+    g.B = B; g.sbk = ldb; g.sbn = 1;
+    g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K; g.beta = beta;
+    return launch_gemm_simt(g, st);
+}
+// C[M,N] += A^T * B with A stored [K, M], B stored [K, N]  (weight gradients, K = number of messages)
+static int gemm_tn_acc(const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K,
+                       cudaStream_t st) {
+    GemmArgs g;
+    g.A = A; g.sam = 1; g.sak = lda;
+    g.B = B; g.sbk = ldb; g.sbn = 1;
+    g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K; g.beta = 1.f;
+    // enough K-slices to fill the machine: tiles(M,N) * splits >= ~2 waves
+    int tiles = ceil_div(M, 128) * ceil_div(N, 128);
+    int splits = ceil_div(2 * sm_count(), tiles);
+    int max_splits = ceil_div(K, 256);
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    g.split_k = splits;
+    if (splits == 1) g.beta = 1.f;
+    return launch_gemm_simt(g, st);
+}
+
+}  // namespace ggpm
+
+using namespace ggpm;
+
+extern "C" const char* ggpm_last_error(void) { return g_err; }
+extern "C" int ggpm_abi_version(void) { return 1; }
+extern "C" long long ggpm_launch_count(void) { return g_launches.load(); }
+extern "C" int ggpm_get_gemm_engine(void) { return g_engine.load(); }
+extern "C" int ggpm_set_gemm_engine(int engine) {
+    GGPM_REQUIRE(engine >= GGPM_ENGINE_AUTO && engine <= GGPM_ENGINE_TCGEN05_3XTF32, "unknown GEMM engine %d", engine);
+    g_engine.store(engine);
+    return 0;
+}
+
+extern "C" int ggpm_prof_enable(int on) {
+    if (on && !g_prof_ev) {
+        g_prof_ev = new cudaEvent_t[2 * kProfMax];
+        for (int i = 0; i < 2 * kProfMax; ++i) GGPM_CUDA(cudaEventCreate(&g_prof_ev[i]));
+    }
+    g_prof_on = on != 0;
+    if (on) g_prof_n = 0;
+    return 0;
+}
+
+extern "C" int ggpm_prof_collect(double* ms, long long* count, double* work, int n_class) {
+    GGPM_REQUIRE(ms && count && work && n_class >= PROF_NCLASS, "prof_collect: need %d classes", PROF_NCLASS);
+    for (int c = 0; c < n_class; ++c) { ms[c] = 0; count[c] = 0; work[c] = 0; }
+    GGPM_CUDA(cudaDeviceSynchronize());
+    for (int i = 0; i < g_prof_n; ++i) {
+        float t = 0.f;
+        GGPM_CUDA(cudaEventElapsedTime(&t, g_prof_ev[2 * i], g_prof_ev[2 * i + 1]));
+        ms[g_prof_cls[i]] += t;
+        count[g_prof_cls[i]] += 1;
+        work[g_prof_cls[i]] += g_prof_work[i];
+    }
+    g_prof_n = 0;
+    return 0;
+}
+
+extern "C" int ggpm_gemm(const float* A, long long sam, long long sak, const float* B, long long sbk, long long sbn,
+                         float* C, int ldc, int M, int N, int K, float beta, const float* bias, int act, int zero_row0,
+                         int split_k, void* stream) {
+    GGPM_REQUIRE(A && B && C, "gemm: null pointer");
+    GemmArgs g;
+    g.A = A; g.sam = sam; g.sak = sak; g.B = B; g.sbk = sbk; g.sbn = sbn; g.C = C; g.ldc = ldc;
+    g.M = M; g.N = N; g.K = K; g.beta = beta; g.bias = bias; g.act = act; g.zero_row0 = zero_row0; g.split_k = split_k;
+    if (sak == 1 && sbk == 1 && split_k <= 1) return launch_gemm_nt(g, (cudaStream_t)stream);
+    return launch_gemm_simt(g, (cudaStream_t)stream);
+}
+
+// ----------------------------------------------------------------------------------------------------
+// LSTM
+// ----------------------------------------------------------------------------------------------------
+static int check_dims(const char* who, int E1, int H, int Hp, int depth) {
+    GGPM_REQUIRE(E1 >= 1 && H >= 1 && depth >= 1, "%s: bad sizes E1=%d H=%d depth=%d", who, E1, H, depth);
+    GGPM_REQUIRE(Hp >= H && Hp % 32 == 0, "%s: Hp=%d must be a multiple of 32 and >= H=%d", who, Hp, H);
+    return 0;
+}
+
+extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
+                             const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
+                             const float* Ug, const float* Uf, float* hist_h, float* hist_c, float* hist_gp,
+                             float* s_scratch, int keep_history, void* stream) {
+    GGPM_TRY(check_dims("lstm_fwd", E1, H, Hp, depth));
+    GGPM_REQUIRE(b_ptr && b_col && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp && s_scratch,
+                 "lstm_fwd: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t row = (size_t)E1 * Hp;
+    const XTabArgs x{Yn, src, T, k1, k2};
+    for (int t = 1; t <= depth; ++t) {
+        const int cur = keep_history ? (t - 1) : ((t - 1) & 1);
+        const int prev = keep_history ? (t - 2) : ((t - 2) & 1);
+        float* h_cur = hist_h + cur * row;
+        float* c_cur = hist_c + cur * row;
+        float* gp = hist_gp + (size_t)cur * 4 * row;
+        if (t == 1) {
+            GGPM_TRY(launch_lstm_cell_fwd(true, E1, H, Hp, b_ptr, b_col, x, nullptr, nullptr, h_cur, c_cur, st));
+            continue;
+        }
+        const float* h_prev = hist_h + prev * row;
+        const float* c_prev = hist_c + prev * row;
+        // S = sum of neighbour states; [G_i|G_o|G_u] = S Ug^T ; P = h_prev Uf^T
+        GGPM_TRY(launch_gather_sum(h_prev, Hp, b_ptr, b_col, s_scratch, Hp, E1, Hp, false, st));
+        GGPM_TRY(gemm_nt(s_scratch, Hp, Ug, Hp, gp, 4 * Hp, E1, 3 * Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
+        GGPM_TRY(gemm_nt(h_prev, Hp, Uf, Hp, gp + 3 * Hp, 4 * Hp, E1, Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
+        GGPM_TRY(launch_lstm_cell_fwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, h_cur, c_cur, st));
+    }
+    return 0;
+}
+
+extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
+                             const int32_t* bt_ptr, const int32_t* bt_row, const float* Yn, const int32_t* src,
+                             const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
+                             const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
+                             float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
+                             void* stream) {
+    GGPM_TRY(check_dims("lstm_bwd", E1, H, Hp, depth));
+    GGPM_REQUIRE(b_ptr && b_col && bt_ptr && bt_row && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp &&
+                     dH_final && dX && dUg && dUf && dA && dC && dP && dS && S && dHn,
+                 "lstm_bwd: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t row = (size_t)E1 * Hp;
+    const XTabArgs x{Yn, src, T, k1, k2};
+    float* dH = dH_final;
+    float* dH_next = dHn;
+    const float* dC_cur = nullptr;   // dL/dc^depth = 0
+    for (int t = depth; t >= 1; --t) {
+        const float* c_cur = hist_c + (size_t)(t - 1) * row;
+        const float* gp = hist_gp + (size_t)(t - 1) * 4 * row;
+        const bool overwrite = (t == depth);
+        if (t == 1) {
+            GGPM_TRY(launch_lstm_cell_bwd(true, E1, H, Hp, b_ptr, b_col, x, nullptr, nullptr, c_cur, dH, dC_cur, dA, dX,
+                                          overwrite, nullptr, nullptr, st));
+            break;
+        }
+        const float* h_prev = hist_h + (size_t)(t - 2) * row;
+        const float* c_prev = hist_c + (size_t)(t - 2) * row;
+        float* dC_prev = dC + (size_t)(t & 1) * row;
+        GGPM_CUDA(cudaMemsetAsync(dP, 0, sizeof(float) * row, st));
+        GGPM_CUDA(cudaMemsetAsync(dC_prev, 0, sizeof(float) * row, st));
+        GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_cur, dA, dX, overwrite,
+                                      dP, dC_prev, st));
+        // weight gradients: dUg += dA[:, :3Hp]^T S^t ; dUf += dP^T h^{t-1}
+        GGPM_TRY(launch_gather_sum(h_prev, Hp, b_ptr, b_col, S, Hp, E1, Hp, false, st));
+        GGPM_TRY(gemm_tn_acc(dA, 4 * Hp, S, Hp, dUg, Hp, 3 * Hp, Hp, E1, st));
+        GGPM_TRY(gemm_tn_acc(dP, Hp, h_prev, Hp, dUf, Hp, Hp, Hp, E1, st));
+        // state gradients: dS = dA[:, :3Hp] Ug ; dH^{t-1}[n] = sum_{e: n in N(e)} dS[e] + (dP Uf)[n]
+        GGPM_TRY(gemm_nn(dA, 4 * Hp, Ug, Hp, dS, Hp, E1, Hp, 3 * Hp, 0.f, st));
+        GGPM_TRY(launch_gather_sum(dS, Hp, bt_ptr, bt_row, dH_next, Hp, E1, Hp, false, st));
+        GGPM_TRY(gemm_nn(dP, Hp, Uf, Hp, dH_next, Hp, E1, Hp, Hp, 1.f, st));
+        float* tmp = dH; dH = dH_next; dH_next = tmp;
+        dC_cur = dC_prev;
+    }
+    return 0;
+}
+
+// ----------------------------------------------------------------------------------------------------
+// GRU      aux row layout (5*Hp): [S | Gz | Gh | Pr | Sg]
+// ----------------------------------------------------------------------------------------------------
+extern "C" int ggpm_gru_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
+                            const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
+                            const float* Uz, const float* Ur, const float* br, const float* Uh, float* hist_h,
+                            float* hist_aux, int keep_history, void* stream) {
+    GGPM_TRY(check_dims("gru_fwd", E1, H, Hp, depth));
+    GGPM_REQUIRE(b_ptr && b_col && Yn && src && T && k1 && Uz && Ur && br && Uh && hist_h && hist_aux, "gru_fwd: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t row = (size_t)E1 * Hp;
+    const XTabArgs x{Yn, src, T, k1, k2};
+    GGPM_CUDA(cudaMemsetAsync(hist_h, 0, sizeof(float) * row, st));   // h^0 = 0
+    for (int t = 1; t <= depth; ++t) {
+        const float* h_prev = hist_h + (size_t)(keep_history ? (t - 1) : ((t - 1) & 1)) * row;
+        float* h_cur = hist_h + (size_t)(keep_history ? t : (t & 1)) * row;
+        float* aux = hist_aux + (size_t)(keep_history ? (t - 1) : 0) * 5 * row;
+        GGPM_TRY(launch_gather_sum(h_prev, Hp, b_ptr, b_col, aux, 5 * Hp, E1, Hp, false, st));                          // S
+        GGPM_TRY(gemm_nt(aux, 5 * Hp, Uz, Hp, aux + Hp, 5 * Hp, E1, Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));        // Gz
+        GGPM_TRY(gemm_nt(h_prev, Hp, Ur, Hp, aux + 3 * Hp, 5 * Hp, E1, Hp, Hp, 0.f, br, GGPM_ACT_NONE, 0, st));          // Pr
+        GGPM_TRY(launch_gru_gate(E1, Hp, b_ptr, b_col, x, h_prev, aux, st));                                            // Sg
+        GGPM_TRY(gemm_nt(aux + 4 * Hp, 5 * Hp, Uh, Hp, aux + 2 * Hp, 5 * Hp, E1, Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));  // Gh
+        GGPM_TRY(launch_gru_out(E1, H, Hp, x, aux, h_cur, st));
+    }
+    return 0;
+}
+
+extern "C" int ggpm_gru_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
+                            const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
+                            const float* Uz, const float* Ur, const float* Uh, const float* hist_h, const float* hist_aux,
+                            float* dH_final, float* dX, float* dUz, float* dUr, float* dbr, float* dUh, float* dA,
+                            float* dS, float* dSg, float* dPr, float* dHn, void* stream) {
+    GGPM_TRY(check_dims("gru_bwd", E1, H, Hp, depth));
+    GGPM_REQUIRE(b_ptr && b_col && Yn && src && T && k1 && Uz && Ur && Uh && hist_h && hist_aux && dH_final && dX && dUz &&
+                     dUr && dbr && dUh && dA && dS && dSg && dPr && dHn,
+                 "gru_bwd: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t row = (size_t)E1 * Hp;
+    const XTabArgs x{Yn, src, T, k1, k2};
+    float* dH = dH_final;
+    float* dH_next = dHn;
+    for (int t = depth; t >= 1; --t) {
+        const float* h_prev = hist_h + (size_t)(t - 1) * row;
+        const float* aux = hist_aux + (size_t)(t - 1) * 5 * row;
+        const bool overwrite = (t == depth);
+        GGPM_TRY(launch_gru_out_bwd(E1, H, Hp, x, aux, dH, dA, dS, st));        // dA = [daz|dah], dS = dH (1-z)
+        if (t == 1) {   // h^0 = 0: no neighbour terms, no weight gradients from this round
+            GGPM_TRY(launch_gru_pair_bwd(E1, Hp, b_ptr, b_col, x, aux, h_prev, dA, dS, dSg, dX, overwrite, false, dPr, dH_next, st));
+            break;
+        }
+        GGPM_TRY(gemm_nn(dA, 2 * Hp, Uz, Hp, dS, Hp, E1, Hp, Hp, 1.f, st));       // dS += daz Uz
+        GGPM_TRY(gemm_nn(dA + Hp, 2 * Hp, Uh, Hp, dSg, Hp, E1, Hp, Hp, 0.f, st)); // dSg = dah Uh
+        GGPM_TRY(gemm_tn_acc(dA, 2 * Hp, aux, 5 * Hp, dUz, Hp, Hp, Hp, E1, st));                  // dUz += daz^T S
+        GGPM_TRY(gemm_tn_acc(dA + Hp, 2 * Hp, aux + 4 * Hp, 5 * Hp, dUh, Hp, Hp, Hp, E1, st));    // dUh += dah^T Sg
+        GGPM_CUDA(cudaMemsetAsync(dPr, 0, sizeof(float) * row, st));
+        GGPM_CUDA(cudaMemsetAsync(dH_next, 0, sizeof(float) * row, st));
+        GGPM_TRY(launch_gru_pair_bwd(E1, Hp, b_ptr, b_col, x, aux, h_prev, dA, dS, dSg, dX, overwrite, true, dPr, dH_next, st));
+        GGPM_TRY(gemm_nn(dPr, Hp, Ur, Hp, dH_next, Hp, E1, Hp, Hp, 1.f, st));     // dH^{t-1} += dPr Ur
+        GGPM_TRY(gemm_tn_acc(dPr, Hp, h_prev, Hp, dUr, Hp, Hp, Hp, E1, st));      // dUr += dPr^T h^{t-1}
+        GGPM_TRY(ggpm_colsum(dPr, Hp, E1, Hp, dbr, 1, stream));                   // db_r += column sums of dPr
+        float* tmp = dH; dH = dH_next; dH_next = tmp;
+    }
+    return 0;
+}

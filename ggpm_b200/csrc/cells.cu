@@ -1,0 +1,449 @@
+// Per-round cell kernels of the graph LSTM / GRU (forward and backward) and small element-wise helpers.
+//
+// One warp per message row, lanes across the hidden dimension in 128-bit chunks.  Neighbour rows are
+// reached through the CSR of bgraph; the padded [E, K, H] tensors of the reference (ggpm/rnn.py:26-38,
+// 86-93) are never built.  The depth-invariant x-projection is read as a sum of table rows:
+//     X_g[e] = Yn[src[e], g] + T[k1[e], g] (+ T[k2[e], g])
+// Math: SURVEY.md Appendix A (restated and checked against autograd in tests/_proto.py).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ggpm {
+
+constexpr int kCellWarps = 8;
+
+struct XTab {
+    const float* Yn; const int* src; const float* T; const int* k1; const int* k2; int ld;   // ld = G*Hp
+};
+
+struct XRow {   // resolved row pointers of one message
+    const float* y; const float* t1; const float* t2;
+};
+
+__device__ __forceinline__ XRow xrow(const XTab& x, int e) {
+    XRow r;
+    r.y = x.Yn + (size_t)__ldg(x.src + e) * x.ld;
+    r.t1 = x.T + (size_t)__ldg(x.k1 + e) * x.ld;
+    r.t2 = x.k2 ? x.T + (size_t)__ldg(x.k2 + e) * x.ld : nullptr;
+    return r;
+}
+__device__ __forceinline__ float4 xval(const XRow& r, int off) {
+    float4 v = ldg4(r.y + off) + ldg4(r.t1 + off);
+    if (r.t2) v += ldg4(r.t2 + off);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// LSTM forward cell:  reads gp = [G_i|G_o|G_u|P] of this round (rows e: G, rows n: P), c_prev; writes h, c
+// ------------------------------------------------------------------------------------------------
+template <bool FIRST>
+__global__ void __launch_bounds__(kCellWarps * 32)
+lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
+                     const float* __restrict__ gp, const float* __restrict__ c_prev, float* __restrict__ h_out,
+                     float* __restrict__ c_out) {
+    const int lane = threadIdx.x & 31;
+    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (e >= E1) return;
+    const int ld4h = 4 * Hp;
+    if (e == 0) {   // padding row: forced to zero after every round (ggpm/rnn.py:106-107)
+        for (int c = lane * 4; c < Hp; c += 128) {
+            st4(h_out + c, f4zero());
+            st4(c_out + c, f4zero());
+        }
+        return;
+    }
+    const XRow xr = xrow(xt, e);
+    const int b = FIRST ? 0 : __ldg(rp + e), en = FIRST ? 0 : __ldg(rp + e + 1);
+    const float* ge = gp + (size_t)e * ld4h;
+    for (int c = lane * 4; c < Hp; c += 128) {
+        float4 ai = xval(xr, c), ao = xval(xr, Hp + c), au = xval(xr, 2 * Hp + c);
+        float4 chat;
+        if (FIRST) {
+            chat = sigmoid4(ai) * tanh4(au);
+        } else {
+            ai += ld4(ge + c);
+            ao += ld4(ge + Hp + c);
+            au += ld4(ge + 2 * Hp + c);
+            chat = sigmoid4(ai) * tanh4(au);
+            const float4 xf = xval(xr, 3 * Hp + c);
+            int j = b;
+            for (; j + 2 <= en; j += 2) {
+                const int n0 = __ldg(col + j), n1 = __ldg(col + j + 1);
+                float4 p0 = ld4(gp + (size_t)n0 * ld4h + 3 * Hp + c), p1 = ld4(gp + (size_t)n1 * ld4h + 3 * Hp + c);
+                float4 c0 = ld4(c_prev + (size_t)n0 * Hp + c), c1 = ld4(c_prev + (size_t)n1 * Hp + c);
+                chat = fma4(sigmoid4(xf + p0), c0, chat);
+                chat = fma4(sigmoid4(xf + p1), c1, chat);
+            }
+            if (j < en) {
+                const int n0 = __ldg(col + j);
+                float4 p0 = ld4(gp + (size_t)n0 * ld4h + 3 * Hp + c);
+                float4 c0 = ld4(c_prev + (size_t)n0 * Hp + c);
+                chat = fma4(sigmoid4(xf + p0), c0, chat);
+            }
+        }
+        chat = clip_cols(chat, c, H);
+        float4 h = clip_cols(sigmoid4(ao) * tanh4(chat), c, H);
+        st4(c_out + (size_t)e * Hp + c, chat);
+        st4(h_out + (size_t)e * Hp + c, h);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// LSTM backward cell (one round).  dP / dC_prev are accumulated with vector reductions (zeroed by caller).
+// ------------------------------------------------------------------------------------------------
+template <bool FIRST>
+__global__ void __launch_bounds__(kCellWarps * 32)
+lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
+                     const float* __restrict__ gp, const float* __restrict__ c_prev, const float* __restrict__ c_cur,
+                     const float* __restrict__ dH, const float* __restrict__ dC, float* __restrict__ dA,
+                     float* __restrict__ dX, int dx_overwrite, float* __restrict__ dP, float* __restrict__ dC_prev) {
+    const int lane = threadIdx.x & 31;
+    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (e >= E1) return;
+    const int ld4h = 4 * Hp;
+    float* dAe = dA + (size_t)e * ld4h;
+    float* dXe = dX + (size_t)e * ld4h;
+    if (e == 0) {
+        for (int c = lane * 4; c < ld4h; c += 128) {
+            st4(dAe + c, f4zero());
+            if (dx_overwrite) st4(dXe + c, f4zero());
+        }
+        return;
+    }
+    const XRow xr = xrow(xt, e);
+    const int b = FIRST ? 0 : __ldg(rp + e), en = FIRST ? 0 : __ldg(rp + e + 1);
+    const float* ge = gp + (size_t)e * ld4h;
+    const float4 one = make_float4(1.f, 1.f, 1.f, 1.f);
+    for (int c = lane * 4; c < Hp; c += 128) {
+        float4 ai = xval(xr, c), ao = xval(xr, Hp + c), au = xval(xr, 2 * Hp + c);
+        if (!FIRST) {
+            ai += ld4(ge + c);
+            ao += ld4(ge + Hp + c);
+            au += ld4(ge + 2 * Hp + c);
+        }
+        const float4 gi = sigmoid4(ai), go = sigmoid4(ao), gu = tanh4(au);
+        const float4 th = tanh4(ld4(c_cur + (size_t)e * Hp + c));
+        const float4 dh = clip_cols(ld4(dH + (size_t)e * Hp + c), c, H);
+        float4 dchat = dh * go * (one - th * th);
+        if (dC) dchat += clip_cols(ld4(dC + (size_t)e * Hp + c), c, H);
+        const float4 dai = dchat * gu * gi * (one - gi);
+        const float4 dao = dh * th * go * (one - go);
+        const float4 dau = dchat * gi * (one - gu * gu);
+        float4 dafs = f4zero();
+        if (!FIRST) {
+            const float4 xf = xval(xr, 3 * Hp + c);
+            for (int j = b; j < en; ++j) {
+                const int n = __ldg(col + j);
+                const float4 f = sigmoid4(xf + ld4(gp + (size_t)n * ld4h + 3 * Hp + c));
+                const float4 cn = ld4(c_prev + (size_t)n * Hp + c);
+                const float4 daf = dchat * cn * f * (one - f);
+                dafs += daf;
+                red_add4(dP + (size_t)n * Hp + c, daf);
+                red_add4(dC_prev + (size_t)n * Hp + c, dchat * f);
+            }
+        }
+        st4(dAe + c, dai);
+        st4(dAe + Hp + c, dao);
+        st4(dAe + 2 * Hp + c, dau);
+        st4(dAe + 3 * Hp + c, dafs);
+        if (dx_overwrite) {
+            st4(dXe + c, dai);
+            st4(dXe + Hp + c, dao);
+            st4(dXe + 2 * Hp + c, dau);
+            st4(dXe + 3 * Hp + c, dafs);
+        } else {
+            st4(dXe + c, ld4(dXe + c) + dai);
+            st4(dXe + Hp + c, ld4(dXe + Hp + c) + dao);
+            st4(dXe + 2 * Hp + c, ld4(dXe + 2 * Hp + c) + dau);
+            st4(dXe + 3 * Hp + c, ld4(dXe + 3 * Hp + c) + dafs);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// GRU kernels.  aux row layout (5*Hp): [S | Gz | Gh | Pr | Sg];  x-gates (3*Hp): [z | h | r]
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCellWarps * 32)
+gru_gate_kernel(int E1, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
+                const float* __restrict__ h_prev, float* __restrict__ aux) {
+    const int lane = threadIdx.x & 31;
+    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (e >= E1) return;
+    const int ld = 5 * Hp;
+    const XRow xr = xrow(xt, e);
+    const int b = __ldg(rp + e), en = __ldg(rp + e + 1);
+    for (int c = lane * 4; c < Hp; c += 128) {
+        const float4 xrr = xval(xr, 2 * Hp + c);
+        float4 sg = f4zero();
+        for (int j = b; j < en; ++j) {
+            const int n = __ldg(col + j);
+            const float4 r = sigmoid4(xrr + ld4(aux + (size_t)n * ld + 3 * Hp + c));
+            sg = fma4(r, ld4(h_prev + (size_t)n * Hp + c), sg);
+        }
+        st4(aux + (size_t)e * ld + 4 * Hp + c, sg);
+    }
+}
+
+__global__ void __launch_bounds__(kCellWarps * 32)
+gru_out_kernel(int E1, int H, int Hp, XTab xt, const float* __restrict__ aux, float* __restrict__ h_out) {
+    const int lane = threadIdx.x & 31;
+    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (e >= E1) return;
+    const int ld = 5 * Hp;
+    const float4 one = make_float4(1.f, 1.f, 1.f, 1.f);
+    if (e == 0) {
+        for (int c = lane * 4; c < Hp; c += 128) st4(h_out + c, f4zero());
+        return;
+    }
+    const XRow xr = xrow(xt, e);
+    const float* a = aux + (size_t)e * ld;
+    for (int c = lane * 4; c < Hp; c += 128) {
+        const float4 z = sigmoid4(xval(xr, c) + ld4(a + Hp + c));
+        const float4 cand = tanh4(xval(xr, Hp + c) + ld4(a + 2 * Hp + c));
+        const float4 s = ld4(a + c);
+        st4(h_out + (size_t)e * Hp + c, clip_cols((one - z) * s + z * cand, c, H));
+    }
+}
+
+// dA[e] = [daz | dah], dS[e] = dH (1 - z)
+__global__ void __launch_bounds__(kCellWarps * 32)
+gru_out_bwd_kernel(int E1, int H, int Hp, XTab xt, const float* __restrict__ aux, const float* __restrict__ dH,
+                   float* __restrict__ dA, float* __restrict__ dS) {
+    const int lane = threadIdx.x & 31;
+    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (e >= E1) return;
+    const int ld = 5 * Hp;
+    const float4 one = make_float4(1.f, 1.f, 1.f, 1.f);
+    if (e == 0) {
+        for (int c = lane * 4; c < Hp; c += 128) {
+            st4(dA + c, f4zero());
+            st4(dA + Hp + c, f4zero());
+            st4(dS + c, f4zero());
+        }
+        return;
+    }
+    const XRow xr = xrow(xt, e);
+    const float* a = aux + (size_t)e * ld;
+    for (int c = lane * 4; c < Hp; c += 128) {
+        const float4 z = sigmoid4(xval(xr, c) + ld4(a + Hp + c));
+        const float4 cand = tanh4(xval(xr, Hp + c) + ld4(a + 2 * Hp + c));
+        const float4 s = ld4(a + c);
+        const float4 dh = clip_cols(ld4(dH + (size_t)e * Hp + c), c, H);
+        st4(dA + (size_t)e * 2 * Hp + c, dh * (cand - s) * z * (one - z));
+        st4(dA + (size_t)e * 2 * Hp + Hp + c, dh * z * (one - cand * cand));
+        st4(dS + (size_t)e * Hp + c, dh * (one - z));
+    }
+}
+
+// per pair (e, n): reset-gate backward; dX[e] += [daz | dah | sum_n dar_en]; atomics into dPr[n], dHn[n]
+__global__ void __launch_bounds__(kCellWarps * 32)
+gru_pair_bwd_kernel(int E1, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
+                    const float* __restrict__ aux, const float* __restrict__ h_prev, const float* __restrict__ dA,
+                    const float* __restrict__ dS, const float* __restrict__ dSg, float* __restrict__ dX,
+                    int dx_overwrite, int with_pairs, float* __restrict__ dPr, float* __restrict__ dHn) {
+    const int lane = threadIdx.x & 31;
+    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (e >= E1) return;
+    const int ld = 5 * Hp;
+    const float4 one = make_float4(1.f, 1.f, 1.f, 1.f);
+    const XRow xr = xrow(xt, e);
+    const int b = with_pairs ? __ldg(rp + e) : 0, en = with_pairs ? __ldg(rp + e + 1) : 0;
+    float* dXe = dX + (size_t)e * 3 * Hp;
+    for (int c = lane * 4; c < Hp; c += 128) {
+        float4 dxr = f4zero();
+        if (en > b) {
+            const float4 xrr = xval(xr, 2 * Hp + c);
+            const float4 dsg = ld4(dSg + (size_t)e * Hp + c);
+            const float4 ds = ld4(dS + (size_t)e * Hp + c);
+            for (int j = b; j < en; ++j) {
+                const int n = __ldg(col + j);
+                const float4 r = sigmoid4(xrr + ld4(aux + (size_t)n * ld + 3 * Hp + c));
+                const float4 dar = dsg * ld4(h_prev + (size_t)n * Hp + c) * r * (one - r);
+                dxr += dar;
+                red_add4(dPr + (size_t)n * Hp + c, dar);
+                red_add4(dHn + (size_t)n * Hp + c, ds + dsg * r);
+            }
+        }
+        const float4 daz = ld4(dA + (size_t)e * 2 * Hp + c), dah = ld4(dA + (size_t)e * 2 * Hp + Hp + c);
+        if (dx_overwrite) {
+            st4(dXe + c, daz);
+            st4(dXe + Hp + c, dah);
+            st4(dXe + 2 * Hp + c, dxr);
+        } else {
+            st4(dXe + c, ld4(dXe + c) + daz);
+            st4(dXe + Hp + c, ld4(dXe + Hp + c) + dah);
+            st4(dXe + 2 * Hp + c, ld4(dXe + 2 * Hp + c) + dxr);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// element-wise helpers
+// ------------------------------------------------------------------------------------------------
+__global__ void act_bwd_kernel(const float* __restrict__ dY, int ld_dy, const float* __restrict__ Y, int ld_y,
+                               float* __restrict__ dZ, int ld_dz, int rows, int width, int act, int zero_row0) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)rows * width) return;
+    int r = (int)(i / width), c = (int)(i % width);
+    float g = dY[(size_t)r * ld_dy + c];
+    float y = Y[(size_t)r * ld_y + c];
+    if (act == GGPM_ACT_RELU) g = y > 0.f ? g : 0.f;
+    else if (act == GGPM_ACT_TANH) g = g * (1.f - y * y);
+    else if (act == GGPM_ACT_SIGMOID) g = g * y * (1.f - y);
+    if (zero_row0 && r == 0) g = 0.f;
+    dZ[(size_t)r * ld_dz + c] = g;
+}
+
+constexpr int kColsumRows = 256;
+__global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X, int ld_x, int rows, int width,
+                                                     float* __restrict__ out) {
+    // block: 32 columns x 8 row-lanes; grid.x over column groups, grid.y over row chunks
+    __shared__ float part[8][33];
+    const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cx;
+    const int r0 = blockIdx.y * kColsumRows;
+    const int r1 = min(rows, r0 + kColsumRows);
+    float s = 0.f;
+    if (c < width)
+        for (int r = r0 + ry; r < r1; r += 8) s += X[(size_t)r * ld_x + c];
+    part[ry][cx] = s;
+    __syncthreads();
+    if (ry == 0 && c < width) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += part[k][cx];
+        atomicAdd(out + c, t);
+    }
+}
+
+constexpr int kTabRows = 32;      // max table rows held in shared memory
+constexpr int kTabChunk = 512;    // message rows per block
+__global__ void __launch_bounds__(256)
+table_wgrad_kernel(const float* __restrict__ dX, int ld_dx, int rows, int width, const int* __restrict__ k1,
+                   const int* __restrict__ k2, float* __restrict__ dT, int ld_dt, int ntab) {
+    // block: 128 columns (32 lanes x float4) x 8 warps over a chunk of rows; accumulate per table row in smem
+    __shared__ float acc[kTabRows][128];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < kTabRows * 128; i += blockDim.x) (&acc[0][0])[i] = 0.f;
+    __syncthreads();
+    const int c = blockIdx.x * 128 + lane * 4;
+    const int r0 = blockIdx.y * kTabChunk, r1 = min(rows, r0 + kTabChunk);
+    if (c < width) {
+        for (int r = r0 + w; r < r1; r += 8) {
+            const float4 v = ld4(dX + (size_t)r * ld_dx + c);
+            const int a = __ldg(k1 + r);
+            atomicAdd(&acc[a][lane * 4 + 0], v.x);
+            atomicAdd(&acc[a][lane * 4 + 1], v.y);
+            atomicAdd(&acc[a][lane * 4 + 2], v.z);
+            atomicAdd(&acc[a][lane * 4 + 3], v.w);
+            if (k2) {
+                const int b = __ldg(k2 + r);
+                atomicAdd(&acc[b][lane * 4 + 0], v.x);
+                atomicAdd(&acc[b][lane * 4 + 1], v.y);
+                atomicAdd(&acc[b][lane * 4 + 2], v.z);
+                atomicAdd(&acc[b][lane * 4 + 3], v.w);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < ntab * 128; i += blockDim.x) {
+        int k = i >> 7, cc = blockIdx.x * 128 + (i & 127);
+        float v = acc[k][i & 127];
+        if (cc < width && v != 0.f) atomicAdd(dT + (size_t)k * ld_dt + cc, v);
+    }
+}
+
+// ---- launchers ----------------------------------------------------------------------------------
+static inline int cell_blocks(int E1) { return ceil_div(E1, kCellWarps); }
+
+int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
+                         const float* gp, const float* c_prev, float* h_out, float* c_out, cudaStream_t st) {
+    XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
+    ProfScope prof(PROF_CELL_FWD, st, 0.0);
+    if (first)
+        lstm_cell_fwd_kernel<true><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out);
+    else
+        lstm_cell_fwd_kernel<false><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out);
+    return check_launch("lstm_cell_fwd");
+}
+
+int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
+                         const float* gp, const float* c_prev, const float* c_cur, const float* dH, const float* dC,
+                         float* dA, float* dX, bool dx_overwrite, float* dP, float* dC_prev, cudaStream_t st) {
+    XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
+    ProfScope prof(PROF_CELL_BWD, st, 0.0);
+    if (first)
+        lstm_cell_bwd_kernel<true><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, dx_overwrite, dP, dC_prev);
+    else
+        lstm_cell_bwd_kernel<false><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, dx_overwrite, dP, dC_prev);
+    return check_launch("lstm_cell_bwd");
+}
+
+int launch_gru_gate(int E1, int Hp, const int* rp, const int* col, const XTabArgs& x, const float* h_prev, float* aux,
+                    cudaStream_t st) {
+    XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 3 * Hp};
+    ProfScope prof(PROF_CELL_FWD, st, 0.0);
+    gru_gate_kernel<<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, Hp, rp, col, xt, h_prev, aux);
+    return check_launch("gru_gate");
+}
+
+int launch_gru_out(int E1, int H, int Hp, const XTabArgs& x, const float* aux, float* h_out, cudaStream_t st) {
+    XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 3 * Hp};
+    ProfScope prof(PROF_CELL_FWD, st, 0.0);
+    gru_out_kernel<<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, xt, aux, h_out);
+    return check_launch("gru_out");
+}
+
+int launch_gru_out_bwd(int E1, int H, int Hp, const XTabArgs& x, const float* aux, const float* dH, float* dA, float* dS,
+                       cudaStream_t st) {
+    XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 3 * Hp};
+    ProfScope prof(PROF_CELL_BWD, st, 0.0);
+    gru_out_bwd_kernel<<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, xt, aux, dH, dA, dS);
+    return check_launch("gru_out_bwd");
+}
+
+int launch_gru_pair_bwd(int E1, int Hp, const int* rp, const int* col, const XTabArgs& x, const float* aux,
+                        const float* h_prev, const float* dA, const float* dS, const float* dSg, float* dX,
+                        bool dx_overwrite, bool with_pairs, float* dPr, float* dHn, cudaStream_t st) {
+    XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 3 * Hp};
+    ProfScope prof(PROF_CELL_BWD, st, 0.0);
+    gru_pair_bwd_kernel<<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, Hp, rp, col, xt, aux, h_prev, dA, dS, dSg, dX,
+                                                                    dx_overwrite, with_pairs, dPr, dHn);
+    return check_launch("gru_pair_bwd");
+}
+
+}  // namespace ggpm
+
+using namespace ggpm;
+
+extern "C" int ggpm_act_bwd(const float* dY, int ld_dy, const float* Y, int ld_y, float* dZ, int ld_dz, int rows,
+                            int width, int act, int zero_row0, void* stream) {
+    GGPM_REQUIRE(dY && Y && dZ, "act_bwd: null pointer");
+    if (rows <= 0 || width <= 0) return 0;
+    long long n = (long long)rows * width;
+    act_bwd_kernel<<<(unsigned)ceil_div_ll(n, 256), 256, 0, (cudaStream_t)stream>>>(dY, ld_dy, Y, ld_y, dZ, ld_dz, rows,
+                                                                                 width, act, zero_row0);
+    return check_launch("act_bwd");
+}
+
+extern "C" int ggpm_colsum(const float* X, int ld_x, int rows, int width, float* out, int accumulate, void* stream) {
+    GGPM_REQUIRE(X && out, "colsum: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (width <= 0) return 0;
+    if (!accumulate) GGPM_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * (size_t)width, st));
+    if (rows <= 0) return 0;
+    dim3 grid(ceil_div(width, 32), ceil_div(rows, kColsumRows));
+    colsum_kernel<<<grid, 256, 0, st>>>(X, ld_x, rows, width, out);
+    return check_launch("colsum");
+}
+
+extern "C" int ggpm_table_wgrad(const float* dX, int ld_dx, int rows, int width, const int32_t* k1, const int32_t* k2,
+                                float* dT, int ld_dt, int n_table_rows, void* stream) {
+    GGPM_REQUIRE(dX && k1 && dT, "table_wgrad: null pointer");
+    GGPM_REQUIRE(n_table_rows > 0 && n_table_rows <= kTabRows, "table_wgrad: at most %d table rows", kTabRows);
+    GGPM_REQUIRE(width % 4 == 0 && ld_dx % 4 == 0, "table_wgrad: width/ld must be multiples of 4");
+    if (rows <= 0) return 0;
+    dim3 grid(ceil_div(width, 128), ceil_div(rows, kTabChunk));
+    table_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(dX, ld_dx, rows, width, k1, k2, dT, ld_dt, n_table_rows);
+    return check_launch("table_wgrad");
+}

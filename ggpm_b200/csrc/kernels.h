@@ -1,0 +1,46 @@
+// Internal launcher prototypes shared between the translation units of libggpm_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/ggpm_b200.h"
+
+namespace ggpm {
+
+struct GemmArgs {
+    const float* A = nullptr; long long sam = 0, sak = 1;   // A(m,k) = A[m*sam + k*sak]
+    const float* B = nullptr; long long sbk = 1, sbn = 0;   // B(k,n) = B[k*sbk + n*sbn]
+    float* C = nullptr; int ldc = 0;
+    int M = 0, N = 0, K = 0;
+    float beta = 0.f;
+    const float* bias = nullptr;
+    int act = GGPM_ACT_NONE;
+    int zero_row0 = 0;
+    int split_k = 1;
+};
+
+int launch_gemm_simt(const GemmArgs& g, cudaStream_t st);
+// C[M,N] = A[M,K] * W[N,K]^T (+ epilogue); picks the tcgen05 3xTF32 kernel when the shape allows it
+int launch_gemm_nt(const GemmArgs& g, cudaStream_t st);
+
+struct XTabArgs {   // hoisted x-projection: X_g[e] = Yn[src[e], g] + T[k1[e], g] (+ T[k2[e], g])
+    const float* Yn; const int* src; const float* T; const int* k1; const int* k2;
+};
+
+int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
+                         const float* gp, const float* c_prev, float* h_out, float* c_out, cudaStream_t st);
+int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
+                         const float* gp, const float* c_prev, const float* c_cur, const float* dH, const float* dC,
+                         float* dA, float* dX, bool dx_overwrite, float* dP, float* dC_prev, cudaStream_t st);
+int launch_gru_gate(int E1, int Hp, const int* rp, const int* col, const XTabArgs& x, const float* h_prev, float* aux,
+                    cudaStream_t st);
+int launch_gru_out(int E1, int H, int Hp, const XTabArgs& x, const float* aux, float* h_out, cudaStream_t st);
+int launch_gru_out_bwd(int E1, int H, int Hp, const XTabArgs& x, const float* aux, const float* dH, float* dA, float* dS,
+                       cudaStream_t st);
+int launch_gru_pair_bwd(int E1, int Hp, const int* rp, const int* col, const XTabArgs& x, const float* aux,
+                        const float* h_prev, const float* dA, const float* dS, const float* dSg, float* dX,
+                        bool dx_overwrite, bool with_pairs, float* dPr, float* dHn, cudaStream_t st);
+
+int launch_gather_sum(const float* table, int ld_t, const int* row_ptr, const int* col, float* out, int ld_o,
+                      int rows, int width, bool accumulate, cudaStream_t st);
+
+}  // namespace ggpm

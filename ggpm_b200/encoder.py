@@ -1,0 +1,203 @@
+"""Hierarchical message-passing encoder — drop-in for ggpm/encoder.py MPNEncoder (:8-38),
+HierMPNEncoder (:41-157) and MotifEncoder (:252-341).
+
+Same constructor arguments (the configs/*.json keys rnn_type, embed_size, hidden_size, depthT, depthG,
+dropout), same forward inputs/outputs, same parameter names / shapes / registration order (state_dicts
+load strictly both ways), same tie_embedding contract.  All arithmetic on the path runs in
+libggpm_b200.so; hidden-state tables are carried internally at a padded width Hp (multiple of 32) and
+sliced to H on return.  nn.Dropout / nn.Embedding stay torch modules (they are tied to the decoder's
+modules by tie_embedding and must keep the reference's RNG behaviour).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+from ._lib import ACT_RELU, ACT_TANH
+from .nnutils import to_cuda
+from .rnn import GRU, LSTM
+
+N_BOND_TYPES = 4     # len(MolGraph.BOND_LIST), ggpm/mol_graph.py:14
+MAX_POS = 20         # MolGraph.MAX_POS, ggpm/mol_graph.py:15
+
+
+def _i32(t: torch.Tensor) -> torch.Tensor:
+    return t.to(torch.int32).contiguous()
+
+
+def _public(t: torch.Tensor, H: int) -> torch.Tensor:
+    """padded internal table -> fresh contiguous [rows, H] tensor"""
+    return t if t.shape[1] == H else t[:, :H].contiguous()
+
+
+class MPNEncoder(nn.Module):
+
+    def __init__(self, rnn_type, input_size, node_fdim, hidden_size, depth, dropout):
+        super(MPNEncoder, self).__init__()
+        self.hidden_size = hidden_size
+        self.input_size = input_size
+        self.depth = depth
+        self.W_o = nn.Sequential(
+            nn.Linear(node_fdim + hidden_size, hidden_size),
+            nn.ReLU(),
+            nn.Dropout(dropout)
+        )
+        if rnn_type == 'GRU':
+            self.rnn = GRU(input_size, hidden_size, depth)
+        elif rnn_type == 'LSTM':
+            self.rnn = LSTM(input_size, hidden_size, depth)
+        else:
+            raise ValueError('unsupported rnn cell type ' + rnn_type)
+
+    # -- factored path used by the hierarchical encoders ------------------------------------------------
+    def encode(self, phi_n, phi_x, mg: Fn.MessageGraph, a_csr: Fn.CSR, n_feat_x: int, n_bias_rows: int):
+        """phi_n [N1, >=F]: node features for the read-out; phi_x [N1, >=Fx]: node features feeding the
+        message inputs x_e = [phi_x[src_e] | one-hots].  Returns padded (node [N1, Hp], h [E1, Hp],
+        incoming [N1, Hp]) where incoming[v] = sum of final messages into v."""
+        H = self.hidden_size
+        F = self.W_o[0].in_features - H
+        out = self.rnn.messages(phi_x[:, :n_feat_x], mg, n_feat_x, n_bias_rows)
+        h = out[0] if isinstance(out, tuple) else out
+        incoming = Fn.gather_sum(h, a_csr)                                    # ggpm/encoder.py:31-32
+        w = self.W_o[0].weight
+        node = Fn.linear_act([phi_n[:, :F], incoming[:, :H]], [w[:, :F], w[:, F:]], self.W_o[0].bias,
+                             act=ACT_RELU, zero_row0=True, out_width=h.shape[1])   # :33-38 (mask commutes with dropout)
+        node = self.W_o[2](node)
+        return node, h, incoming
+
+    # -- reference signature (dense message inputs) -----------------------------------------------------
+    def forward(self, fnode, fmess, agraph, bgraph):
+        from .rnn import _identity_graph
+        if fnode.shape[0] != agraph.shape[0]:
+            raise ValueError("fnode and agraph disagree on the number of nodes")
+        mg = _identity_graph(fmess, bgraph)
+        a_csr = Fn.csr_from_padded(agraph, fmess.shape[0])
+        H = self.hidden_size
+        F = self.W_o[0].in_features - H
+        out = self.rnn.messages(fmess, mg, self.input_size, 1)
+        h = out[0] if isinstance(out, tuple) else out
+        incoming = Fn.gather_sum(h, a_csr)
+        w = self.W_o[0].weight
+        node = Fn.linear_act([fnode[:, :F], incoming[:, :H]], [w[:, :F], w[:, F:]], self.W_o[0].bias,
+                             act=ACT_RELU, zero_row0=True)
+        return self.W_o[2](node), _public(h, H)
+
+
+class _TreeBatch:
+    """Per-batch index structures shared by the attachment and motif layers."""
+
+    def __init__(self, tree_tensors):
+        fnode, fmess, agraph, bgraph, cgraph, scope = tree_tensors
+        self.n_nodes, self.n_mess = fnode.shape[0], fmess.shape[0]
+        self.fnode = fnode
+        self.cgraph = cgraph
+        self.a = Fn.csr_from_padded(agraph, self.n_mess)
+        b = Fn.csr_from_padded(bgraph, self.n_mess)
+        self.mg = Fn.MessageGraph(b, _i32(fmess[:, 0]), _i32(fmess[:, 2]), None, self.n_nodes, MAX_POS)
+        self.roots = torch.tensor([st for st, le in scope], dtype=torch.long, device=fnode.device)
+
+
+def _root_vectors(W_root, feat, incoming, roots, H):
+    """W_root([feat[root] | sum of final messages into root]) with tanh, ggpm/encoder.py:128-138"""
+    w = W_root[0].weight
+    f = feat.index_select(0, roots)
+    m = incoming.index_select(0, roots)
+    return Fn.linear_act([f[:, :H], m[:, :H]], [w[:, :H], w[:, H:]], W_root[0].bias, act=ACT_TANH)
+
+
+class HierMPNEncoder(nn.Module):
+
+    def __init__(self, vocab, avocab, rnn_type, embed_size, hidden_size, depthT, depthG, dropout):
+        super(HierMPNEncoder, self).__init__()
+        self.vocab = vocab
+        self.hidden_size = hidden_size
+        self.dropout = dropout
+        self.atom_size = atom_size = avocab.size()
+        self.bond_size = bond_size = N_BOND_TYPES + MAX_POS
+
+        self.E_c = nn.Sequential(nn.Embedding(vocab.size()[0], embed_size), nn.Dropout(dropout))
+        self.E_i = nn.Sequential(nn.Embedding(vocab.size()[1], embed_size), nn.Dropout(dropout))
+        self.W_c = nn.Sequential(nn.Linear(embed_size + hidden_size, hidden_size), nn.ReLU(), nn.Dropout(dropout))
+        self.W_i = nn.Sequential(nn.Linear(embed_size * 2, hidden_size), nn.ReLU(), nn.Dropout(dropout))
+
+        # plain tensors, not buffers: absent from state_dict and re-bindable by tie_embedding (ggpm/encoder.py:74-77)
+        self.E_a = to_cuda(torch.eye(atom_size))
+        self.E_b = to_cuda(torch.eye(N_BOND_TYPES))
+        self.E_apos = to_cuda(torch.eye(MAX_POS))
+        self.E_pos = to_cuda(torch.eye(MAX_POS))
+
+        self.W_root = nn.Sequential(nn.Linear(hidden_size * 2, hidden_size), nn.Tanh())
+        self.tree_encoder = MPNEncoder(rnn_type, hidden_size + MAX_POS, hidden_size, hidden_size, depthT, dropout)
+        self.inter_encoder = MPNEncoder(rnn_type, hidden_size + MAX_POS, hidden_size, hidden_size, depthT, dropout)
+        self.graph_encoder = MPNEncoder(rnn_type, atom_size + bond_size, atom_size, hidden_size, depthG, dropout)
+
+    def tie_embedding(self, other):
+        self.E_c, self.E_i = other.E_c, other.E_i
+        self.E_a, self.E_b = other.E_a, other.E_b
+
+    def forward(self, tree_tensors, graph_tensors):
+        H = self.hidden_size
+        g_fnode, g_fmess, g_agraph, g_bgraph, _ = graph_tensors
+        tb = _TreeBatch(tree_tensors)
+
+        # atom layer: x_e = [E_a[atom(src_e)] | E_b[bond_e] | E_apos[pos_e]]  (embed_graph, :119-126)
+        n_atoms, n_bonds = g_fnode.shape[0], g_fmess.shape[0]
+        atom_feat = self.E_a.index_select(0, g_fnode)
+        mg = Fn.MessageGraph(Fn.csr_from_padded(g_bgraph, n_bonds), _i32(g_fmess[:, 0]), _i32(g_fmess[:, 2]),
+                             _i32(g_fmess[:, 3] + N_BOND_TYPES), n_atoms, N_BOND_TYPES + MAX_POS)
+        hatom, _, _ = self.graph_encoder.encode(atom_feat, atom_feat, mg, Fn.csr_from_padded(g_agraph, n_bonds),
+                                                self.atom_size, N_BOND_TYPES)
+
+        # attachment layer (embed_inter, :96-107)
+        attach_emb = self.E_i(tb.fnode[:, 1])
+        atoms_of_motif = Fn.gather_sum(hatom, Fn.csr_from_padded(tb.cgraph, n_atoms))
+        wi = self.W_i[0].weight
+        E = attach_emb.shape[1]
+        inter_feat = Fn.linear_act([attach_emb, atoms_of_motif[:, :H]], [wi[:, :E], wi[:, E:]], self.W_i[0].bias,
+                                   act=ACT_RELU, out_width=hatom.shape[1])
+        inter_feat = self.W_i[2](inter_feat)
+        hinter, _, _ = self.inter_encoder.encode(inter_feat, inter_feat, tb.mg, tb.a, H, MAX_POS)
+
+        # motif layer (embed_tree, :109-117)
+        motif_emb = self.E_c(tb.fnode[:, 0])
+        wc = self.W_c[0].weight
+        E = motif_emb.shape[1]
+        tree_feat = Fn.linear_act([motif_emb, hinter[:, :H]], [wc[:, :E], wc[:, E:]], self.W_c[0].bias,
+                                  act=ACT_RELU, out_width=hatom.shape[1])
+        tree_feat = self.W_c[2](tree_feat)
+        hnode, _, incoming = self.tree_encoder.encode(tree_feat, tree_feat, tb.mg, tb.a, H, MAX_POS)
+
+        hroot = _root_vectors(self.W_root, tree_feat, incoming, tb.roots, H)
+        return hroot, _public(hnode, H), _public(hinter, H), _public(hatom, H)
+
+
+class MotifEncoder(nn.Module):
+
+    def __init__(self, vocab, avocab, rnn_type, embed_size, hidden_size, depthT, depthG, dropout):
+        super(MotifEncoder, self).__init__()
+        self.vocab = vocab
+        self.hidden_size = hidden_size
+        self.dropout = dropout
+        self.atom_size = atom_size = avocab.size()
+        self.bond_size = bond_size = N_BOND_TYPES + MAX_POS
+
+        self.E_c = nn.Sequential(nn.Embedding(vocab.size()[0], embed_size), nn.Dropout(dropout))
+        self.E_i = nn.Sequential(nn.Embedding(vocab.size()[1], embed_size), nn.Dropout(dropout))
+        self.W_root = nn.Sequential(nn.Linear(hidden_size * 2, hidden_size), nn.Tanh())
+        self.E_a = to_cuda(torch.eye(atom_size))
+        self.E_pos = to_cuda(torch.eye(MAX_POS))
+        self.tree_encoder = MPNEncoder(rnn_type, hidden_size + MAX_POS, hidden_size, hidden_size, depthT, dropout)
+
+    def tie_embedding(self, other):
+        self.E_c, self.E_i = other.E_c, other.E_i
+        self.E_a = other.E_a
+
+    def forward(self, tree_tensors):
+        H = self.hidden_size
+        tb = _TreeBatch(tree_tensors)
+        motif_emb = self.E_c(tb.fnode[:, 0])         # node feature of the read-out (embed_tree, :305-317)
+        attach_emb = self.E_i(tb.fnode[:, 1])        # feeds the message inputs
+        node, _, incoming = self.tree_encoder.encode(motif_emb, attach_emb, tb.mg, tb.a, H, MAX_POS)
+        root = _root_vectors(self.W_root, motif_emb, incoming, tb.roots, H)
+        return root, _public(node, H)

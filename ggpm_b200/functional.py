@@ -1,0 +1,376 @@
+"""Autograd functions over the C ABI (libggpm_b200.so): CSR index prep, neighbour gather-sum, fused
+linear layers and the graph LSTM / GRU message passing with hand-written backward.
+
+PyTorch is used for device memory (caching allocator), the stream and the autograd graph between
+these nodes; every FLOP and every gathered byte of the hot path goes through the CUDA library.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import ACT_NONE, ACT_RELU, ACT_TANH, call, fptr, iptr, stream_ptr
+
+
+def round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def padded_width(hidden: int) -> int:
+    """internal row width of hidden-state tables: multiple of 32 floats (16-byte rows, K tiles of 32)"""
+    return round_up(hidden, 32)
+
+
+# ----------------------------------------------------------------------------------------------
+# CSR neighbour lists
+# ----------------------------------------------------------------------------------------------
+class CSR:
+    """Non-zero entries of a padded [rows, width] index tensor (ggpm/nnutils.py:105-110) in slot order,
+    plus (lazily) the reverse lists used by the backward pass."""
+
+    def __init__(self, row_ptr, col, rows, n_src):
+        self.row_ptr, self.col, self.rows, self.n_src = row_ptr, col, rows, n_src
+        self._t = None
+
+    @property
+    def T(self) -> "CSR":
+        if self._t is None:
+            dev = self.row_ptr.device
+            cap = max(1, self.col.numel())
+            t_ptr = torch.empty(self.n_src + 1, dtype=torch.int32, device=dev)
+            t_row = torch.empty(cap, dtype=torch.int32, device=dev)
+            t_pos = torch.empty(cap, dtype=torch.int32, device=dev)
+            cursor = torch.empty(self.n_src, dtype=torch.int32, device=dev)
+            call("ggpm_csr_transpose", iptr(self.row_ptr), iptr(self.col), self.rows, self.n_src,
+                 iptr(t_ptr), iptr(t_row), iptr(t_pos), iptr(cursor), stream_ptr(dev))
+            t = CSR(t_ptr, t_row, self.n_src, self.rows)
+            t.pos = t_pos
+            t._t = self
+            self._t = t
+        return self._t
+
+
+def csr_from_padded(index: torch.Tensor, n_src: int, check: bool = False) -> CSR:
+    """index: [rows, width] int64 (what make_cuda yields, ggpm/nnutils.py:210-214) or int32, on the GPU."""
+    _lib.require_device(index, "index tensor")
+    if index.dtype not in (torch.int64, torch.int32):
+        raise ValueError("index tensors must be int64 or int32, got %s" % index.dtype)
+    if index.dim() == 1:
+        index = index.unsqueeze(1)
+    if index.dim() != 2:
+        raise ValueError("index tensor must be 2-D [rows, width]")
+    index = index.contiguous()
+    rows, width = index.shape
+    if rows < 1:
+        raise ValueError("index tensor needs at least the padding row")
+    dev = index.device
+    row_ptr = torch.empty(rows + 1, dtype=torch.int32, device=dev)
+    col = torch.empty(max(1, rows * width), dtype=torch.int32, device=dev)
+    bad = torch.zeros(1, dtype=torch.int32, device=dev)
+    call("ggpm_csr_from_padded", index.data_ptr(), int(index.dtype == torch.int64), rows, width, n_src,
+         iptr(row_ptr), iptr(col), iptr(bad), stream_ptr(dev))
+    if check and int(bad.item()) != 0:
+        raise IndexError("neighbour index out of range [0, %d)" % n_src)
+    return CSR(row_ptr, col, rows, n_src)
+
+
+def _row_stride(t: torch.Tensor) -> int:
+    return t.stride(0) if t.shape[0] > 1 else max(t.shape[1], 1)
+
+
+def _aligned_table(t: torch.Tensor) -> torch.Tensor:
+    """fp32 2-D, unit column stride, row stride % 4 == 0, 16-byte aligned base (copy only if violated)"""
+    if t.dim() != 2:
+        raise ValueError("expected a 2-D table")
+    ok = t.stride(1) == 1 and _row_stride(t) % 4 == 0 and t.data_ptr() % 16 == 0 and t.shape[1] % 4 == 0
+    if ok:
+        return t
+    w = round_up(t.shape[1], 4)
+    out = torch.zeros(t.shape[0], w, dtype=t.dtype, device=t.device)
+    out[:, :t.shape[1]] = t
+    return out
+
+
+def _gather_sum_raw(table: torch.Tensor, csr: CSR, width: int) -> torch.Tensor:
+    out = torch.empty(csr.rows, width, dtype=torch.float32, device=table.device)
+    call("ggpm_gather_sum", fptr(table, "table"), _row_stride(table), iptr(csr.row_ptr), iptr(csr.col),
+         fptr(out), width, csr.rows, width, 0, stream_ptr(table.device))
+    return out
+
+
+class GatherSum(torch.autograd.Function):
+    """out[r] = sum_{j in csr row r} table[col[j]]  ==  index_select_ND(table, 0, index).sum(1)
+    (ggpm/nnutils.py:65-70 + .sum(dim=1) at ggpm/rnn.py:26,86 and ggpm/encoder.py:32,100,136)."""
+
+    @staticmethod
+    def forward(ctx, table, csr):
+        if table.shape[0] != csr.n_src:
+            raise ValueError("table has %d rows, index expects %d" % (table.shape[0], csr.n_src))
+        src = _aligned_table(table)
+        ctx.csr, ctx.width, ctx.cols = csr, src.shape[1], table.shape[1]
+        out = _gather_sum_raw(src, csr, src.shape[1])
+        return out if out.shape[1] == table.shape[1] else out[:, :table.shape[1]]
+
+    @staticmethod
+    def backward(ctx, dout):
+        g = _aligned_table(dout)
+        if g.shape[1] != ctx.width:
+            gg = torch.zeros(g.shape[0], ctx.width, dtype=g.dtype, device=g.device)
+            gg[:, :g.shape[1]] = g
+            g = gg
+        dt = _gather_sum_raw(g, ctx.csr.T, ctx.width)
+        return (dt if ctx.cols == ctx.width else dt[:, :ctx.cols]), None
+
+
+def gather_sum(table: torch.Tensor, csr: CSR) -> torch.Tensor:
+    return GatherSum.apply(table, csr)
+
+
+# ----------------------------------------------------------------------------------------------
+# dense layers
+# ----------------------------------------------------------------------------------------------
+def _gemm(A, sam, sak, B, sbk, sbn, C, M, N, K, beta=0.0, bias=None, act=ACT_NONE, zero_row0=False, split_k=1):
+    call("ggpm_gemm", fptr_any(A), sam, sak, fptr_any(B), sbk, sbn, fptr(C), _row_stride(C), M, N, K, float(beta),
+         None if bias is None else fptr(bias), act, int(zero_row0), split_k, stream_ptr(C.device))
+
+
+def fptr_any(t):
+    _lib.require_device(t)
+    if t.dtype != torch.float32:
+        raise ValueError("expected float32, got %s" % t.dtype)
+    return t.data_ptr()
+
+
+def _kmajor(t: torch.Tensor) -> torch.Tensor:
+    """2-D fp32 with unit stride along dim 1 (views of weights / padded tables are fine)"""
+    if t.dim() != 2:
+        raise ValueError("expected a 2-D operand")
+    return t if (t.stride(1) == 1 or t.shape[1] == 1) else t.contiguous()
+
+
+def gemm_nt(A, W, out=None, beta=0.0, bias=None, act=ACT_NONE, zero_row0=False, out_width=None):
+    """out[M, :N] = act(A[M,K] @ W[N,K]^T + beta*out + bias)"""
+    A, W = _kmajor(A), _kmajor(W)
+    M, K = A.shape
+    N = W.shape[0]
+    if W.shape[1] != K:
+        raise ValueError("gemm_nt: K mismatch %d vs %d" % (K, W.shape[1]))
+    if out is None:
+        width = N if out_width is None else out_width
+        out = (torch.empty if width == N else torch.zeros)(M, width, dtype=torch.float32, device=A.device)
+    _gemm(A, _row_stride(A), 1, W, 1, _row_stride(W), out, M, N, K, beta, bias, act, zero_row0)
+    return out
+
+
+def gemm_nn(A, B, out=None, beta=0.0):
+    """out[M,N] = A[M,K] @ B[K,N] (+ beta*out), B row-major"""
+    A, B = _kmajor(A), _kmajor(B)
+    M, K = A.shape
+    N = B.shape[1]
+    if B.shape[0] != K:
+        raise ValueError("gemm_nn: K mismatch")
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.float32, device=A.device)
+    _gemm(A, _row_stride(A), 1, B, _row_stride(B), 1, out, M, N, K, beta)
+    return out
+
+
+def gemm_tn(A, B, out=None, beta=0.0):
+    """out[M,N] = A[K,M]^T @ B[K,N] (+ beta*out): weight gradients, split over K to fill the GPU"""
+    A, B = _kmajor(A), _kmajor(B)
+    K, M = A.shape
+    N = B.shape[1]
+    if B.shape[0] != K:
+        raise ValueError("gemm_tn: K mismatch")
+    if out is None:
+        out = torch.zeros(M, N, dtype=torch.float32, device=A.device)
+        beta = 1.0
+    tiles = ((M + 127) // 128) * ((N + 127) // 128)
+    splits = max(1, min((2 * 148 + tiles - 1) // tiles, (K + 255) // 256))
+    if splits > 1 and beta == 0.0:
+        out.zero_()
+        beta = 1.0
+    _gemm(A, 1, _row_stride(A), B, _row_stride(B), 1, out, M, N, K, beta, split_k=splits)
+    return out
+
+
+class LinearAct(torch.autograd.Function):
+    """Y = act(sum_i A_i @ W_i^T + b), optional zero row 0.  Replaces cat + nn.Linear + ReLU/Tanh + mask
+    (ggpm/encoder.py:33-38, 101, 112, 137-138) without building the concatenation."""
+
+    @staticmethod
+    def forward(ctx, bias, act, zero_row0, out_width, *ops):
+        n = len(ops) // 2
+        As, Ws = ops[:n], ops[n:]
+        out = None
+        for i, (A, W) in enumerate(zip(As, Ws)):
+            last = i == n - 1
+            out = gemm_nt(A, W, out=out, beta=0.0 if i == 0 else 1.0, bias=bias if last else None,
+                          act=act if last else ACT_NONE, zero_row0=zero_row0 and last, out_width=out_width)
+        ctx.act, ctx.zero_row0, ctx.n, ctx.N = act, zero_row0, n, Ws[0].shape[0]
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(out, *ops)
+        return out
+
+    @staticmethod
+    def backward(ctx, dY):
+        out, *ops = ctx.saved_tensors
+        n, N = ctx.n, ctx.N
+        As, Ws = ops[:n], ops[n:]
+        dY = _kmajor(dY)
+        M = out.shape[0]
+        dZ = torch.empty(M, N, dtype=torch.float32, device=out.device)
+        call("ggpm_act_bwd", fptr(dY), _row_stride(dY), fptr(out), _row_stride(out), fptr(dZ), N, M, N, ctx.act,
+             int(ctx.zero_row0), stream_ptr(out.device))
+        dbias = None
+        if ctx.has_bias and ctx.needs_input_grad[0]:
+            dbias = torch.empty(N, dtype=torch.float32, device=out.device)
+            call("ggpm_colsum", fptr(dZ), N, M, N, fptr(dbias), 0, stream_ptr(out.device))
+        grads: List[Optional[torch.Tensor]] = []
+        for i, (A, W) in enumerate(zip(As, Ws)):
+            grads.append(gemm_nn(dZ, W) if ctx.needs_input_grad[4 + i] else None)
+        for i, (A, W) in enumerate(zip(As, Ws)):
+            grads.append(gemm_tn(dZ, A) if ctx.needs_input_grad[4 + n + i] else None)
+        return (dbias, None, None, None, *grads)
+
+
+def linear_act(As: Sequence[torch.Tensor], Ws: Sequence[torch.Tensor], bias, act=ACT_NONE, zero_row0=False,
+               out_width=None):
+    return LinearAct.apply(bias, act, zero_row0, out_width, *As, *Ws)
+
+
+# ----------------------------------------------------------------------------------------------
+# message passing
+# ----------------------------------------------------------------------------------------------
+class MessageGraph:
+    """Index side of one message-passing layer, prepared once per batch:
+    b (bgraph CSR), src/k1/k2 (int32 per message: source node, one-hot column ids), out-edge lists."""
+
+    def __init__(self, bgraph_csr: CSR, src: torch.Tensor, k1: torch.Tensor, k2: Optional[torch.Tensor],
+                 n_nodes: int, n_table_rows: int):
+        self.b = bgraph_csr
+        self.src, self.k1, self.k2 = src, k1, k2
+        self.n_nodes, self.n_table_rows = n_nodes, n_table_rows
+        self._by_src = None
+
+    @property
+    def E1(self):
+        return self.b.rows
+
+    @property
+    def by_src(self) -> CSR:
+        """for every node, the messages it emits (transpose of the [E1, 1] padded tensor `src`)"""
+        if self._by_src is None:
+            self._by_src = csr_from_padded(self.src.view(-1, 1), self.n_nodes).T
+        return self._by_src
+
+
+def _empty(*shape, device):
+    return torch.empty(*shape, dtype=torch.float32, device=device)
+
+
+class LSTMMessages(torch.autograd.Function):
+    """`depth` rounds of the graph LSTM (ggpm/rnn.py:85-108) over a message graph.
+    phi_x [N1, F]: node features feeding the message inputs; Wx [4Hp, F], T [ntab, 4Hp], Ug [3Hp, Hp],
+    Uf [Hp, Hp]: packed gate weights (ggpm_b200.packing).  Returns (h, c): [E1, Hp] final states."""
+
+    @staticmethod
+    def forward(ctx, phi_x, Wx, T, Ug, Uf, mg: MessageGraph, depth: int, H: int):
+        Hp = Uf.shape[0]
+        E1, dev = mg.E1, Uf.device
+        keep = any(ctx.needs_input_grad)
+        Yn = gemm_nt(phi_x, Wx)                                    # [N1, 4Hp]
+        slots = depth if keep else min(depth, 2)
+        hist_h, hist_c = _empty(slots, E1, Hp, device=dev), _empty(slots, E1, Hp, device=dev)
+        hist_gp = _empty(slots, E1, 4 * Hp, device=dev)
+        scratch = _empty(E1, Hp, device=dev)
+        T, Ug, Uf = T.contiguous(), Ug.contiguous(), Uf.contiguous()
+        call("ggpm_lstm_fwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), fptr(Yn), iptr(mg.src), fptr(T),
+             iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf), fptr(hist_h), fptr(hist_c),
+             fptr(hist_gp), fptr(scratch), int(keep), stream_ptr(dev))
+        last = (depth - 1) if keep else ((depth - 1) & 1)
+        ctx.mg, ctx.depth, ctx.H, ctx.Hp = mg, depth, H, Hp
+        ctx.hist = (hist_h, hist_c, hist_gp, Yn) if keep else None
+        ctx.save_for_backward(phi_x, Wx, T, Ug, Uf)
+        h, c = hist_h[last], hist_c[last]
+        ctx.mark_non_differentiable(c)
+        return h, c
+
+    @staticmethod
+    def backward(ctx, dh, _dc):
+        phi_x, Wx, T, Ug, Uf = ctx.saved_tensors
+        mg, depth, H, Hp = ctx.mg, ctx.depth, ctx.H, ctx.Hp
+        hist_h, hist_c, hist_gp, Yn = ctx.hist
+        E1, dev = mg.E1, Uf.device
+        dH = dh.clone(memory_format=torch.contiguous_format)
+        dX = _empty(E1, 4 * Hp, device=dev)
+        dUg, dUf = torch.zeros_like(Ug), torch.zeros_like(Uf)
+        dA = _empty(E1, 4 * Hp, device=dev)
+        dC, dP, dS = _empty(2, E1, Hp, device=dev), _empty(E1, Hp, device=dev), _empty(E1, Hp, device=dev)
+        S, dHn = _empty(E1, Hp, device=dev), _empty(E1, Hp, device=dev)
+        bt = mg.b.T
+        call("ggpm_lstm_bwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), iptr(bt.row_ptr), iptr(bt.col),
+             fptr(Yn), iptr(mg.src), fptr(T), iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf),
+             fptr(hist_h), fptr(hist_c), fptr(hist_gp), fptr(dH), fptr(dX), fptr(dUg), fptr(dUf), fptr(dA), fptr(dC),
+             fptr(dP), fptr(dS), fptr(S), fptr(dHn), stream_ptr(dev))
+        dphi, dWx, dT = _xproj_backward(ctx, dX, phi_x, Wx, T, mg)
+        return dphi, dWx, dT, dUg, dUf, None, None, None
+
+
+def _xproj_backward(ctx, dX, phi_x, Wx, T, mg: MessageGraph):
+    """dX [E1, G*Hp] -> gradients of the hoisted input projection: node features, packed x-weights, tables"""
+    dev = dX.device
+    dphi = dWx = dT = None
+    if ctx.needs_input_grad[0] or ctx.needs_input_grad[1]:
+        dYn = _gather_sum_raw(dX, mg.by_src, dX.shape[1])                 # [N1, G*Hp]
+        if ctx.needs_input_grad[0]:
+            dphi = gemm_nn(dYn, Wx)
+        if ctx.needs_input_grad[1]:
+            dWx = gemm_tn(dYn, phi_x)
+    if ctx.needs_input_grad[2]:
+        dT = torch.zeros_like(T)
+        call("ggpm_table_wgrad", fptr(dX), dX.shape[1], dX.shape[0], dX.shape[1], iptr(mg.k1),
+             None if mg.k2 is None else iptr(mg.k2), fptr(dT), dT.shape[1], dT.shape[0], stream_ptr(dev))
+    return dphi, dWx, dT
+
+
+class GRUMessages(torch.autograd.Function):
+    """`depth` rounds of the graph GRU (ggpm/rnn.py:25-50).  Wx [3Hp, F], T [ntab, 3Hp] packed [z|h|r];
+    Uz, Ur, Uh [Hp, Hp]; br [Hp].  Returns h [E1, Hp]."""
+
+    @staticmethod
+    def forward(ctx, phi_x, Wx, T, Uz, Ur, br, Uh, mg: MessageGraph, depth: int, H: int):
+        Hp = Uz.shape[0]
+        E1, dev = mg.E1, Uz.device
+        keep = any(ctx.needs_input_grad)
+        Yn = gemm_nt(phi_x, Wx)                                    # [N1, 3Hp]
+        hist_h = _empty(depth + 1 if keep else 2, E1, Hp, device=dev)
+        hist_aux = _empty(depth if keep else 1, E1, 5 * Hp, device=dev)
+        T, Uz, Ur, br, Uh = (t.contiguous() for t in (T, Uz, Ur, br, Uh))
+        call("ggpm_gru_fwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), fptr(Yn), iptr(mg.src), fptr(T),
+             iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Uz), fptr(Ur), fptr(br), fptr(Uh), fptr(hist_h),
+             fptr(hist_aux), int(keep), stream_ptr(dev))
+        ctx.mg, ctx.depth, ctx.H, ctx.Hp = mg, depth, H, Hp
+        ctx.hist = (hist_h, hist_aux, Yn) if keep else None
+        ctx.save_for_backward(phi_x, Wx, T, Uz, Ur, br, Uh)
+        return hist_h[depth if keep else (depth & 1)]
+
+    @staticmethod
+    def backward(ctx, dh):
+        phi_x, Wx, T, Uz, Ur, br, Uh = ctx.saved_tensors
+        mg, depth, H, Hp = ctx.mg, ctx.depth, ctx.H, ctx.Hp
+        hist_h, hist_aux, Yn = ctx.hist
+        E1, dev = mg.E1, Uz.device
+        dH = dh.clone(memory_format=torch.contiguous_format)
+        dX = _empty(E1, 3 * Hp, device=dev)
+        dUz, dUr, dUh, dbr = torch.zeros_like(Uz), torch.zeros_like(Ur), torch.zeros_like(Uh), torch.zeros_like(br)
+        dA = _empty(E1, 2 * Hp, device=dev)
+        dS, dSg, dPr, dHn = (_empty(E1, Hp, device=dev) for _ in range(4))
+        call("ggpm_gru_bwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), fptr(Yn), iptr(mg.src), fptr(T),
+             iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Uz), fptr(Ur), fptr(Uh), fptr(hist_h),
+             fptr(hist_aux), fptr(dH), fptr(dX), fptr(dUz), fptr(dUr), fptr(dbr), fptr(dUh), fptr(dA), fptr(dS),
+             fptr(dSg), fptr(dPr), fptr(dHn), stream_ptr(dev))
+        dphi, dWx, dT = _xproj_backward(ctx, dX, phi_x, Wx, T, mg)
+        return dphi, dWx, dT, dUz, dUr, dbr, dUh, None, None, None

@@ -1,0 +1,72 @@
+"""Tensor utilities of the encoder path — host-side mirror of ggpm/nnutils.py for the functions the
+encoder uses: index_select_ND (:65-70), create_pad_tensor (:105-110), make_tensor / make_cuda
+(:201-214).  Device work goes through libggpm_b200.so; there is no CPU implementation."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import functional as Fn
+
+_DEVICE = None
+
+
+def default_device() -> torch.device:
+    """The reference fixes a global device at import time (ggpm/nnutils.py:9-10: cuda:0 if available).
+    One process per GPU: cuda:<current device> of this process."""
+    if _DEVICE is not None:
+        return _DEVICE
+    if not torch.cuda.is_available():
+        raise RuntimeError("ggpm_b200 needs a CUDA device (the encoder path has no CPU fallback)")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def set_default_device(device):
+    global _DEVICE
+    _DEVICE = None if device is None else torch.device(device)
+
+
+def to_cuda(tensor):
+    return tensor.to(default_device())
+
+
+def index_select_ND(source: torch.Tensor, dim: int, index: torch.Tensor) -> torch.Tensor:
+    """source [R, H], index [M, K] -> [M, K, H]; same semantics as ggpm/nnutils.py:65-70 (padding slots
+    read row `index` points at, normally the zero row 0).  Materialises the result — the encoder itself
+    uses index_select_sum below, which never does."""
+    if dim != 0 or source.dim() != 2:
+        raise ValueError("index_select_ND supports dim=0 on a 2-D source")
+    flat = index.reshape(-1).to(torch.int32)
+    n = flat.numel()
+    row_ptr = torch.arange(n + 1, dtype=torch.int32, device=source.device)
+    csr = Fn.CSR(row_ptr, flat.contiguous(), n, source.shape[0])
+    return Fn.gather_sum(source, csr).reshape(tuple(index.shape) + (source.shape[1],))
+
+
+def index_select_sum(source: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
+    """index_select_ND(source, 0, index).sum(dim=1) as one CSR gather-sum kernel."""
+    return Fn.gather_sum(source, Fn.csr_from_padded(index, source.shape[0]))
+
+
+def create_pad_tensor(alist):
+    """list of id lists -> zero padded IntTensor with one extra trailing zero column (ggpm/nnutils.py:105-110)"""
+    width = max(len(a) for a in alist) + 1
+    out = np.zeros((len(alist), width), dtype=np.int32)
+    for i, a in enumerate(alist):
+        out[i, :len(a)] = a
+    return torch.from_numpy(out)
+
+
+def make_tensor(x):
+    if not isinstance(x, torch.Tensor):
+        x = torch.from_numpy(np.ascontiguousarray(x)) if isinstance(x, np.ndarray) else torch.tensor(x)
+    return to_cuda(x)
+
+
+def make_cuda(tensors):
+    """(tree_tensors, graph_tensors) of numpy / tensors -> torch.long tensors on the device; the trailing
+    `scope` list is passed through (ggpm/nnutils.py:210-214)."""
+    tree_tensors, graph_tensors = tensors
+    tree_tensors = [make_tensor(x).long() for x in tree_tensors[:-1]] + [tree_tensors[-1]]
+    graph_tensors = [make_tensor(x).long() for x in graph_tensors[:-1]] + [graph_tensors[-1]]
+    return tree_tensors, graph_tensors

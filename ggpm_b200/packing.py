@@ -1,0 +1,65 @@
+"""Gate-weight packing for the CUDA message-passing kernels (differentiable torch reshuffling).
+
+The reference stores every gate as nn.Linear(IN + H -> H) applied to the concatenation [x | h]
+(ggpm/rnn.py:13-16, 69-72), with x = [node feature of the source (F columns) | one-hot columns]
+(ggpm/encoder.py:103-106, 114-116, 121-125).  The kernels want, per layer:
+
+  Wx  [G*Hp, F]     x-columns that multiply the node feature, gates stacked along rows
+  T   [ntab, G*Hp]  the one-hot columns transposed into lookup rows; rows [0, n_bias_rows) (the ones
+                    indexed by k1, exactly one of which every message selects) also carry the biases
+  U*  [.., Hp]      the h-columns, zero padded from H to Hp = multiple of 32
+
+These are built with ordinary autograd-tracked torch ops on the nn.Parameters, so parameter
+gradients flow back through the packing without hand-written unpacking, the module keeps the
+reference's state_dict, and nothing is cached across optimizer steps.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F_
+
+
+def _pack_common(weights, biases, F, IN, H, Hp, n_bias_rows):
+    """weights: list of [H, IN(+H)] gate matrices; biases: list of [H] or None (same length)."""
+    G = len(weights)
+    Wall = torch.stack([w[:, :IN] for w in weights])                        # [G, H, IN]
+    Wx = F_.pad(Wall[:, :, :F], (0, 0, 0, Hp - H)).reshape(G * Hp, F)       # [G*Hp, F]
+    ntab = IN - F
+    ball = torch.stack([b if b is not None else torch.zeros_like(weights[0][:, 0]) for b in biases])  # [G, H]
+    if ntab == 0:
+        # dense message inputs (no one-hot columns): a single lookup row that carries the biases
+        ntab, T = 1, ball.unsqueeze(0)
+    else:
+        T = Wall[:, :, F:IN].permute(2, 0, 1)                               # [ntab, G, H]
+        carrier = torch.zeros(ntab, 1, 1, dtype=Wall.dtype, device=Wall.device)
+        carrier[:n_bias_rows] = 1.0
+        T = T + carrier * ball.unsqueeze(0)
+    T = F_.pad(T, (0, Hp - H)).reshape(ntab, G * Hp)
+    return Wx, T
+
+
+def _pad_square(u, H, Hp):
+    return F_.pad(u, (0, Hp - H, 0, Hp - H))
+
+
+def pack_lstm(rnn, F: int, Hp: int, n_bias_rows: int):
+    """rnn: module with W_i, W_o, W_f, W = Sequential(Linear(IN+H -> H), act).  Gate order [i | o | u | f]."""
+    H, IN = rnn.hidden_size, rnn.input_size
+    lin = [rnn.W_i[0], rnn.W_o[0], rnn.W[0], rnn.W_f[0]]
+    Wx, T = _pack_common([l.weight for l in lin], [l.bias for l in lin], F, IN, H, Hp, n_bias_rows)
+    Ug = torch.cat([_pad_square(l.weight[:, IN:], H, Hp) for l in lin[:3]], dim=0)    # [3Hp, Hp]
+    Uf = _pad_square(lin[3].weight[:, IN:], H, Hp)
+    return Wx, T, Ug, Uf
+
+
+def pack_gru(rnn, F: int, Hp: int, n_bias_rows: int):
+    """rnn: module with W_z, W_h = Linear(IN+H -> H), W_r = Linear(IN -> H, no bias), U_r = Linear(H -> H).
+    x-gate order [z | h | r]."""
+    H, IN = rnn.hidden_size, rnn.input_size
+    Wx, T = _pack_common([rnn.W_z.weight, rnn.W_h.weight, rnn.W_r.weight], [rnn.W_z.bias, rnn.W_h.bias, None],
+                         F, IN, H, Hp, n_bias_rows)
+    Uz = _pad_square(rnn.W_z.weight[:, IN:], H, Hp)
+    Uh = _pad_square(rnn.W_h.weight[:, IN:], H, Hp)
+    Ur = _pad_square(rnn.U_r.weight, H, Hp)
+    br = F_.pad(rnn.U_r.bias, (0, Hp - H))
+    return Wx, T, Uz, Ur, br, Uh

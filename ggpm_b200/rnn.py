@@ -1,0 +1,99 @@
+"""Graph GRU / LSTM cells over a directed message graph — drop-in for ggpm/rnn.py (GRU :5-59,
+LSTM :61-121), forward path.  Same constructor, attribute names, parameter names/shapes/registration
+order (so state_dicts interchange), same forward(fmess, bgraph) contract; the arithmetic runs in
+libggpm_b200.so (hoisted x-projection, CSR neighbour lists, hand-written BPTT)."""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+from . import packing
+
+
+def _identity_graph(fmess: torch.Tensor, bgraph: torch.Tensor) -> Fn.MessageGraph:
+    """dense message inputs: every message is its own 'node', one table row carries the bias"""
+    E1 = fmess.shape[0]
+    dev = fmess.device
+    src = torch.arange(E1, dtype=torch.int32, device=dev)
+    k1 = torch.zeros(E1, dtype=torch.int32, device=dev)
+    return Fn.MessageGraph(Fn.csr_from_padded(bgraph, E1), src, k1, None, E1, 1)
+
+
+class _GraphRNN(nn.Module):
+    def __init__(self, input_size, hidden_size, depth):
+        super().__init__()
+        self.hidden_size = hidden_size
+        self.input_size = input_size
+        self.depth = depth
+
+    @property
+    def padded_hidden(self):
+        return Fn.padded_width(self.hidden_size)
+
+    def _check(self, fmess, bgraph):
+        if fmess.dim() != 2 or fmess.shape[1] != self.input_size:
+            raise ValueError("fmess must be [E, %d], got %s" % (self.input_size, tuple(fmess.shape)))
+        if bgraph.shape[0] != fmess.shape[0]:
+            raise ValueError("bgraph and fmess disagree on the number of messages")
+
+
+class GRU(_GraphRNN):
+
+    def __init__(self, input_size, hidden_size, depth):
+        super().__init__(input_size, hidden_size, depth)
+        self.W_z = nn.Linear(input_size + hidden_size, hidden_size)
+        self.W_r = nn.Linear(input_size, hidden_size, bias=False)
+        self.U_r = nn.Linear(hidden_size, hidden_size)
+        self.W_h = nn.Linear(input_size + hidden_size, hidden_size)
+
+    def get_init_state(self, fmess, init_state=None):
+        h = torch.zeros(len(fmess), self.hidden_size, device=fmess.device)
+        return h if init_state is None else torch.cat((h, init_state), dim=0)
+
+    def get_hidden_state(self, h):
+        return h
+
+    def messages(self, phi_x, mg: Fn.MessageGraph, n_feat: int, n_bias_rows: int):
+        """factored entry used by the encoders: x_e = [phi_x[src_e] | one-hot(k1_e) | one-hot(k2_e)];
+        returns the padded final state [E1, Hp]"""
+        Hp = self.padded_hidden
+        Wx, T, Uz, Ur, br, Uh = packing.pack_gru(self, n_feat, Hp, n_bias_rows)
+        return Fn.GRUMessages.apply(phi_x, Wx, T, Uz, Ur, br, Uh, mg, self.depth, self.hidden_size)
+
+    def forward(self, fmess, bgraph):
+        self._check(fmess, bgraph)
+        h = self.messages(fmess, _identity_graph(fmess, bgraph), self.input_size, 1)
+        return h[:, :self.hidden_size].contiguous()
+
+
+class LSTM(_GraphRNN):
+
+    def __init__(self, input_size, hidden_size, depth):
+        super().__init__(input_size, hidden_size, depth)
+        self.W_i = nn.Sequential(nn.Linear(input_size + hidden_size, hidden_size), nn.Sigmoid())
+        self.W_o = nn.Sequential(nn.Linear(input_size + hidden_size, hidden_size), nn.Sigmoid())
+        self.W_f = nn.Sequential(nn.Linear(input_size + hidden_size, hidden_size), nn.Sigmoid())
+        self.W = nn.Sequential(nn.Linear(input_size + hidden_size, hidden_size), nn.Tanh())
+
+    def get_init_state(self, fmess, init_state=None):
+        h = torch.zeros(len(fmess), self.hidden_size, device=fmess.device)
+        c = torch.zeros(len(fmess), self.hidden_size, device=fmess.device)
+        if init_state is not None:
+            h = torch.cat((h, init_state), dim=0)
+            c = torch.cat((c, torch.zeros_like(init_state)), dim=0)
+        return h, c
+
+    def get_hidden_state(self, h):
+        return h[0]
+
+    def messages(self, phi_x, mg: Fn.MessageGraph, n_feat: int, n_bias_rows: int):
+        Hp = self.padded_hidden
+        Wx, T, Ug, Uf = packing.pack_lstm(self, n_feat, Hp, n_bias_rows)
+        return Fn.LSTMMessages.apply(phi_x, Wx, T, Ug, Uf, mg, self.depth, self.hidden_size)
+
+    def forward(self, fmess, bgraph):
+        self._check(fmess, bgraph)
+        h, c = self.messages(fmess, _identity_graph(fmess, bgraph), self.input_size, 1)
+        H = self.hidden_size
+        return h[:, :H].contiguous(), c[:, :H].contiguous()

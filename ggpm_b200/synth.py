@@ -199,3 +199,24 @@ def batch_stats(tree_tensors, graph_tensors):
         nnz_bA=int(np.count_nonzero(gb)), nnz_aA=int(np.count_nonzero(ga)),
         nnz_bT=int(np.count_nonzero(tb)), nnz_aT=int(np.count_nonzero(ta)), nnz_c=int(np.count_nonzero(tc)),
     )
+
+
+class SizeOnlyPairVocab:
+    """Motif vocabulary stand-in: the encoder constructor only calls .size() (ggpm/encoder.py:52,57);
+    defaults are PairVocab(trio_polymer_vocab.txt).size() == (721, 6215)."""
+
+    def __init__(self, n_motif=721, n_attach=6215):
+        self._size = (n_motif, n_attach)
+
+    def size(self):
+        return self._size
+
+
+class SizeOnlyAtomVocab:
+    """common_atom_vocab stand-in (ggpm/vocab.py:64-69): 38 atom types."""
+
+    def __init__(self, n=38):
+        self._n = n
+
+    def size(self):
+        return self._n

@@ -1,0 +1,146 @@
+/* ggpm_b200 — C ABI of the B200 (sm_100a) hierarchical message-passing encoder kernels.
+ *
+ * Drop-in boundary for ggpm's encoder hot path.  The reference has no FFI of its own (it is pure
+ * PyTorch); these entry points are what a binding for that path has to call.  Each one cites the
+ * reference code it replaces (paths relative to the reference checkout).  The Python host side
+ * (ggpm_b200/_lib.py) binds them with ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every pointer is a DEVICE pointer on the current CUDA device;
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); all work is
+ *    enqueued on it, nothing synchronises, nothing is allocated: callers own every buffer;
+ *  - float tables are fp32 row-major with a leading dimension (`ld*`, in floats) that is a multiple of
+ *    4 and a 16-byte aligned base; the hidden width H is carried in a padded width Hp (multiple of 32,
+ *    zero-filled columns H..Hp-1) so rows stay 16-byte aligned for 128-bit loads and tensor-core tiles;
+ *  - neighbour lists are CSR (int32 row_ptr[rows+1], col[nnz]) over 1-based row ids with id 0 = padding;
+ *  - return value: 0 = ok, non-zero = error; ggpm_last_error() returns the message (thread local).
+ *  - no CPU fallback exists: without a CUDA device every compute entry point fails.
+ */
+#ifndef GGPM_B200_H
+#define GGPM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GGPM_ACT_NONE 0
+#define GGPM_ACT_RELU 1
+#define GGPM_ACT_TANH 2
+#define GGPM_ACT_SIGMOID 3
+
+/* GEMM engines (ggpm_set_gemm_engine): AUTO picks tcgen05 3xTF32 whenever the shape allows it */
+#define GGPM_ENGINE_AUTO 0
+#define GGPM_ENGINE_SIMT_FP32 1
+#define GGPM_ENGINE_TCGEN05_3XTF32 2
+
+const char* ggpm_last_error(void);
+int ggpm_abi_version(void);
+int ggpm_set_gemm_engine(int engine);
+int ggpm_get_gemm_engine(void);
+/* number of kernels this library has launched since load (bench.py "gpu_launches") */
+long long ggpm_launch_count(void);
+
+/* Optional per-launch timing for the roofline report (bench.py): while enabled, every kernel launch is
+ * bracketed by CUDA events on its stream.  Classes: 0 gather-sum, 1 tcgen05 GEMM, 2 fp32 CUDA-core GEMM,
+ * 3 weight-gradient GEMM, 4 forward cell, 5 backward cell, 6 misc.  collect() synchronises the device and
+ * returns, per class, summed milliseconds, launch count and algorithmic work (FLOPs for GEMMs, bytes for
+ * gather-sum excluding the data-dependent neighbour rows, which the caller adds from nnz). */
+int ggpm_prof_enable(int on);
+int ggpm_prof_collect(double* ms, long long* count, double* work, int n_class);
+
+/* ---- index construction ------------------------------------------------------------------------
+ * Padded neighbour tensor (create_pad_tensor, ggpm/nnutils.py:105-110; rows built by
+ * MolGraph.tensorize_graph, ggpm/mol_graph.py:238-281) -> CSR of its non-zero entries in slot order.
+ * idx: [rows, width] int64 (idx_is_64bit=1, the dtype make_cuda produces, ggpm/nnutils.py:210-214) or
+ * int32.  row_ptr: [rows+1]; col: capacity rows*width; *bad_flag is set to 1 if an entry is outside
+ * [0, n_src_rows).  nnz stays on the device (row_ptr[rows]). */
+int ggpm_csr_from_padded(const void* idx, int idx_is_64bit, int rows, int width, int n_src_rows,
+                         int32_t* row_ptr, int32_t* col, int32_t* bad_flag, void* stream);
+
+/* Reverse CSR: for every source row n the destination rows that list it (t_row, ascending) and the
+ * position of that entry in the forward `col` array (t_pos).  This is the deterministic form of the
+ * scatter-add that autograd runs for index_select (ggpm/nnutils.py:65-70).  cursor: scratch [n_src_rows]. */
+int ggpm_csr_transpose(const int32_t* row_ptr, const int32_t* col, int rows, int n_src_rows,
+                       int32_t* t_ptr, int32_t* t_row, int32_t* t_pos, int32_t* cursor, void* stream);
+
+/* ---- neighbour gather-sum ----------------------------------------------------------------------
+ * out[r, 0:width] (+)= sum_{j in row r} table[col[j], 0:width]
+ * == index_select_ND(table, 0, index).sum(dim=1)   (ggpm/nnutils.py:65-70; ggpm/rnn.py:26,86;
+ * ggpm/encoder.py:31-32,100,135-136).  With the reverse CSR it is the backward of the same. */
+int ggpm_gather_sum(const float* table, int ld_table, const int32_t* row_ptr, const int32_t* col,
+                    float* out, int ld_out, int rows, int width, int accumulate, void* stream);
+
+/* ---- dense layers --------------------------------------------------------------------------------
+ * C[M,N] = act( A(M,K) * B(K,N) + beta*C + bias[n] ), row 0 optionally forced to 0.
+ * A(m,k) = A[m*sam + k*sak], B(k,n) = B[k*sbk + n*sbn] (one stride of each operand must be 1).
+ * Replaces nn.Linear + activation + row-0 mask: W_o (ggpm/encoder.py:15-19,33-38), W_i / W_c
+ * (ggpm/encoder.py:62-72,101,112), W_root (ggpm/encoder.py:79-82,138), their autograd backward
+ * (input grads: B = W; weight grads: A transposed, split_k > 1 accumulates atomically into C). */
+int ggpm_gemm(const float* A, long long sam, long long sak, const float* B, long long sbk, long long sbn,
+              float* C, int ldc, int M, int N, int K, float beta, const float* bias, int act,
+              int zero_row0, int split_k, void* stream);
+
+/* dZ = dY * act'(Y) with row 0 optionally zeroed (backward of the fused epilogue above). */
+int ggpm_act_bwd(const float* dY, int ld_dy, const float* Y, int ld_y, float* dZ, int ld_dz, int rows,
+                 int width, int act, int zero_row0, void* stream);
+
+/* out[c] (+)= sum_r X[r, c]  (bias gradients) */
+int ggpm_colsum(const float* X, int ld_x, int rows, int width, float* out, int accumulate, void* stream);
+
+/* dT[k, :] += sum_{e: k1[e]==k} dX[e, :] + sum_{e: k2[e]==k} dX[e, :]   (k2 may be NULL)
+ * Weight gradient of the one-hot part of the message input (E_b / E_apos / E_pos columns,
+ * ggpm/encoder.py:104-106,114-116,121-125): the one-hot GEMM collapses to a row scatter. */
+int ggpm_table_wgrad(const float* dX, int ld_dx, int rows, int width, const int32_t* k1, const int32_t* k2,
+                     float* dT, int ld_dt, int n_table_rows, void* stream);
+
+/* ---- graph LSTM over a message graph ---------------------------------------------------------------
+ * LSTM.forward (ggpm/rnn.py:96-108) with the cell of ggpm/rnn.py:85-94, `depth` rounds, h0 = c0 = 0, row 0
+ * masked after every round.  The depth-invariant input projection is hoisted and never materialised:
+ *     x-part of gate g for message e:  Yn[src[e], g] + T[k1[e], g] (+ T[k2[e], g])
+ * with Yn = (node features) x (x-columns of W_i|W_o|W|W_f)^T, T = the one-hot columns (+bias), both with
+ * 4*Hp columns packed [i | o | u | f].  Ug = [U_i;U_o;U_u] ([3Hp, Hp] row-major, h-columns of the gate
+ * weights), Uf [Hp, Hp].  The forget gate is factored per SOURCE message: P = h U_f^T, f_en = s(Xf_e + P_n).
+ * History buffers (saved for backward): hist_h, hist_c: [slots, E1, Hp]; hist_gp: [slots, E1, 4Hp]
+ * ([G_i|G_o|G_u|P]); slots = depth when keep_history, else 2 (ping-pong).  s_scratch: [E1, Hp].
+ * The final hidden state is slot (depth-1) (keep_history) or slot ((depth-1) & 1). */
+int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
+                  const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
+                  const float* Ug, const float* Uf, float* hist_h, float* hist_c, float* hist_gp,
+                  float* s_scratch, int keep_history, void* stream);
+
+/* Back-propagation through time of the above (what autograd does for ggpm/rnn.py:96-108).
+ * dH_final: [E1, Hp] gradient w.r.t. the final hidden state (consumed, used as scratch).
+ * Outputs: dX [E1, 4Hp] = accumulated gradient of the hoisted x-projection (zeroed here), dUg [3Hp, Hp] and
+ * dUf [Hp, Hp] (accumulated into: caller zeroes).  bt_*: reverse CSR of (b_ptr, b_col).
+ * Scratch: dA [E1, 4Hp], dC [2, E1, Hp], dP [E1, Hp], dS [E1, Hp], S [E1, Hp], dHn [E1, Hp]. */
+int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
+                  const int32_t* bt_ptr, const int32_t* bt_row, const float* Yn, const int32_t* src,
+                  const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
+                  const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
+                  float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
+                  void* stream);
+
+/* ---- graph GRU over a message graph ----------------------------------------------------------------
+ * GRU.forward (ggpm/rnn.py:41-50) with the cell of ggpm/rnn.py:25-39.  x-gates packed [z | h | r] (3*Hp
+ * columns of Yn / T); Uz, Ur, Uh: [Hp, Hp]; br: [Hp] (bias of U_r).  History: hist_h [slots, E1, Hp] holds
+ * h^{t-1} of every round (slot 0 = zeros) plus the final state in slot `depth`; hist_aux [depth, E1, 5Hp] =
+ * [S | Gz | Gh | Pr | Sg] per round (keep_history) or [1, E1, 5Hp]. */
+int ggpm_gru_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col, const float* Yn,
+                 const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2, const float* Uz,
+                 const float* Ur, const float* br, const float* Uh, float* hist_h, float* hist_aux,
+                 int keep_history, void* stream);
+
+/* BPTT of the above.  Outputs: dX [E1, 3Hp] (zeroed here), dUz, dUr, dUh [Hp, Hp], dbr [Hp] (accumulated
+ * into).  Scratch: dA [E1, 2Hp], dS [E1, Hp], dSg [E1, Hp], dPr [E1, Hp], dHn [E1, Hp]. */
+int ggpm_gru_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col, const float* Yn,
+                 const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2, const float* Uz,
+                 const float* Ur, const float* Uh, const float* hist_h, const float* hist_aux, float* dH_final,
+                 float* dX, float* dUz, float* dUr, float* dbr, float* dUh, float* dA, float* dS, float* dSg,
+                 float* dPr, float* dHn, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGPM_B200_H */

@@ -1,0 +1,266 @@
+"""TEST INFRASTRUCTURE ONLY — host emulator of the C ABI in include/ggpm_b200.h.
+
+Implements every entry point on raw HOST addresses (ctypes -> numpy -> torch views) with the torch twins
+of tests/_proto.py, honouring the same buffer layouts (history slots, leading dimensions, in-place
+accumulation).  tests install it through ggpm_b200._lib._install_test_backend so that the Python host
+side of the product (index prep, weight packing, autograd wiring, pointer/stride arithmetic) can be
+exercised on a box without a GPU.  The product never imports this file; on a GPU box the real
+libggpm_b200.so is what runs (and what the -m gpu tests check against the oracle).
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+import _proto as P
+
+DT = torch.float64     # emulate in fp64, store fp32
+
+
+def _arr(ptr, n, ctype, npdtype):
+    if n == 0:
+        return np.zeros(0, dtype=npdtype)
+    return np.ctypeslib.as_array((ctype * n).from_address(int(ptr)))
+
+
+def _f(ptr, n):
+    return torch.from_numpy(_arr(ptr, n, ctypes.c_float, np.float32))
+
+
+def _i(ptr, n):
+    return torch.from_numpy(_arr(ptr, n, ctypes.c_int32, np.int32))
+
+
+def _tab(ptr, rows, ld, width):
+    """strided [rows, width] fp32 view with leading dimension ld"""
+    flat = _f(ptr, (rows - 1) * ld + width if rows > 0 else 0)
+    return flat.as_strided((rows, width), (ld, 1))
+
+
+def _csr(ptr_p, col_p, rows):
+    rp = _i(ptr_p, rows + 1).long()
+    return rp, _i(col_p, int(rp[-1])).long()
+
+
+class EmuLib:
+    def __init__(self):
+        self.launches = 0
+        self.engine = 0
+        self.err = b""
+        self.calls = []
+
+    # -- library state ---------------------------------------------------------------------------
+    def ggpm_last_error(self):
+        return self.err
+
+    def ggpm_abi_version(self):
+        return 1
+
+    def ggpm_set_gemm_engine(self, e):
+        self.engine = e
+        return 0
+
+    def ggpm_get_gemm_engine(self):
+        return self.engine
+
+    def ggpm_launch_count(self):
+        return self.launches
+
+    def _tick(self, name):
+        self.launches += 1
+        self.calls.append(name)
+
+    # -- index construction ----------------------------------------------------------------------
+    def ggpm_csr_from_padded(self, idx, is64, rows, width, n_src, row_ptr, col, bad, stream):
+        self._tick("csr_from_padded")
+        n = rows * width
+        a = _arr(idx, n, ctypes.c_int64 if is64 else ctypes.c_int32, np.int64 if is64 else np.int32)
+        index = torch.from_numpy(a.astype(np.int64)).reshape(rows, width)
+        if ((index < 0) | (index >= n_src)).any():
+            _i(bad, 1)[0] = 1
+            index = index.clamp(0, n_src - 1)
+        rp, c = P.csr_from_padded(index)
+        _i(row_ptr, rows + 1).copy_(rp.int())
+        _i(col, len(c)).copy_(c.int())
+        return 0
+
+    def ggpm_csr_transpose(self, row_ptr, col, rows, n_src, t_ptr, t_row, t_pos, cursor, stream):
+        self._tick("csr_transpose")
+        rp, c = _csr(row_ptr, col, rows)
+        dest = P.csr_rows(rp)
+        pos = torch.arange(len(c))
+        order = torch.from_numpy(np.lexsort((pos.numpy(), c.numpy())))
+        tp = torch.zeros(n_src + 1, dtype=torch.long)
+        tp[1:] = torch.cumsum(torch.bincount(c, minlength=n_src), 0)
+        _i(t_ptr, n_src + 1).copy_(tp.int())
+        _i(t_row, len(c)).copy_(dest[order].int())
+        _i(t_pos, len(c)).copy_(pos[order].int())
+        return 0
+
+    # -- primitives ------------------------------------------------------------------------------
+    def ggpm_gather_sum(self, table, ld_t, row_ptr, col, out, ld_o, rows, width, accumulate, stream):
+        self._tick("gather_sum")
+        assert width % 4 == 0 and ld_t % 4 == 0 and ld_o % 4 == 0 and table % 16 == 0 and out % 16 == 0
+        rp, c = _csr(row_ptr, col, rows)
+        n_src = int(c.max()) + 1 if len(c) else 1
+        t = _tab(table, n_src, ld_t, width).to(DT)
+        res = P.gather_sum(t, rp, c)
+        o = _tab(out, rows, ld_o, width)
+        o.copy_((o.to(DT) + res if accumulate else res).float())
+        return 0
+
+    def ggpm_gemm(self, A, sam, sak, B, sbk, sbn, C, ldc, M, N, K, beta, bias, act, zero_row0, split_k, stream):
+        self._tick("gemm")
+        assert sam == 1 or sak == 1, "A needs a unit stride"
+        assert sbk == 1 or sbn == 1, "B needs a unit stride"
+        a = _f(A, (M - 1) * sam + (K - 1) * sak + 1).as_strided((M, K), (sam, sak)).to(DT)
+        b = _f(B, (K - 1) * sbk + (N - 1) * sbn + 1).as_strided((K, N), (sbk, sbn)).to(DT)
+        c = _tab(C, M, ldc, N)
+        r = a @ b
+        if beta != 0:
+            r = r + beta * c.to(DT)
+        if split_k > 1:
+            assert bias is None and act == 0 and not zero_row0
+        if bias is not None:
+            r = r + _f(bias, N).to(DT)
+        r = {0: lambda x: x, 1: torch.relu, 2: torch.tanh, 3: torch.sigmoid}[act](r)
+        if zero_row0:
+            r[0] = 0
+        c.copy_(r.float())
+        return 0
+
+    def ggpm_act_bwd(self, dY, ld_dy, Y, ld_y, dZ, ld_dz, rows, width, act, zero_row0, stream):
+        self._tick("act_bwd")
+        g, y = _tab(dY, rows, ld_dy, width).to(DT), _tab(Y, rows, ld_y, width).to(DT)
+        if act == 1:
+            g = g * (y > 0)
+        elif act == 2:
+            g = g * (1 - y * y)
+        elif act == 3:
+            g = g * y * (1 - y)
+        if zero_row0:
+            g[0] = 0
+        _tab(dZ, rows, ld_dz, width).copy_(g.float())
+        return 0
+
+    def ggpm_colsum(self, X, ld_x, rows, width, out, accumulate, stream):
+        self._tick("colsum")
+        s = _tab(X, rows, ld_x, width).to(DT).sum(0)
+        o = _f(out, width)
+        o.copy_((o.to(DT) + s if accumulate else s).float())
+        return 0
+
+    def ggpm_table_wgrad(self, dX, ld_dx, rows, width, k1, k2, dT, ld_dt, ntab, stream):
+        self._tick("table_wgrad")
+        assert ntab <= 32
+        x = _tab(dX, rows, ld_dx, width).to(DT)
+        t = _tab(dT, ntab, ld_dt, width)
+        acc = t.to(DT)
+        acc.index_add_(0, _i(k1, rows).long(), x)
+        if k2:
+            acc.index_add_(0, _i(k2, rows).long(), x)
+        t.copy_(acc.float())
+        return 0
+
+    # -- LSTM ------------------------------------------------------------------------------------
+    @staticmethod
+    def _xtab(Yn, src, T, k1, k2, E1, G, Hp):
+        s, a = _i(src, E1).long(), _i(k1, E1).long()
+        b = _i(k2, E1).long() if k2 else None
+        n1 = int(s.max()) + 1
+        ntab = max(int(a.max()), int(b.max()) if b is not None else 0) + 1
+        return P.xproj(_tab(Yn, n1, G * Hp, G * Hp).to(DT), s, _tab(T, ntab, G * Hp, G * Hp).to(DT), a, b)
+
+    def ggpm_lstm_fwd(self, E1, H, Hp, depth, b_ptr, b_col, Yn, src, T, k1, k2, Ug, Uf, hist_h, hist_c, hist_gp,
+                      s_scratch, keep, stream):
+        self._tick("lstm_fwd")
+        assert Hp % 32 == 0 and Hp >= H
+        rp, col = _csr(b_ptr, b_col, E1)
+        X = self._xtab(Yn, src, T, k1, k2, E1, 4, Hp)
+        ug, uf = _tab(Ug, 3 * Hp, Hp, Hp).to(DT), _tab(Uf, Hp, Hp, Hp).to(DT)
+        slots = depth if keep else min(depth, 2)
+        hh, hc = _f(hist_h, slots * E1 * Hp).view(slots, E1, Hp), _f(hist_c, slots * E1 * Hp).view(slots, E1, Hp)
+        gp = _f(hist_gp, slots * E1 * 4 * Hp).view(slots, E1, 4 * Hp)
+        h = c = None
+        for t in range(1, depth + 1):
+            cur = (t - 1) if keep else ((t - 1) & 1)
+            if t > 1:
+                G = P.gather_sum(h, rp, col) @ ug.t()
+                Pm = h @ uf.t()
+                gp[cur].copy_(torch.cat([G, Pm], 1).float())
+            else:
+                G = Pm = None
+            h, c = P.lstm_cell_fwd(X, G, Pm, c, rp, col, H, Hp)
+            hh[cur].copy_(h.float())
+            hc[cur].copy_(c.float())
+            h, c = hh[cur].to(DT), hc[cur].to(DT)      # carry fp32-rounded state like the device does
+        return 0
+
+    def ggpm_lstm_bwd(self, E1, H, Hp, depth, b_ptr, b_col, bt_ptr, bt_row, Yn, src, T, k1, k2, Ug, Uf, hist_h,
+                      hist_c, hist_gp, dH_final, dX, dUg, dUf, dA, dC, dP, dS, S, dHn, stream):
+        self._tick("lstm_bwd")
+        rp, col = _csr(b_ptr, b_col, E1)
+        trp, tcol = _csr(bt_ptr, bt_row, E1)
+        # the reverse CSR must be the transpose of the forward one
+        fwd_pairs = sorted(zip(P.csr_rows(rp).tolist(), col.tolist()))
+        rev_pairs = sorted(zip(tcol.tolist(), P.csr_rows(trp).tolist()))
+        assert fwd_pairs == rev_pairs, "bt is not the transpose of b"
+        X = self._xtab(Yn, src, T, k1, k2, E1, 4, Hp)
+        ug, uf = _tab(Ug, 3 * Hp, Hp, Hp).to(DT), _tab(Uf, Hp, Hp, Hp).to(DT)
+        hh = _f(hist_h, depth * E1 * Hp).view(depth, E1, Hp).to(DT)
+        hc = _f(hist_c, depth * E1 * Hp).view(depth, E1, Hp).to(DT)
+        gp = _f(hist_gp, depth * E1 * 4 * Hp).view(depth, E1, 4 * Hp).to(DT)
+        hist = dict(X=X, h=list(hh), c=list(hc), G=[None] + [gp[t][:, :3 * Hp] for t in range(1, depth)],
+                    P=[None] + [gp[t][:, 3 * Hp:] for t in range(1, depth)])
+        dx, dug, duf = P.lstm_layer_bwd(hist, _tab(dH_final, E1, Hp, Hp).to(DT), ug, uf, rp, col, depth, H, Hp)
+        _tab(dX, E1, 4 * Hp, 4 * Hp).copy_(dx.float())
+        g = _tab(dUg, 3 * Hp, Hp, Hp)
+        g.copy_((g.to(DT) + dug).float())
+        f = _tab(dUf, Hp, Hp, Hp)
+        f.copy_((f.to(DT) + duf).float())
+        return 0
+
+    # -- GRU -------------------------------------------------------------------------------------
+    def ggpm_gru_fwd(self, E1, H, Hp, depth, b_ptr, b_col, Yn, src, T, k1, k2, Uz, Ur, br, Uh, hist_h, hist_aux,
+                     keep, stream):
+        self._tick("gru_fwd")
+        rp, col = _csr(b_ptr, b_col, E1)
+        X = self._xtab(Yn, src, T, k1, k2, E1, 3, Hp)
+        uz, ur, uh = (_tab(p, Hp, Hp, Hp).to(DT) for p in (Uz, Ur, Uh))
+        b = _f(br, Hp).to(DT)
+        # run the twin with an already-projected X: feed it through identity tables
+        ident_src = torch.arange(E1)
+        h, hist = P.gru_layer_fwd(X, ident_src, torch.zeros(1, 3 * Hp, dtype=DT), torch.zeros(E1, dtype=torch.long),
+                                  None, uz, ur, b, uh, rp, col, depth, H, Hp)
+        nslots = depth + 1 if keep else 2
+        hh = _f(hist_h, nslots * E1 * Hp).view(nslots, E1, Hp)
+        aux = _f(hist_aux, (depth if keep else 1) * E1 * 5 * Hp).view(-1, E1, 5 * Hp)
+        if keep:
+            for t in range(depth):
+                hh[t].copy_(hist["h"][t].float())
+                aux[t].copy_(torch.cat([hist[k][t] for k in ("S", "Gz", "Gh", "Pr", "Sg")], 1).float())
+            hh[depth].copy_(h.float())
+        else:
+            hh[depth & 1].copy_(h.float())
+        return 0
+
+    def ggpm_gru_bwd(self, E1, H, Hp, depth, b_ptr, b_col, Yn, src, T, k1, k2, Uz, Ur, Uh, hist_h, hist_aux,
+                     dH_final, dX, dUz, dUr, dbr, dUh, dA, dS, dSg, dPr, dHn, stream):
+        self._tick("gru_bwd")
+        rp, col = _csr(b_ptr, b_col, E1)
+        X = self._xtab(Yn, src, T, k1, k2, E1, 3, Hp)
+        uz, ur, uh = (_tab(p, Hp, Hp, Hp).to(DT) for p in (Uz, Ur, Uh))
+        hh = _f(hist_h, (depth + 1) * E1 * Hp).view(depth + 1, E1, Hp).to(DT)
+        aux = _f(hist_aux, depth * E1 * 5 * Hp).view(depth, E1, 5, Hp).to(DT)
+        hist = dict(X=X, h=list(hh[:depth]))
+        for i, k in enumerate(("S", "Gz", "Gh", "Pr", "Sg")):
+            hist[k] = [aux[t][:, i] for t in range(depth)]
+        dx, duz, dur, dbr_, duh = P.gru_layer_bwd(hist, _tab(dH_final, E1, Hp, Hp).to(DT), uz, ur, uh, rp, col,
+                                                  depth, H, Hp)
+        _tab(dX, E1, 3 * Hp, 3 * Hp).copy_(dx.float())
+        for ptr, val in ((dUz, duz), (dUr, dur), (dUh, duh)):
+            t = _tab(ptr, Hp, Hp, Hp)
+            t.copy_((t.to(DT) + val).float())
+        b = _f(dbr, Hp)
+        b.copy_((b.to(DT) + dbr_).float())
+        return 0

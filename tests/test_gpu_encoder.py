@@ -1,0 +1,77 @@
+"""B200: the real CUDA library behind the drop-in modules, against the golden vectors of the unmodified
+reference and the oracle on seeded inputs (fp32 path, tolerance 1e-5 relative on outputs as BASELINE.json's
+north_star states; 2e-5 on gradients).  Every call goes through the C ABI (ggpm_b200/_lib.py)."""
+import os
+import sys
+
+import pytest
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from conftest import golden_names                                     # noqa: E402
+import _checks as C                                                    # noqa: E402
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+SMALL = [n for n in golden_names() if n != "hier_lstm_cfg1"]
+ENGINES = [1, 0]      # 1 = fp32 CUDA cores only, 0 = auto (tcgen05 3xTF32 where the shape allows)
+
+
+@pytest.fixture(params=ENGINES, ids=["simt", "auto"])
+def engine(request):
+    from ggpm_b200 import _lib
+    assert _lib._TEST_BACKEND is None
+    _lib.set_gemm_engine(request.param)
+    yield request.param
+    _lib.set_gemm_engine(0)
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_forward_backward_matches_reference_golden(engine, name):
+    C.check_forward_backward_golden(name, DEV)
+
+
+def test_cfg1_matches_reference_golden(engine):
+    C.check_cfg1(DEV)
+
+
+def test_root_only_loss_leaves_tree_readout_without_grad(engine):
+    C.check_root_only_loss(DEV)
+
+
+def test_no_grad_and_eval_mode(engine):
+    C.check_no_grad_eval(DEV)
+
+
+def test_train_mode_dropout_is_applied():
+    C.check_train_dropout(DEV)
+
+
+def test_inputs_are_not_mutated():
+    C.check_inputs_not_mutated(DEV)
+
+
+@pytest.mark.parametrize("rnn", ["LSTM", "GRU"])
+def test_mpn_encoder_reference_signature(engine, rnn):
+    C.check_mpn_reference_signature(rnn, DEV)
+
+
+def test_index_select_nd():
+    C.check_index_select_nd(DEV)
+
+
+def test_cpu_tensors_are_rejected():
+    import ggpm_b200
+    from oracle.ref_loader import FakePairVocab, IdAtomVocab
+    from conftest import load_golden
+    meta, z, tree, graph = load_golden("motif_lstm_small")
+    model = C.build_model(meta, DEV)
+    with pytest.raises(RuntimeError, match="CUDA devices only"):
+        model(tree)          # index tensors left on the host
+
+
+def test_launches_are_counted():
+    from ggpm_b200 import _lib
+    before = _lib.launch_count()
+    C.check_no_grad_eval(DEV)
+    assert _lib.launch_count() > before

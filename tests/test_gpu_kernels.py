@@ -1,0 +1,269 @@
+"""B200: every CUDA kernel, called through the C ABI, against its torch twin (tests/_proto.py, fp64) or the
+numpy index oracle (oracle/tensorize_oracle.py) on identical seeded inputs.  Integer/index work is compared
+bit-exactly; fp32 arithmetic within 1e-5 relative of the fp64 twin."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import _proto as P                                                     # noqa: E402
+from conftest import load_golden                                       # noqa: E402
+from ggpm_b200 import _lib, functional as Fn, synth                    # noqa: E402
+from oracle import tensorize_oracle as to                              # noqa: E402
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max()) / max(float(b.abs().max()), 1e-30)
+
+
+@pytest.fixture(params=[1, 0], ids=["simt", "auto"])
+def engine(request):
+    _lib.set_gemm_engine(request.param)
+    yield request.param
+    _lib.set_gemm_engine(0)
+
+
+def random_padded(rng, rows, width, n_src, density=0.5, mid_zeros=True):
+    idx = rng.integers(1, n_src, size=(rows, width))
+    keep = rng.random((rows, width)) < density
+    if not mid_zeros:
+        keep = np.sort(keep, axis=1)[:, ::-1]
+    idx = idx * keep
+    idx[0] = 0
+    return idx.astype(np.int64)
+
+
+# ---------------------------------------------------------------------------------------------------
+# index construction: bit-exact
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("rows,width,n_src,dtype", [(1, 1, 1, torch.int64), (2, 3, 2, torch.int64),
+                                                     (1000, 6, 777, torch.int64), (5000, 9, 5000, torch.int32),
+                                                     (300000, 5, 300000, torch.int64)])
+def test_csr_from_padded_and_transpose_bit_exact(rows, width, n_src, dtype):
+    rng = np.random.default_rng(rows + width)
+    idx = random_padded(rng, rows, width, max(n_src, 2)) % n_src
+    csr = Fn.csr_from_padded(torch.from_numpy(idx).to(dtype).to(DEV), n_src, check=True)
+    rp, col = to.csr_from_padded_oracle(idx)
+    assert np.array_equal(csr.row_ptr.cpu().numpy(), rp)
+    nnz = int(rp[-1])
+    assert np.array_equal(csr.col[:nnz].cpu().numpy(), col)
+    tp, trow, tpos = to.csr_transpose_oracle(rp, col, n_src)
+    t = csr.T
+    assert np.array_equal(t.row_ptr.cpu().numpy(), tp)
+    assert np.array_equal(t.col[:nnz].cpu().numpy(), trow)
+    assert np.array_equal(t.pos[:nnz].cpu().numpy(), tpos)
+
+
+def test_csr_of_golden_batch_and_bad_index():
+    meta, z, tree, graph = load_golden("hier_lstm_cfg1")
+    for idx, n_src in ((tree[2], tree[1].shape[0]), (tree[3], tree[1].shape[0]), (tree[4], graph[0].shape[0]),
+                       (graph[2], graph[1].shape[0]), (graph[3], graph[1].shape[0])):
+        csr = Fn.csr_from_padded(idx.to(DEV), n_src, check=True)
+        rp, col = to.csr_from_padded_oracle(idx.numpy())
+        assert np.array_equal(csr.row_ptr.cpu().numpy(), rp)
+        assert np.array_equal(csr.col[:rp[-1]].cpu().numpy(), col)
+    with pytest.raises(IndexError):
+        Fn.csr_from_padded(torch.tensor([[0, 0], [5, 0]], device=DEV), 3, check=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+# gather-sum
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("rows,n_src,width,K", [(1, 1, 4, 1), (50, 40, 40, 3), (2000, 1500, 256, 6),
+                                                 (3000, 3000, 512, 4), (700, 900, 2816, 5), (64, 64, 1024, 40)])
+def test_gather_sum_forward_backward(rows, n_src, width, K):
+    rng = np.random.default_rng(rows)
+    idx = torch.from_numpy(random_padded(rng, rows, K, max(n_src, 2)) % n_src)
+    table = torch.randn(n_src, width, dtype=torch.float64)
+    table[0] = 0
+    rp, col = P.csr_from_padded(idx)
+    expect = P.gather_sum(table, rp, col)
+    t = table.float().to(DEV).requires_grad_(True)
+    csr = Fn.csr_from_padded(idx.to(DEV), n_src)
+    out = Fn.gather_sum(t, csr)
+    assert rel(out, expect) <= 2e-6
+    cot = torch.randn(rows, width, dtype=torch.float64)
+    out.backward(cot.float().to(DEV))
+    assert rel(t.grad, P.scatter_rows(cot, rp, col, n_src)) <= 2e-6
+
+
+def test_gather_sum_unaligned_table_is_repacked():
+    idx = torch.tensor([[0, 0], [1, 2], [2, 0]])
+    table = torch.randn(3, 10, device=DEV)[:, 1:8]           # 7 columns, misaligned base
+    out = Fn.gather_sum(table, Fn.csr_from_padded(idx.to(DEV), 3))
+    ref = torch.stack([torch.zeros(7, device=DEV), table[1] + table[2], table[2]])
+    assert torch.allclose(out, ref, atol=1e-6)
+
+
+# ---------------------------------------------------------------------------------------------------
+# GEMM (all operand layouts, ragged sizes, epilogues)
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K", [(1, 1, 1), (300, 250, 38), (129, 257, 250), (1000, 768, 256), (4097, 256, 256),
+                                    (513, 1024, 512), (200, 704, 720), (130, 2112, 704)])
+def test_gemm_nt_with_epilogue(engine, M, N, K):
+    g = torch.Generator().manual_seed(M + N + K)
+    A = torch.randn(M, K, generator=g, dtype=torch.float64)
+    W = torch.randn(N, K, generator=g, dtype=torch.float64) / K ** 0.5
+    b = torch.randn(N, generator=g, dtype=torch.float64)
+    C0 = torch.randn(M, N, generator=g, dtype=torch.float64)
+    for act, fn in ((0, lambda x: x), (1, torch.relu), (2, torch.tanh)):
+        out = C0.float().to(DEV)
+        Fn.gemm_nt(A.float().to(DEV), W.float().to(DEV), out=out, beta=1.0, bias=b.float().to(DEV), act=act,
+                   zero_row0=True)
+        ref = fn(A.float().double() @ W.float().double().t() + C0.float().double() + b.float().double())
+        ref[0] = 0
+        assert rel(out, ref) <= 1e-5, (act, rel(out, ref))
+
+
+def test_gemm_strided_views_and_padded_output(engine):
+    g = torch.Generator().manual_seed(5)
+    big = torch.randn(500, 300, generator=g).to(DEV)
+    Wfull = torch.randn(250, 538, generator=g).to(DEV) * 0.05
+    A = big[:, :250]                       # row stride 300
+    W = Wfull[:, 288:]                     # row stride 538, misaligned base
+    out = Fn.gemm_nt(A, W, out_width=256)
+    assert out.shape == (500, 256) and float(out[:, 250:].abs().max()) == 0.0
+    assert rel(out[:, :250], A.double() @ W.double().t()) <= 1e-5
+
+
+@pytest.mark.parametrize("M,N,K", [(300, 250, 768), (1000, 256, 256), (77, 40, 1024)])
+def test_gemm_nn_input_gradient(M, N, K):
+    A, B = torch.randn(M, K).to(DEV), (torch.randn(K, N) / K ** 0.5).to(DEV)
+    base = torch.randn(M, N).to(DEV)
+    out = base.clone()
+    Fn.gemm_nn(A, B, out=out, beta=1.0)
+    assert rel(out, A.double() @ B.double() + base.double()) <= 1e-5
+    assert rel(Fn.gemm_nn(A, B), A.double() @ B.double()) <= 1e-5
+
+
+@pytest.mark.parametrize("K,M,N", [(1, 8, 8), (5000, 768, 256), (16001, 256, 250), (300, 38, 1024), (70000, 256, 256)])
+def test_gemm_tn_weight_gradient_split_k(K, M, N):
+    A, B = torch.randn(K, M).to(DEV), torch.randn(K, N).to(DEV)
+    ref = A.double().t() @ B.double()
+    assert rel(Fn.gemm_tn(A, B), ref) <= 1e-5
+    acc = torch.ones(M, N, device=DEV)
+    Fn.gemm_tn(A, B, out=acc, beta=1.0)
+    assert rel(acc, ref + 1.0) <= 1e-5
+    over = torch.full((M, N), 7.0, device=DEV)
+    Fn.gemm_tn(A, B, out=over, beta=0.0)
+    assert rel(over, ref) <= 1e-5
+
+
+def test_linear_act_autograd(engine):
+    g = torch.Generator().manual_seed(9)
+    A1 = torch.randn(400, 38, generator=g, dtype=torch.float64, requires_grad=True)
+    A2 = torch.randn(400, 250, generator=g, dtype=torch.float64, requires_grad=True)
+    W = (torch.randn(250, 288, generator=g, dtype=torch.float64) * 0.1).requires_grad_(True)
+    b = torch.randn(250, generator=g, dtype=torch.float64, requires_grad=True)
+    cot = torch.randn(400, 250, generator=g, dtype=torch.float64)
+    mask = torch.ones(400, 1, dtype=torch.float64)
+    mask[0] = 0
+    ref = torch.relu(torch.cat([A1, A2], 1) @ W.t() + b) * mask
+    (ref * cot).sum().backward()
+    a1, a2, w, bb = (t.detach().float().to(DEV).requires_grad_(True) for t in (A1, A2, W, b))
+    out = Fn.linear_act([a1, a2], [w[:, :38], w[:, 38:]], bb, act=_lib.ACT_RELU, zero_row0=True)
+    assert rel(out, ref) <= 1e-5
+    (out * cot.float().to(DEV)).sum().backward()
+    for got, want in ((a1, A1), (a2, A2), (w, W), (bb, b)):
+        assert rel(got.grad, want.grad) <= 1e-5
+
+
+def test_small_helpers():
+    x = torch.randn(1000, 96, device=DEV)
+    out = torch.ones(96, device=DEV)
+    _lib.call("ggpm_colsum", x.data_ptr(), 96, 1000, 96, out.data_ptr(), 1, None)
+    assert rel(out, x.double().sum(0) + 1) <= 1e-5
+    k1 = torch.randint(0, 4, (1000,), device=DEV, dtype=torch.int32)
+    k2 = torch.randint(4, 24, (1000,), device=DEV, dtype=torch.int32)
+    dT = torch.zeros(24, 96, device=DEV)
+    _lib.call("ggpm_table_wgrad", x.data_ptr(), 96, 1000, 96, k1.data_ptr(), k2.data_ptr(), dT.data_ptr(), 96, 24, None)
+    ref = torch.zeros(24, 96, dtype=torch.float64).index_add_(0, k1.cpu().long(), x.cpu().double())
+    ref.index_add_(0, k2.cpu().long(), x.cpu().double())
+    assert rel(dT, ref) <= 1e-5
+
+
+# ---------------------------------------------------------------------------------------------------
+# whole message-passing layers against the fp64 twins (random packed weights, ragged hidden width)
+# ---------------------------------------------------------------------------------------------------
+def _layer_inputs(H, Hp, G, batch, seed, with_k2):
+    mols = synth.random_batch(seed, batch)
+    tree, graph = synth.tensorize(mols)
+    fnode, fmess, agraph, bgraph = (graph if with_k2 else tree)[:4]
+    E1, N1 = fmess.shape[0], fnode.shape[0]
+    g = torch.Generator().manual_seed(seed)
+    F = 38 if with_k2 else H
+    ntab = 24 if with_k2 else 20
+    colmask = torch.zeros(Hp, dtype=torch.float64)
+    colmask[:H] = 1
+
+    def gate_rows(n):          # [n, G*Hp] with zero pad columns
+        return (torch.randn(n, G, Hp, generator=g, dtype=torch.float64) * 0.3 * colmask).reshape(n, G * Hp)
+    phi = torch.randn(N1, F, generator=g, dtype=torch.float64)
+    Wx = gate_rows(F).t().contiguous()                         # [G*Hp, F]
+    T = gate_rows(ntab)
+    sq = lambda: torch.randn(Hp, Hp, generator=g, dtype=torch.float64) * (0.5 / H ** 0.5) * colmask[:, None] * colmask[None]
+    src = torch.from_numpy(fmess[:, 0].astype(np.int64))
+    k1 = torch.from_numpy(fmess[:, 2].astype(np.int64))
+    k2 = torch.from_numpy(fmess[:, 3].astype(np.int64) + 4) if with_k2 else None
+    bg = torch.from_numpy(bgraph.astype(np.int64))
+    cot = torch.randn(E1, Hp, generator=g, dtype=torch.float64) * colmask
+    return dict(phi=phi, Wx=Wx, T=T, sq=sq, src=src, k1=k1, k2=k2, bg=bg, cot=cot, E1=E1, N1=N1, ntab=ntab)
+
+
+def _message_graph(d):
+    i32 = lambda t: None if t is None else t.to(torch.int32).to(DEV)
+    return Fn.MessageGraph(Fn.csr_from_padded(d["bg"].to(DEV), d["E1"]), i32(d["src"]), i32(d["k1"]), i32(d["k2"]),
+                           d["N1"], d["ntab"])
+
+
+@pytest.mark.parametrize("H,Hp,depth,batch,with_k2", [(20, 32, 3, 3, False), (250, 256, 5, 8, True), (60, 64, 20, 4, False)])
+def test_lstm_layer_forward_backward(engine, H, Hp, depth, batch, with_k2):
+    d = _layer_inputs(H, Hp, 4, batch, 100 + H, with_k2)
+    Ug = torch.cat([d["sq"](), d["sq"](), d["sq"]()], 0)
+    Uf = d["sq"]()
+    rp, col = P.csr_from_padded(d["bg"])
+    Yn = d["phi"] @ d["Wx"].t()
+    h_ref, hist = P.lstm_layer_fwd(Yn, d["src"], d["T"], d["k1"], d["k2"], Ug, Uf, rp, col, depth, H, Hp)
+    dX, dUg, dUf = P.lstm_layer_bwd(hist, d["cot"], Ug, Uf, rp, col, depth, H, Hp)
+    dYn = torch.zeros_like(Yn).index_add_(0, d["src"], dX)
+    dT = torch.zeros_like(d["T"]).index_add_(0, d["k1"], dX)
+    if d["k2"] is not None:
+        dT.index_add_(0, d["k2"], dX)
+    leaf = lambda t: t.float().to(DEV).requires_grad_(True)
+    phi, Wx, T, ug, uf = leaf(d["phi"]), leaf(d["Wx"]), leaf(d["T"]), leaf(Ug), leaf(Uf)
+    h, c = Fn.LSTMMessages.apply(phi, Wx, T, ug, uf, _message_graph(d), depth, H)
+    assert rel(h, h_ref) <= 1e-5
+    assert rel(c, hist["c"][-1]) <= 1e-5
+    assert float(h[0].abs().max()) == 0 and float(h[:, H:].abs().max()) == 0
+    (h * d["cot"].float().to(DEV)).sum().backward()
+    assert rel(ug.grad, dUg) <= 2e-5 and rel(uf.grad, dUf) <= 2e-5
+    assert rel(T.grad, dT) <= 2e-5
+    assert rel(Wx.grad, dYn.t() @ d["phi"]) <= 2e-5
+    assert rel(phi.grad, dYn @ d["Wx"]) <= 2e-5
+
+
+@pytest.mark.parametrize("H,Hp,depth,batch,with_k2", [(20, 32, 3, 3, False), (250, 256, 4, 6, True)])
+def test_gru_layer_forward_backward(engine, H, Hp, depth, batch, with_k2):
+    d = _layer_inputs(H, Hp, 3, batch, 200 + H, with_k2)
+    Uz, Ur, Uh = d["sq"](), d["sq"](), d["sq"]()
+    br = torch.zeros(Hp, dtype=torch.float64)
+    br[:H] = torch.randn(H, dtype=torch.float64, generator=torch.Generator().manual_seed(1)) * 0.1
+    rp, col = P.csr_from_padded(d["bg"])
+    Yn = d["phi"] @ d["Wx"].t()
+    h_ref, hist = P.gru_layer_fwd(Yn, d["src"], d["T"], d["k1"], d["k2"], Uz, Ur, br, Uh, rp, col, depth, H, Hp)
+    dX, dUz, dUr, dbr, dUh = P.gru_layer_bwd(hist, d["cot"], Uz, Ur, Uh, rp, col, depth, H, Hp)
+    dYn = torch.zeros_like(Yn).index_add_(0, d["src"], dX)
+    leaf = lambda t: t.float().to(DEV).requires_grad_(True)
+    phi, Wx, T, uz, ur, b, uh = (leaf(t) for t in (d["phi"], d["Wx"], d["T"], Uz, Ur, br, Uh))
+    h = Fn.GRUMessages.apply(phi, Wx, T, uz, ur, b, uh, _message_graph(d), depth, H)
+    assert rel(h, h_ref) <= 1e-5
+    (h * d["cot"].float().to(DEV)).sum().backward()
+    for got, want in ((uz, dUz), (ur, dUr), (uh, dUh), (b, dbr), (phi, dYn @ d["Wx"]), (Wx, dYn.t() @ d["phi"])):
+        assert rel(got.grad, want) <= 2e-5
