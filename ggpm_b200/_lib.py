@@ -31,6 +31,8 @@ SIGNATURES = {
     "ggpm_csr_transpose": (I, [P, P, I, I, P, P, P, P, P]),
     "ggpm_gather_sum": (I, [P, I, P, P, P, I, I, I, I, P]),
     "ggpm_gemm": (I, [P, c_longlong, c_longlong, P, c_longlong, c_longlong, P, I, I, I, I, c_float, P, I, I, I, P]),
+    "ggpm_gemm_fused": (I, [P, c_longlong, c_longlong, P, c_longlong, c_longlong, P, I, I, I, I, c_float, P, I, I, I,
+                            P, P, P, P, I, I, P, c_longlong, I, P]),
     "ggpm_act_bwd": (I, [P, I, P, I, P, I, I, I, I, I, P]),
     "ggpm_colsum": (I, [P, I, I, I, P, I, P]),
     "ggpm_table_wgrad": (I, [P, I, I, I, P, P, P, I, I, P]),

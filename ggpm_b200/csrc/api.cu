@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <initializer_list>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -78,7 +79,7 @@ static int gemm_nn(const float* A, int lda, const float* B, int ldb, float* C, i
     g.A = A; g.sam = lda; g.sak = 1;
     g.B = B; g.sbk = ldb; g.sbn = 1;
     g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K; g.beta = beta;
-    return launch_gemm_simt(g, st);
+    return launch_gemm_nt(g, st);
 }
 // C[M,N] += A^T * B with A stored [K, M], B stored [K, N]  (weight gradients, K = number of messages)
 static int gemm_tn_acc(const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K,
@@ -94,8 +95,24 @@ static int gemm_tn_acc(const float* A, int lda, const float* B, int ldb, float* 
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
     g.split_k = splits;
-    if (splits == 1) g.beta = 1.f;
-    return launch_gemm_simt(g, st);
+    return launch_gemm_nt(g, st);
+}
+
+// enough K-slices to fill the machine with 128 x 256 tiles, each slice at least 256 deep
+static int wgrad_splits(int M, int N, int K) {
+    int tiles = ceil_div(M, 128) * ceil_div(N, 256);
+    int splits = ceil_div(sm_count(), tiles);
+    int max_splits = ceil_div(K, 256);
+    if (splits > max_splits) splits = max_splits;
+    return splits < 1 ? 1 : splits;
+}
+
+// the fused tcgen05 layer path needs the tensor-core engine and 16-byte aligned tables
+static bool tc_layer_ok(int Hp, std::initializer_list<const void*> ptrs) {
+    if (gemm_engine() == GGPM_ENGINE_SIMT_FP32 || Hp % 32 != 0) return false;
+    for (const void* q : ptrs)
+        if (((uintptr_t)q & 15) != 0) return false;
+    return true;
 }
 
 }  // namespace ggpm
@@ -144,8 +161,25 @@ extern "C" int ggpm_gemm(const float* A, long long sam, long long sak, const flo
     GemmArgs g;
     g.A = A; g.sam = sam; g.sak = sak; g.B = B; g.sbk = sbk; g.sbn = sbn; g.C = C; g.ldc = ldc;
     g.M = M; g.N = N; g.K = K; g.beta = beta; g.bias = bias; g.act = act; g.zero_row0 = zero_row0; g.split_k = split_k;
-    if (sak == 1 && sbk == 1 && split_k <= 1) return launch_gemm_nt(g, (cudaStream_t)stream);
-    return launch_gemm_simt(g, (cudaStream_t)stream);
+    return launch_gemm_nt(g, (cudaStream_t)stream);
+}
+
+extern "C" int ggpm_gemm_fused(const float* A, long long sam, long long sak, const float* B, long long sbk, long long sbn,
+                               float* C, int ldc, int M, int N, int K, float beta, const float* bias, int act,
+                               int zero_row0, int split_k, const int32_t* a_row_ptr, const int32_t* a_col,
+                               const int32_t* b_row_ptr, const int32_t* b_col, int split_dim, int split_at,
+                               const float* A2, long long lda2, int tile_n, void* stream) {
+    GGPM_REQUIRE(A && B && C, "gemm_fused: null pointer");
+    GGPM_REQUIRE((a_row_ptr == nullptr) == (a_col == nullptr) && (b_row_ptr == nullptr) == (b_col == nullptr),
+                 "gemm_fused: CSR arrays come in pairs");
+    GGPM_REQUIRE(split_dim >= 0 && split_dim <= 3, "gemm_fused: split_dim must be 0..3");
+    GemmArgs g;
+    g.A = A; g.sam = sam; g.sak = sak; g.B = B; g.sbk = sbk; g.sbn = sbn; g.C = C; g.ldc = ldc;
+    g.M = M; g.N = N; g.K = K; g.beta = beta; g.bias = bias; g.act = act; g.zero_row0 = zero_row0; g.split_k = split_k;
+    g.a_row_ptr = a_row_ptr; g.a_col = a_col; g.b_row_ptr = b_row_ptr; g.b_col = b_col;
+    g.split_dim = split_dim; g.split_at = split_at; g.A2 = A2; g.lda2 = lda2; g.tile_n = tile_n;
+    GGPM_REQUIRE(gemm_tc_eligible(g), "gemm_fused: needs the tcgen05 engine and 16-byte aligned, 4-float strided operands");
+    return launch_gemm_tc(g, (cudaStream_t)stream);
 }
 
 // ----------------------------------------------------------------------------------------------------
@@ -167,6 +201,8 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
     cudaStream_t st = (cudaStream_t)stream;
     const size_t row = (size_t)E1 * Hp;
     const XTabArgs x{Yn, src, T, k1, k2};
+    const bool tc_ok = tc_layer_ok(Hp, {hist_h, hist_c, hist_gp, Ug, Uf});
+    const bool fused_w = tc_ok && Uf == Ug + (size_t)3 * Hp * Hp && Hp % 128 == 0;
     for (int t = 1; t <= depth; ++t) {
         const int cur = keep_history ? (t - 1) : ((t - 1) & 1);
         const int prev = keep_history ? (t - 2) : ((t - 2) & 1);
@@ -180,9 +216,24 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
         const float* h_prev = hist_h + prev * row;
         const float* c_prev = hist_c + prev * row;
         // S = sum of neighbour states; [G_i|G_o|G_u] = S Ug^T ; P = h_prev Uf^T
-        GGPM_TRY(launch_gather_sum(h_prev, Hp, b_ptr, b_col, s_scratch, Hp, E1, Hp, false, st));
-        GGPM_TRY(gemm_nt(s_scratch, Hp, Ug, Hp, gp, 4 * Hp, E1, 3 * Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
-        GGPM_TRY(gemm_nt(h_prev, Hp, Uf, Hp, gp + 3 * Hp, 4 * Hp, E1, Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
+        if (tc_ok) {
+            // tcgen05: the gather-sum is the A-operand prologue of the gate GEMM; S is never written
+            GemmArgs g;
+            g.A = h_prev; g.sam = Hp; g.sak = 1; g.B = Ug; g.sbk = 1; g.sbn = Hp; g.C = gp; g.ldc = 4 * Hp;
+            g.M = E1; g.K = Hp; g.a_row_ptr = b_ptr; g.a_col = b_col;
+            if (fused_w) {   // one launch: columns >= 3Hp (the forget projection) read h_prev un-gathered
+                g.N = 4 * Hp; g.split_dim = 1; g.split_at = 3 * Hp;
+                GGPM_TRY(launch_gemm_tc(g, st));
+            } else {
+                g.N = 3 * Hp;
+                GGPM_TRY(launch_gemm_tc(g, st));
+                GGPM_TRY(gemm_nt(h_prev, Hp, Uf, Hp, gp + 3 * Hp, 4 * Hp, E1, Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
+            }
+        } else {
+            GGPM_TRY(launch_gather_sum(h_prev, Hp, b_ptr, b_col, s_scratch, Hp, E1, Hp, false, st));
+            GGPM_TRY(gemm_nt(s_scratch, Hp, Ug, Hp, gp, 4 * Hp, E1, 3 * Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
+            GGPM_TRY(gemm_nt(h_prev, Hp, Uf, Hp, gp + 3 * Hp, 4 * Hp, E1, Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
+        }
         GGPM_TRY(launch_lstm_cell_fwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, h_cur, c_cur, st));
     }
     return 0;
@@ -204,6 +255,8 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     float* dH = dH_final;
     float* dH_next = dHn;
     const float* dC_cur = nullptr;   // dL/dc^depth = 0
+    const bool tc_ok = tc_layer_ok(Hp, {hist_h, hist_c, hist_gp, Ug, Uf, dUg, dUf, dA, dP, dH_final, dHn});
+    const bool fused_w = tc_ok && Uf == Ug + (size_t)3 * Hp * Hp && dUf == dUg + (size_t)3 * Hp * Hp && Hp % 128 == 0;
     for (int t = depth; t >= 1; --t) {
         const float* c_cur = hist_c + (size_t)(t - 1) * row;
         const float* gp = hist_gp + (size_t)(t - 1) * 4 * row;
@@ -220,14 +273,44 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
         GGPM_CUDA(cudaMemsetAsync(dC_prev, 0, sizeof(float) * row, st));
         GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_cur, dA, dX, overwrite,
                                       dP, dC_prev, st));
-        // weight gradients: dUg += dA[:, :3Hp]^T S^t ; dUf += dP^T h^{t-1}
-        GGPM_TRY(launch_gather_sum(h_prev, Hp, b_ptr, b_col, S, Hp, E1, Hp, false, st));
-        GGPM_TRY(gemm_tn_acc(dA, 4 * Hp, S, Hp, dUg, Hp, 3 * Hp, Hp, E1, st));
-        GGPM_TRY(gemm_tn_acc(dP, Hp, h_prev, Hp, dUf, Hp, Hp, Hp, E1, st));
-        // state gradients: dS = dA[:, :3Hp] Ug ; dH^{t-1}[n] = sum_{e: n in N(e)} dS[e] + (dP Uf)[n]
-        GGPM_TRY(gemm_nn(dA, 4 * Hp, Ug, Hp, dS, Hp, E1, Hp, 3 * Hp, 0.f, st));
-        GGPM_TRY(launch_gather_sum(dS, Hp, bt_ptr, bt_row, dH_next, Hp, E1, Hp, false, st));
-        GGPM_TRY(gemm_nn(dP, Hp, Uf, Hp, dH_next, Hp, E1, Hp, Hp, 1.f, st));
+        if (tc_ok) {
+            // weight gradients: dUg += dA[:, :3Hp]^T S^t (S re-gathered inside the B-operand prologue) ;
+            // dUf += dP^T h^{t-1}
+            GemmArgs w;
+            w.A = dA; w.sam = 1; w.sak = 4 * Hp; w.B = h_prev; w.sbk = Hp; w.sbn = 1; w.C = dUg; w.ldc = Hp;
+            w.N = Hp; w.K = E1; w.beta = 1.f; w.b_row_ptr = b_ptr; w.b_col = b_col;
+            if (fused_w) {   // rows >= 3Hp of [dUg; dUf]: A = dP, B = h_prev un-gathered
+                w.M = 4 * Hp; w.split_dim = 3; w.split_at = 3 * Hp; w.A2 = dP; w.lda2 = Hp;
+                w.split_k = wgrad_splits(4 * Hp, Hp, E1);
+                GGPM_TRY(launch_gemm_tc(w, st));
+            } else {
+                w.M = 3 * Hp; w.split_k = wgrad_splits(3 * Hp, Hp, E1);
+                GGPM_TRY(launch_gemm_tc(w, st));
+                GGPM_TRY(gemm_tn_acc(dP, Hp, h_prev, Hp, dUf, Hp, Hp, Hp, E1, st));
+            }
+            // state gradient: dH^{t-1}[n] = sum_{e: n in N(e)} dA[e, :3Hp] Ug + dP[n] Uf
+            //               = [gather^T(dA[:, :3Hp]) | dP] [Ug; Uf]   (gather moved in front of the GEMM by linearity)
+            GemmArgs d;
+            d.A = dA; d.sam = 4 * Hp; d.sak = 1; d.B = Ug; d.sbk = Hp; d.sbn = 1; d.C = dH_next; d.ldc = Hp;
+            d.M = E1; d.N = Hp; d.a_row_ptr = bt_ptr; d.a_col = bt_row;
+            if (fused_w) {
+                d.K = 4 * Hp; d.split_dim = 2; d.split_at = 3 * Hp; d.A2 = dP; d.lda2 = Hp;
+                GGPM_TRY(launch_gemm_tc(d, st));
+            } else {
+                d.K = 3 * Hp;
+                GGPM_TRY(launch_gemm_tc(d, st));
+                GGPM_TRY(gemm_nn(dP, Hp, Uf, Hp, dH_next, Hp, E1, Hp, Hp, 1.f, st));
+            }
+        } else {
+            // weight gradients: dUg += dA[:, :3Hp]^T S^t ; dUf += dP^T h^{t-1}
+            GGPM_TRY(launch_gather_sum(h_prev, Hp, b_ptr, b_col, S, Hp, E1, Hp, false, st));
+            GGPM_TRY(gemm_tn_acc(dA, 4 * Hp, S, Hp, dUg, Hp, 3 * Hp, Hp, E1, st));
+            GGPM_TRY(gemm_tn_acc(dP, Hp, h_prev, Hp, dUf, Hp, Hp, Hp, E1, st));
+            // state gradients: dS = dA[:, :3Hp] Ug ; dH^{t-1}[n] = sum_{e: n in N(e)} dS[e] + (dP Uf)[n]
+            GGPM_TRY(gemm_nn(dA, 4 * Hp, Ug, Hp, dS, Hp, E1, Hp, 3 * Hp, 0.f, st));
+            GGPM_TRY(launch_gather_sum(dS, Hp, bt_ptr, bt_row, dH_next, Hp, E1, Hp, false, st));
+            GGPM_TRY(gemm_nn(dP, Hp, Uf, Hp, dH_next, Hp, E1, Hp, Hp, 1.f, st));
+        }
         float* tmp = dH; dH = dH_next; dH_next = tmp;
         dC_cur = dC_prev;
     }

@@ -1,13 +1,478 @@
-// Dispatcher for C[M,N] = A[M,K] * W[N,K]^T: tcgen05 3xTF32 tensor-core kernel when the shape allows,
-// else the fp32 CUDA-core kernel.
+// tcgen05 (5th-gen tensor core) GEMM with fp32-level accuracy by the 3xTF32 operand split, optional CSR
+// gather-sum fused into the operand prologue, fused epilogue (beta / bias / activation / row-0 mask) or split-K
+// atomic accumulation.
+//
+//   C[M,N] (+)= A(M,K) * B(K,N)          A(m,k) = A[m*sam + k*sak],  B(k,n) = B[k*sbk + n*sbn]
+//
+// Every nn.Linear on the encoder path runs through this: the gate projections of the graph LSTM / GRU
+// (ggpm/rnn.py:13-16, 28-37, 69-72, 88-91) forward, their input gradients and their weight gradients.
+// With `a_row_ptr/a_col` the A rows are S_e = sum_{n in N(e)} table[n] — index_select_ND(h, 0, bgraph).sum(1)
+// of ggpm/rnn.py:26,86 — built in registers by the producer warps, never written to memory.
+//
+// Structure (one CTA = one 128 x BN output tile, 9 warps):
+//   warps 0-7  producers: global -> registers (gather-sum) -> hi/lo tf32 split -> 128B-swizzled smem stage
+//                         (K-major or MN-major canonical UMMA layouts, so no operand is ever transposed in memory);
+//                         afterwards the same warps run the epilogue: TMEM -> registers -> smem transpose -> global
+//   warp  8    allocates TMEM; one lane issues tcgen05.mma.kind::tf32 (3 MMAs per 8-deep K step:
+//              lo*hi, hi*lo, hi*hi) into a fp32 accumulator of BN TMEM columns; tcgen05.commit releases stages.
+// Operands pass through registers (not TMA) because the A operand is computed (gather-sum + split), and the
+// split of B rides the same path.
 #include "common.cuh"
 #include "kernels.h"
+#include "tc_ptx.cuh"
 
 namespace ggpm {
 
 int gemm_engine();
 
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 32;                 // fp32 elements per stage = one 128-byte swizzle row
+constexpr int PRODUCERS = 256;         // warps 0-7
+constexpr int MMA_WARP = 8;            // warp 8
+constexpr int EPI_WARP0 = 9;           // warps 9-12
+constexpr int EPI_THREADS = 128;
+constexpr int THREADS = PRODUCERS + 32 + EPI_THREADS;
+constexpr int A_BYTES = BM * 128;
+constexpr int SCR_LD = 36;              // epilogue transpose scratch: row stride in floats
+constexpr int SCRATCH_BYTES = 4 * 32 * SCR_LD * 4;
+enum { EPI_STORE = 0, EPI_ATOMIC = 1, EPI_GENERIC = 2, EPI_SCALAR = 3 };
+constexpr int TMEM_COLS = 512;
+
+// "second region" of a launch (index >= split_at along split_dim): no gather, A replaced by A2 (when given)
+enum { SPLIT_NONE = 0, SPLIT_N = 1, SPLIT_K = 2, SPLIT_M = 3 };
+
+struct TcParams {
+    const float* A; long long lda;      // leading stride (the non-unit one)
+    const float* A2; long long lda2;
+    const float* B; long long ldb;
+    float* C; int ldc;
+    int M, N, K, k_chunk;
+    int split_dim, split_at;
+    const int* a_row_ptr; const int* a_col;      // CSR gather-sum over A's row index (K-major A only)
+    const int* b_row_ptr; const int* b_col;      // CSR gather-sum over B's k index (MN-major B only)
+    float beta; const float* bias; int act; int zero_row0; int splits;
+    int m_tiles, n_tiles, total_tiles;
+    int epi_mode;
+};
+
+template <int BN> struct Cfg {
+    static constexpr int B_BYTES = BN * 128;
+    static constexpr int STAGE = 2 * A_BYTES + 2 * B_BYTES;
+    static constexpr int NSTAGE = (BN == 256) ? 2 : 3;
+    static constexpr int NACC = TMEM_COLS / (2 * BN);          // accumulator sets (main + correction) in TMEM
+    static constexpr int SMEM = NSTAGE * STAGE + SCRATCH_BYTES + 1024;
+};
+
+// K-contiguous operand: tile of ROWS rows x 32 k  -> K-major SWIZZLE_128B layout (8-row groups of 1024 B)
+template <int ROWS>
+__device__ __forceinline__ void load_kmajor(const float* __restrict__ base, long long ld, int i0, int n_i, int k0,
+                                            int k_end, const int* __restrict__ rp, const int* __restrict__ col,
+                                            uint32_t s_hi, uint32_t s_lo, int tid) {
+    const int c = tid & 7, rq = tid >> 3;
+    const int k = k0 + 4 * c;
+    constexpr int P = ROWS / 32;
+    float4 v[P];
+    if (rp == nullptr) {
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const int gi = i0 + p * 32 + rq;
+            v[p] = (gi < n_i && k < k_end) ? ld4(base + (long long)gi * ld + k) : f4zero();
+        }
+    } else {
+        int jb[P], je[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const int gi = i0 + p * 32 + rq;
+            const bool ok = gi < n_i && k < k_end;
+            jb[p] = ok ? __ldg(rp + gi) : 0;
+            je[p] = ok ? __ldg(rp + gi + 1) : 0;
+        }
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            float4 acc = f4zero();
+            int j = jb[p];
+            for (; j + 2 <= je[p]; j += 2) {
+                const int n0 = __ldg(col + j), n1 = __ldg(col + j + 1);
+                const float4 x0 = ld4(base + (long long)n0 * ld + k), x1 = ld4(base + (long long)n1 * ld + k);
+                acc += x0;
+                acc += x1;
+            }
+            if (j < je[p]) acc += ld4(base + (long long)__ldg(col + j) * ld + k);
+            v[p] = acc;
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+        const int r = p * 32 + rq;
+        const uint32_t off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+        float4 hi, lo;
+        tc::split4(v[p], hi, lo);
+        tc::sts4(s_hi + off, hi);
+        tc::sts4(s_lo + off, lo);
+    }
+}
+
+// MN-contiguous operand (element (i,k) at base[k*ld + i]): tile of ROWS i x 32 k -> MN-major tf32 layout
+// SWIZZLE_128B_BASE32B: atoms of 4 k-rows x 32 i (512 B) whose 32-byte chunks are XOR-ed with the k-row,
+// i-blocks contiguous (LBO = 512 B), k-blocks at ROWS/32 * 512 B (SBO).
+template <int ROWS>
+__device__ __forceinline__ void load_mnmajor(const float* __restrict__ base, long long ld, int i0, int n_i, int k0,
+                                             int k_end, const int* __restrict__ rp, const int* __restrict__ col,
+                                             uint32_t s_hi, uint32_t s_lo, int tid) {
+    constexpr int NB = ROWS / 32;
+    const int c = tid & 7, q = tid >> 3;
+    float4 v[NB];
+#pragma unroll
+    for (int p = 0; p < NB; ++p) {
+        const int pair = p * 32 + q;
+        const int ib = pair % NB, k = pair / NB;
+        const int gi = i0 + ib * 32 + 4 * c, gk = k0 + k;
+        float4 acc = f4zero();
+        if (gi < n_i && gk < k_end) {
+            if (rp == nullptr) {
+                acc = ld4(base + (long long)gk * ld + gi);
+            } else {
+                const int jb = __ldg(rp + gk), je = __ldg(rp + gk + 1);
+                for (int j = jb; j < je; ++j) acc += ld4(base + (long long)__ldg(col + j) * ld + gi);
+            }
+        }
+        v[p] = acc;
+    }
+#pragma unroll
+    for (int p = 0; p < NB; ++p) {
+        const int pair = p * 32 + q;
+        const int ib = pair % NB, k = pair / NB;
+        const uint32_t off = (uint32_t)((k >> 2) * (NB * 512) + ib * 512 + (k & 3) * 128 + (((c >> 1) ^ (k & 3)) << 5) +
+                                        ((c & 1) << 4));
+        float4 hi, lo;
+        tc::split4(v[p], hi, lo);
+        tc::sts4(s_hi + off, hi);
+        tc::sts4(s_lo + off, lo);
+    }
+}
+
+template <int ROWS, bool KC>
+__device__ __forceinline__ uint64_t operand_desc(uint32_t saddr, int kstep) {
+    if (KC) return tc::make_sdesc(saddr + kstep * 32, 16, 1024, 2);
+    return tc::make_sdesc(saddr + kstep * 2 * (ROWS / 32) * 512, 512, (ROWS / 32) * 512, 1);
+}
+
+struct TileCoord { int m0, n0, kb, ke, nk; };
+
+template <int BN>
+__device__ __forceinline__ TileCoord tile_coord(const TcParams& p, int t) {
+    TileCoord tc_;
+    const int n_t = t % p.n_tiles;
+    const int rest = t / p.n_tiles;
+    const int m_t = rest % p.m_tiles, z = rest / p.m_tiles;
+    tc_.m0 = m_t * BM;
+    tc_.n0 = n_t * BN;
+    tc_.kb = z * p.k_chunk;
+    tc_.ke = min(p.K, tc_.kb + p.k_chunk);
+    tc_.nk = (tc_.ke - tc_.kb + BK - 1) / BK;
+    return tc_;
+}
+
+template <int BN, bool A_KC, bool B_KC>
+__global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
+    using C = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * C::NSTAGE + 2 * C::NACC];
+    __shared__ uint32_t tmem_slot;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t smem0 = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar0 = tc::smem_u32(bars);
+    auto full_bar = [&](int s) { return bar0 + 8u * s; };
+    auto empty_bar = [&](int s) { return bar0 + 8u * (C::NSTAGE + s); };
+    auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * C::NSTAGE + b); };
+    auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * C::NSTAGE + C::NACC + b); };
+
+    if (tid == 0) {
+        for (int s = 0; s < C::NSTAGE; ++s) {
+            tc::mbar_init(full_bar(s), PRODUCERS);
+            tc::mbar_init(empty_bar(s), 1);
+        }
+        for (int b = 0; b < C::NACC; ++b) {
+            tc::mbar_init(acc_full_bar(b), 1);
+            tc::mbar_init(acc_empty_bar(b), EPI_THREADS);
+        }
+        tc::mbar_fence_init();
+    }
+    if (warp == MMA_WARP) tc::tmem_alloc<TMEM_COLS>(tc::smem_u32(&tmem_slot));
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(&tmem_slot);
+
+    if (warp < MMA_WARP) {
+        // ---------------- producers: global -> (gather-sum) -> tf32 hi/lo -> swizzled smem ----------------
+        int chunk = 0;
+        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+            const TileCoord tl = tile_coord<BN>(p, t);
+            const bool n_reg2 = p.split_dim == SPLIT_N && tl.n0 >= p.split_at;
+            const bool m_reg2 = p.split_dim == SPLIT_M && tl.m0 >= p.split_at;
+            for (int c = 0; c < tl.nk; ++c, ++chunk) {
+                const int s = chunk % C::NSTAGE;
+                const uint32_t ph = (uint32_t)(chunk / C::NSTAGE) & 1u;
+                tc::mbar_wait(empty_bar(s), ph ^ 1u);
+                const uint32_t sa = smem0 + s * C::STAGE;
+                const uint32_t sb = sa + 2 * A_BYTES;
+                int k0 = tl.kb + c * BK;
+                // A operand of this chunk: which table, which rows / k window, gathered or not
+                const bool k_reg2 = p.split_dim == SPLIT_K && k0 >= p.split_at;
+                const bool reg2 = n_reg2 || m_reg2 || k_reg2;
+                const float* Ab = (reg2 && p.A2 != nullptr) ? p.A2 : p.A;
+                const long long lda = (reg2 && p.A2 != nullptr) ? p.lda2 : p.lda;
+                int a_i0 = tl.m0, a_ni = p.M, a_k0 = k0, a_ke = tl.ke;
+                if (p.split_dim == SPLIT_M) {
+                    if (m_reg2) { a_i0 = tl.m0 - p.split_at; a_ni = p.M - p.split_at; }
+                    else a_ni = min(p.M, p.split_at);
+                }
+                if (p.split_dim == SPLIT_K) {
+                    if (k_reg2) { a_k0 = k0 - p.split_at; a_ke = tl.ke - p.split_at; }
+                    else a_ke = min(tl.ke, p.split_at);
+                }
+                if (A_KC)
+                    load_kmajor<BM>(Ab, lda, a_i0, a_ni, a_k0, a_ke, reg2 ? nullptr : p.a_row_ptr, p.a_col, sa, sa + A_BYTES, tid);
+                else
+                    load_mnmajor<BM>(Ab, lda, a_i0, a_ni, a_k0, a_ke, nullptr, nullptr, sa, sa + A_BYTES, tid);
+                if (B_KC)
+                    load_kmajor<BN>(p.B, p.ldb, tl.n0, p.N, k0, tl.ke, nullptr, nullptr, sb, sb + C::B_BYTES, tid);
+                else
+                    load_mnmajor<BN>(p.B, p.ldb, tl.n0, p.N, k0, tl.ke, reg2 ? nullptr : p.b_row_ptr, p.b_col, sb,
+                                     sb + C::B_BYTES, tid);
+                tc::fence_async_smem();
+                tc::mbar_arrive(full_bar(s));
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        // ---------------- MMA issuer: one lane, tcgen05.mma.kind::tf32 into TMEM ----------------
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc::make_idesc_tf32(BM, BN, A_KC ? 0 : 1, B_KC ? 0 : 1);
+            int chunk = 0, it = 0;
+            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+                const TileCoord tl = tile_coord<BN>(p, t);
+                const int b = it % C::NACC;
+                const uint32_t aph = (uint32_t)(it / C::NACC) & 1u;
+                tc::mbar_wait(acc_empty_bar(b), aph ^ 1u);          // epilogue has drained this accumulator set
+                tc::fence_after_sync();
+                const uint32_t d_main = tmem + (uint32_t)(b * 2 * BN), d_corr = d_main + BN;
+                for (int c = 0; c < tl.nk; ++c, ++chunk) {
+                    const int s = chunk % C::NSTAGE;
+                    const uint32_t ph = (uint32_t)(chunk / C::NSTAGE) & 1u;
+                    tc::mbar_wait(full_bar(s), ph);
+                    tc::fence_after_sync();
+                    const uint32_t sa = smem0 + s * C::STAGE;
+                    const uint32_t sb = sa + 2 * A_BYTES;
+#pragma unroll
+                    for (int j = 0; j < BK / 8; ++j) {
+                        const uint64_t a_hi = operand_desc<BM, A_KC>(sa, j), a_lo = operand_desc<BM, A_KC>(sa + A_BYTES, j);
+                        const uint64_t b_hi = operand_desc<BN, B_KC>(sb, j), b_lo = operand_desc<BN, B_KC>(sb + C::B_BYTES, j);
+                        // the small cross terms go to their own accumulator: the main one then sees K/8 roundings only
+                        tc::mma_tf32(d_corr, a_lo, b_hi, idesc, (c | j) != 0);
+                        tc::mma_tf32(d_corr, a_hi, b_lo, idesc, 1u);
+                        tc::mma_tf32(d_main, a_hi, b_hi, idesc, (c | j) != 0);
+                    }
+                    tc::mma_commit(empty_bar(s));
+                }
+                tc::mma_commit(acc_full_bar(b));
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---------------- epilogue warps: TMEM -> registers -> smem transpose -> coalesced global ----------------
+        const int q = warp & 3;                                  // TMEM lane quarter this warp may read
+        const int ew = warp - EPI_WARP0;
+        float* scratch = reinterpret_cast<float*>(smem_raw + (smem0 - tc::smem_u32(smem_raw)) + C::NSTAGE * C::STAGE) +
+                         ew * (32 * SCR_LD);
+        const int epi_mode = p.epi_mode;
+        int it = 0;
+        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+            const TileCoord tl = tile_coord<BN>(p, t);
+            const int b = it % C::NACC;
+            const uint32_t aph = (uint32_t)(it / C::NACC) & 1u;
+            tc::mbar_wait(acc_full_bar(b), aph);
+            tc::fence_after_sync();
+            const uint32_t d_main = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * 2 * BN);
+            const int row_base = tl.m0 + q * 32;
+            const int rows_valid = min(32, p.M - row_base);                 // rows of this warp inside the matrix
+            for (int g = 0; g < BN / 32; ++g) {
+                const int col0 = g * 32;
+                if (tl.n0 + col0 >= p.N) break;
+                uint32_t v[32], w[32];
+                tc::tmem_ld32(d_main + (uint32_t)col0, v);
+                tc::tmem_ld32(d_main + (uint32_t)(BN + col0), w);
+                tc::tmem_ld_wait();
+                // transpose through smem (row stride 36 floats: conflict-free for 128-bit accesses both ways)
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    st4(scratch + lane * SCR_LD + 4 * j,
+                        make_float4(__uint_as_float(v[4 * j]) + __uint_as_float(w[4 * j]),
+                                    __uint_as_float(v[4 * j + 1]) + __uint_as_float(w[4 * j + 1]),
+                                    __uint_as_float(v[4 * j + 2]) + __uint_as_float(w[4 * j + 2]),
+                                    __uint_as_float(v[4 * j + 3]) + __uint_as_float(w[4 * j + 3])));
+                __syncwarp();
+                const int n = tl.n0 + col0 + 4 * (lane & 7);
+                if (epi_mode != EPI_SCALAR) {
+                    // lanes 0-7 cover the 128 bytes of one row: 4 rows per instruction, fully coalesced
+                    if (n < p.N) {
+                        float4 bias4 = f4zero();
+                        if (epi_mode == EPI_GENERIC && p.bias != nullptr) bias4 = ldg4(p.bias + n);
+#pragma unroll 2
+                        for (int r4 = 0; r4 < 8; ++r4) {
+                            const int rr = r4 * 4 + (lane >> 3);
+                            if (rr >= rows_valid) break;
+                            float4 x = ld4(scratch + rr * SCR_LD + 4 * (lane & 7));
+                            float* cp = p.C + (long long)(row_base + rr) * p.ldc + n;
+                            if (epi_mode == EPI_STORE) {
+                                st4(cp, x);
+                            } else if (epi_mode == EPI_ATOMIC) {
+                                red_add4(cp, x);
+                            } else {
+                                if (p.beta != 0.f) {
+                                    const float4 o = ld4(cp);
+                                    x.x += p.beta * o.x; x.y += p.beta * o.y; x.z += p.beta * o.z; x.w += p.beta * o.w;
+                                }
+                                x += bias4;
+                                if (p.act == GGPM_ACT_RELU) x = make_float4(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f), fmaxf(x.z, 0.f), fmaxf(x.w, 0.f));
+                                else if (p.act == GGPM_ACT_TANH) x = tanh4(x);
+                                else if (p.act == GGPM_ACT_SIGMOID) x = sigmoid4(x);
+                                if (p.zero_row0 && row_base + rr == 0) x = f4zero();
+                                st4(cp, x);
+                            }
+                        }
+                    }
+                } else {
+                    // ragged N or unaligned C: one column per lane, one row per iteration
+                    const int ns = tl.n0 + col0 + lane;
+                    const float bias = (p.bias != nullptr && ns < p.N) ? __ldg(p.bias + ns) : 0.f;
+                    for (int rr = 0; rr < rows_valid; ++rr) {
+                        if (ns >= p.N) break;
+                        float x = scratch[rr * SCR_LD + lane];
+                        float* cp = p.C + (long long)(row_base + rr) * p.ldc + ns;
+                        if (p.splits > 1) {
+                            atomicAdd(cp, x);
+                        } else {
+                            if (p.beta != 0.f) x += p.beta * (*cp);
+                            x += bias;
+                            if (p.act == GGPM_ACT_RELU) x = fmaxf(x, 0.f);
+                            else if (p.act == GGPM_ACT_TANH) x = tanhf(x);
+                            else if (p.act == GGPM_ACT_SIGMOID) x = sigmoidf_(x);
+                            if (p.zero_row0 && row_base + rr == 0) x = 0.f;
+                            *cp = x;
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            tc::fence_before_sync();
+            tc::mbar_arrive(acc_empty_bar(b));
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == MMA_WARP) tc::tmem_dealloc<TMEM_COLS>(tmem);
+}
+
+bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+
+template <int BN, bool A_KC, bool B_KC>
+int launch_variant(const TcParams& p, dim3 grid, cudaStream_t st) {
+    static bool configured = false;
+    auto kern = gemm_tc_kernel<BN, A_KC, B_KC>;
+    if (!configured) {
+        GGPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM));
+        configured = true;
+    }
+    kern<<<grid, THREADS, Cfg<BN>::SMEM, st>>>(p);
+    return check_launch("gemm_tcgen05");
+}
+
+}  // namespace
+
+bool gemm_tc_eligible(const GemmArgs& g) {
+    if (gemm_engine() == GGPM_ENGINE_SIMT_FP32) return false;
+    if (g.M <= 0 || g.N <= 0 || g.K <= 0) return false;
+    if (!aligned16(g.A) || !aligned16(g.B)) return false;
+    const bool a_kc = (g.sak == 1), b_kc = (g.sbk == 1);
+    if (!a_kc && g.sam != 1) return false;
+    if (!b_kc && g.sbn != 1) return false;
+    if (a_kc ? (g.sam % 4 != 0 || g.K % 4 != 0) : (g.sak % 4 != 0 || g.M % 4 != 0)) return false;
+    if (b_kc ? (g.sbn % 4 != 0 || g.K % 4 != 0) : (g.sbk % 4 != 0 || g.N % 4 != 0)) return false;
+    if (g.a_row_ptr && !a_kc) return false;
+    if (g.b_row_ptr && b_kc) return false;
+    return true;
+}
+
+int launch_gemm_tc(const GemmArgs& g, cudaStream_t st) {
+    GGPM_REQUIRE(gemm_tc_eligible(g), "gemm_tcgen05: operand layout not supported (alignment / strides)");
+    const bool a_kc = (g.sak == 1), b_kc = (g.sbk == 1);
+    TcParams p;
+    p.A = g.A; p.lda = a_kc ? g.sam : g.sak;
+    p.A2 = g.A2; p.lda2 = g.lda2;
+    p.B = g.B; p.ldb = b_kc ? g.sbn : g.sbk;
+    p.C = g.C; p.ldc = g.ldc; p.M = g.M; p.N = g.N; p.K = g.K;
+    p.a_row_ptr = g.a_row_ptr; p.a_col = g.a_col;
+    p.b_row_ptr = g.b_row_ptr; p.b_col = g.b_col;
+    p.split_dim = g.split_dim; p.split_at = g.split_at;
+    p.beta = g.beta; p.bias = g.bias; p.act = g.act; p.zero_row0 = g.zero_row0;
+    int splits = g.split_k > 1 ? g.split_k : 1;
+    if (splits > 1) GGPM_REQUIRE(!g.bias && g.act == GGPM_ACT_NONE && !g.zero_row0, "gemm: split-K has no epilogue");
+    int k_chunk = g.K;
+    if (splits > 1) {
+        k_chunk = ceil_div(ceil_div(g.K, splits), BK) * BK;
+        splits = ceil_div(g.K, k_chunk);
+    }
+    if (splits > 1 && g.beta == 0.f)
+        GGPM_CUDA(cudaMemset2DAsync(g.C, sizeof(float) * (size_t)g.ldc, 0, sizeof(float) * (size_t)g.N, (size_t)g.M, st));
+    p.k_chunk = k_chunk; p.splits = splits;
+    bool wide = g.N > 128;
+    if (g.tile_n == 128) wide = false;
+    if (g.tile_n == 256) wide = true;
+    const int bn = wide ? 256 : 128;
+    if (g.split_dim != SPLIT_NONE) {
+        GGPM_REQUIRE(g.split_at > 0, "gemm_tcgen05: split_at must be positive");
+        if (g.split_dim == SPLIT_N && g.split_at % bn != 0) { wide = false; }
+        const int bn2 = wide ? 256 : 128;
+        GGPM_REQUIRE(g.split_dim != SPLIT_N || g.split_at % bn2 == 0, "gemm_tcgen05: N split must be a multiple of 128");
+        GGPM_REQUIRE(g.split_dim != SPLIT_M || g.split_at % BM == 0, "gemm_tcgen05: M split must be a multiple of 128");
+        GGPM_REQUIRE(g.split_dim != SPLIT_K || (g.split_at % BK == 0 && splits == 1), "gemm_tcgen05: K split must be a multiple of 32 (no split-K)");
+        GGPM_REQUIRE(g.A2 == nullptr || (aligned16(g.A2) && g.lda2 % 4 == 0), "gemm_tcgen05: A2 alignment");
+    }
+    const int bnf = wide ? 256 : 128;
+    p.m_tiles = ceil_div(g.M, BM);
+    p.n_tiles = ceil_div(g.N, bnf);
+    p.total_tiles = p.m_tiles * p.n_tiles * splits;
+    const bool c_vec = aligned16(g.C) && g.ldc % 4 == 0 && g.N % 4 == 0 && (g.bias == nullptr || aligned16(g.bias));
+    if (!c_vec) p.epi_mode = EPI_SCALAR;
+    else if (splits > 1) p.epi_mode = EPI_ATOMIC;
+    else if (g.beta != 0.f || g.bias != nullptr || g.act != GGPM_ACT_NONE || g.zero_row0) p.epi_mode = EPI_GENERIC;
+    else p.epi_mode = EPI_STORE;
+    int ctas = p.total_tiles < sm_count() ? p.total_tiles : sm_count();
+    dim3 grid(ctas, 1, 1);
+    ProfScope prof(a_kc ? PROF_GEMM_TC : PROF_GEMM_WGRAD, st, 2.0 * g.M * g.N * (double)g.K);
+#define GGPM_TC(BNV, AK, BKC) return launch_variant<BNV, AK, BKC>(p, grid, st)
+    if (wide) {
+        if (a_kc && b_kc) GGPM_TC(256, true, true);
+        if (a_kc && !b_kc) GGPM_TC(256, true, false);
+        if (!a_kc && b_kc) GGPM_TC(256, false, true);
+        GGPM_TC(256, false, false);
+    } else {
+        if (a_kc && b_kc) GGPM_TC(128, true, true);
+        if (a_kc && !b_kc) GGPM_TC(128, true, false);
+        if (!a_kc && b_kc) GGPM_TC(128, false, true);
+        GGPM_TC(128, false, false);
+    }
+#undef GGPM_TC
+}
+
+// generic entry: tensor cores when the layout allows, else the fp32 CUDA-core kernel
 int launch_gemm_nt(const GemmArgs& g, cudaStream_t st) {
+    if (gemm_tc_eligible(g)) return launch_gemm_tc(g, st);
+    GGPM_REQUIRE(!g.a_row_ptr && !g.b_row_ptr, "gemm: fused gather needs the tcgen05 engine");
     return launch_gemm_simt(g, st);
 }
 

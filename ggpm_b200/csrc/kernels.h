@@ -16,11 +16,23 @@ struct GemmArgs {
     int act = GGPM_ACT_NONE;
     int zero_row0 = 0;
     int split_k = 1;
+    // ---- tcgen05 engine only ----
+    // A rows are CSR gather-sums of the rows of the table A (K-major A); B rows along k are CSR gather-sums of
+    // the rows of the table B (MN-major B).
+    const int* a_row_ptr = nullptr; const int* a_col = nullptr;
+    const int* b_row_ptr = nullptr; const int* b_col = nullptr;
+    // second region: output columns (split_dim 1) / k (2) / output rows (3) at or beyond split_at use no gather
+    // and read A from A2 (leading stride lda2, indices relative to split_at along k or m) when A2 is given
+    int split_dim = 0, split_at = 0;
+    const float* A2 = nullptr; long long lda2 = 0;
+    int tile_n = 0;   // 0 = automatic, 128 or 256 forces the N tile
 };
 
 int launch_gemm_simt(const GemmArgs& g, cudaStream_t st);
-// C[M,N] = A[M,K] * W[N,K]^T (+ epilogue); picks the tcgen05 3xTF32 kernel when the shape allows it
+// generic entry: tcgen05 3xTF32 kernel when the operand layout allows it, else the fp32 CUDA-core kernel
 int launch_gemm_nt(const GemmArgs& g, cudaStream_t st);
+int launch_gemm_tc(const GemmArgs& g, cudaStream_t st);
+bool gemm_tc_eligible(const GemmArgs& g);
 
 struct XTabArgs {   // hoisted x-projection: X_g[e] = Yn[src[e], g] + T[k1[e], g] (+ T[k2[e], g])
     const float* Yn; const int* src; const float* T; const int* k1; const int* k2;

@@ -196,6 +196,19 @@ def gemm_tn(A, B, out=None, beta=0.0):
     return out
 
 
+def gemm_fused(A, sam, sak, B, sbk, sbn, C, M, N, K, beta=0.0, a_csr: Optional[CSR] = None, b_csr: Optional[CSR] = None,
+               split_dim=0, split_at=0, A2=None, lda2=0, split_k=1, tile_n=0):
+    """Raw tcgen05 entry (ggpm_gemm_fused): C[M,N] (+)= A(M,K) B(K,N) with CSR gather-sum operand prologues and
+    the second-region switch; see include/ggpm_b200.h.  Used by the library internally for the LSTM layer; exposed
+    for tests and profiling."""
+    call("ggpm_gemm_fused", fptr_any(A), sam, sak, fptr_any(B), sbk, sbn, fptr(C), _row_stride(C), M, N, K, float(beta),
+         None, ACT_NONE, 0, split_k,
+         None if a_csr is None else iptr(a_csr.row_ptr), None if a_csr is None else iptr(a_csr.col),
+         None if b_csr is None else iptr(b_csr.row_ptr), None if b_csr is None else iptr(b_csr.col),
+         split_dim, split_at, None if A2 is None else fptr_any(A2), lda2, tile_n, stream_ptr(C.device))
+    return C
+
+
 class LinearAct(torch.autograd.Function):
     """Y = act(sum_i A_i @ W_i^T + b), optional zero row 0.  Replaces cat + nn.Linear + ReLU/Tanh + mask
     (ggpm/encoder.py:33-38, 101, 112, 137-138) without building the concatenation."""
@@ -306,7 +319,8 @@ class LSTMMessages(torch.autograd.Function):
         E1, dev = mg.E1, Uf.device
         dH = dh.clone(memory_format=torch.contiguous_format)
         dX = _empty(E1, 4 * Hp, device=dev)
-        dUg, dUf = torch.zeros_like(Ug), torch.zeros_like(Uf)
+        dU4 = torch.zeros(4 * Hp, Hp, dtype=torch.float32, device=dev)     # [dUg; dUf] contiguous (single-launch wgrad)
+        dUg, dUf = dU4[:3 * Hp], dU4[3 * Hp:]
         dA = _empty(E1, 4 * Hp, device=dev)
         dC, dP, dS = _empty(2, E1, Hp, device=dev), _empty(E1, Hp, device=dev), _empty(E1, Hp, device=dev)
         S, dHn = _empty(E1, Hp, device=dev), _empty(E1, Hp, device=dev)

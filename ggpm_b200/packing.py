@@ -47,9 +47,10 @@ def pack_lstm(rnn, F: int, Hp: int, n_bias_rows: int):
     H, IN = rnn.hidden_size, rnn.input_size
     lin = [rnn.W_i[0], rnn.W_o[0], rnn.W[0], rnn.W_f[0]]
     Wx, T = _pack_common([l.weight for l in lin], [l.bias for l in lin], F, IN, H, Hp, n_bias_rows)
-    Ug = torch.cat([_pad_square(l.weight[:, IN:], H, Hp) for l in lin[:3]], dim=0)    # [3Hp, Hp]
-    Uf = _pad_square(lin[3].weight[:, IN:], H, Hp)
-    return Wx, T, Ug, Uf
+    # one [4Hp, Hp] buffer [U_i; U_o; U_u; U_f]: Ug / Uf are views of it, which lets the library run the gate and
+    # forget projections (and their gradients) as single tensor-core launches
+    U4 = torch.cat([_pad_square(l.weight[:, IN:], H, Hp) for l in lin], dim=0)
+    return Wx, T, U4[:3 * Hp], U4[3 * Hp:]
 
 
 def pack_gru(rnn, F: int, Hp: int, n_bias_rows: int):

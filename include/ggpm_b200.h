@@ -82,6 +82,22 @@ int ggpm_gemm(const float* A, long long sam, long long sak, const float* B, long
               float* C, int ldc, int M, int N, int K, float beta, const float* bias, int act,
               int zero_row0, int split_k, void* stream);
 
+/* The same product on the tcgen05 tensor cores (3xTF32 operand split: fp32-level accuracy) with the neighbour
+ * gather-sum fused into the operand prologue, so that index_select_ND(h, 0, bgraph).sum(1) feeding a gate
+ * Linear (ggpm/rnn.py:26-28, 86-91) is never materialised:
+ *   a_row_ptr/a_col (A k-contiguous): A(m, :) = sum_{j in CSR row m} A[a_col[j], :]
+ *   b_row_ptr/b_col (B n-contiguous): B(k, :) = sum_{j in CSR row k} B[b_col[j], :]
+ * "Second region": indices >= split_at along split_dim (1: output columns n, 2: k, 3: output rows m) take no
+ * gather and read A from A2 (leading stride lda2; k resp. m counted from split_at) when A2 is given.  Used to
+ * run [S U_g^T | h U_f^T], [gather^T(dA) | dP] [U_g; U_f] and [dA | dP]^T [S | h] as single launches.
+ * split_at must be a multiple of the tile (128 rows / 128 columns / 32 k).  tile_n: 0 auto, 128 or 256.
+ * Fails (no fallback) unless the engine is tcgen05-capable and operands are 16-byte aligned with strides % 4 == 0. */
+int ggpm_gemm_fused(const float* A, long long sam, long long sak, const float* B, long long sbk, long long sbn,
+                    float* C, int ldc, int M, int N, int K, float beta, const float* bias, int act, int zero_row0,
+                    int split_k, const int32_t* a_row_ptr, const int32_t* a_col, const int32_t* b_row_ptr,
+                    const int32_t* b_col, int split_dim, int split_at, const float* A2, long long lda2, int tile_n,
+                    void* stream);
+
 /* dZ = dY * act'(Y) with row 0 optionally zeroed (backward of the fused epilogue above). */
 int ggpm_act_bwd(const float* dY, int ld_dy, const float* Y, int ld_y, float* dZ, int ld_dz, int rows,
                  int width, int act, int zero_row0, void* stream);

@@ -156,6 +156,72 @@ def test_gemm_tn_weight_gradient_split_k(K, M, N):
     assert rel(over, ref) <= 1e-5
 
 
+# ---------------------------------------------------------------------------------------------------
+# tcgen05 GEMM with the gather-sum fused into the operand prologue, and the single-launch layer forms
+# ---------------------------------------------------------------------------------------------------
+def _rand_csr(rng, rows, n_src, width=4, density=0.5):
+    idx = torch.from_numpy(random_padded(rng, rows, width, n_src, density)).to(DEV)
+    return idx, Fn.csr_from_padded(idx, n_src)
+
+
+def _gsum(table, idx):
+    """index_select_ND(table, 0, idx).sum(1) in fp64 with zero entries skipped (row 0 of real tables is zero)"""
+    t = table.double()
+    g = t[idx.reshape(-1)].reshape(idx.shape + (t.shape[1],))
+    return (g * (idx != 0).unsqueeze(-1)).sum(1)
+
+
+@pytest.mark.parametrize("E,Hp,tile_n", [(300, 128, 0), (1000, 256, 0), (1000, 256, 128), (2500, 512, 0)])
+def test_fused_gate_projection_forward(E, Hp, tile_n):
+    """[G | P] = [gather_sum(h) Ug^T | h Uf^T] in one launch (ggpm/rnn.py:86-91)"""
+    rng = np.random.default_rng(E + Hp)
+    h = torch.randn(E, Hp, device=DEV)
+    U4 = torch.randn(4 * Hp, Hp, device=DEV) / Hp ** 0.5
+    idx, csr = _rand_csr(rng, E, E)
+    out = torch.empty(E, 4 * Hp, device=DEV)
+    Fn.gemm_fused(h, Hp, 1, U4, 1, Hp, out, E, 4 * Hp, Hp, a_csr=csr, split_dim=1, split_at=3 * Hp, tile_n=tile_n)
+    S = _gsum(h, idx)
+    ref = torch.cat([S @ U4[:3 * Hp].double().t(), h.double() @ U4[3 * Hp:].double().t()], 1)
+    assert rel(out, ref) <= 1e-5, rel(out, ref)
+
+
+@pytest.mark.parametrize("E,Hp", [(300, 128), (1000, 256), (5000, 256)])
+def test_fused_state_gradient(E, Hp):
+    """dH = [gather^T(dA[:, :3Hp]) | dP] [Ug; Uf] in one launch (backward of ggpm/rnn.py:86-91)"""
+    rng = np.random.default_rng(E)
+    dA = torch.randn(E, 4 * Hp, device=DEV)
+    dP = torch.randn(E, Hp, device=DEV)
+    U4 = torch.randn(4 * Hp, Hp, device=DEV) / Hp ** 0.5
+    idx, csr = _rand_csr(rng, E, E)
+    bt = csr.T
+    out = torch.empty(E, Hp, device=DEV)
+    Fn.gemm_fused(dA, 4 * Hp, 1, U4, Hp, 1, out, E, Hp, 4 * Hp, a_csr=bt, split_dim=2, split_at=3 * Hp, A2=dP, lda2=Hp)
+    dS = dA[:, :3 * Hp].double() @ U4[:3 * Hp].double()
+    scat = torch.zeros(E, Hp, dtype=torch.float64, device=DEV)
+    flat = idx.reshape(-1)
+    rows = torch.arange(E, device=DEV).repeat_interleave(idx.shape[1])
+    keep = flat != 0
+    scat.index_add_(0, flat[keep], dS[rows[keep]])
+    ref = scat + dP.double() @ U4[3 * Hp:].double()
+    assert rel(out, ref) <= 1e-5, rel(out, ref)
+
+
+@pytest.mark.parametrize("E,Hp", [(300, 128), (5000, 256), (40000, 256)])
+def test_fused_weight_gradient(E, Hp):
+    """[dUg; dUf] += [dA[:, :3Hp]^T gather_sum(h) ; dP^T h] in one split-K launch"""
+    rng = np.random.default_rng(E + 1)
+    dA = torch.randn(E, 4 * Hp, device=DEV)
+    dP = torch.randn(E, Hp, device=DEV)
+    h = torch.randn(E, Hp, device=DEV)
+    idx, csr = _rand_csr(rng, E, E)
+    out = torch.ones(4 * Hp, Hp, device=DEV)
+    Fn.gemm_fused(dA, 1, 4 * Hp, h, Hp, 1, out, 4 * Hp, Hp, E, beta=1.0, b_csr=csr, split_dim=3, split_at=3 * Hp, A2=dP,
+                  lda2=Hp, split_k=max(1, min(18, E // 256)))
+    S = _gsum(h, idx)
+    ref = torch.cat([dA[:, :3 * Hp].double().t() @ S, dP.double().t() @ h.double()], 0) + 1.0
+    assert rel(out, ref) <= 1e-5, rel(out, ref)
+
+
 def test_linear_act_autograd(engine):
     g = torch.Generator().manual_seed(9)
     A1 = torch.randn(400, 38, generator=g, dtype=torch.float64, requires_grad=True)
