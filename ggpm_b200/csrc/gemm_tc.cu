@@ -37,7 +37,7 @@ constexpr int THREADS = PRODUCERS + 32 + EPI_THREADS;
 constexpr int A_BYTES = BM * 128;
 constexpr int SCR_LD = 36;              // epilogue transpose scratch: row stride in floats
 constexpr int SCRATCH_BYTES = 4 * 32 * SCR_LD * 4;
-enum { EPI_STORE = 0, EPI_ATOMIC = 1, EPI_GENERIC = 2, EPI_SCALAR = 3 };
+enum { EPI_STORE = 0, EPI_ATOMIC = 1, EPI_GENERIC = 2, EPI_SCALAR = 3, EPI_SCALAR_ATOMIC = 4 };
 constexpr int TMEM_COLS = 512;
 
 // "second region" of a launch (index >= split_at along split_dim): no gather, A replaced by A2 (when given)
@@ -48,12 +48,12 @@ struct TcParams {
     const float* A2; long long lda2;
     const float* B; long long ldb;
     float* C; int ldc;
-    int M, N, K, k_chunk;
+    int M, N, K, nk;
     int split_dim, split_at;
     const int* a_row_ptr; const int* a_col;      // CSR gather-sum over A's row index (K-major A only)
     const int* b_row_ptr; const int* b_col;      // CSR gather-sum over B's k index (MN-major B only)
-    float beta; const float* bias; int act; int zero_row0; int splits;
-    int m_tiles, n_tiles, total_tiles;
+    float beta; const float* bias; int act; int zero_row0;
+    int m_tiles, n_tiles, total_tiles, tiles_full;
     int epi_mode;
 };
 
@@ -65,46 +65,78 @@ template <int BN> struct Cfg {
     static constexpr int SMEM = NSTAGE * STAGE + SCRATCH_BYTES + 1024;
 };
 
-// K-contiguous operand: tile of ROWS rows x 32 k  -> K-major SWIZZLE_128B layout (8-row groups of 1024 B)
+// Per-tile cache of the CSR neighbour lists of the (up to 4) rows a producer thread gathers for the A operand:
+// keeps the row_ptr -> col -> data dependency chain out of the per-chunk loop.
+constexpr int NBR_CACHE = 3;
+struct RowNbrs {
+    int jb[BM / 32], cnt[BM / 32];
+    int id[BM / 32][NBR_CACHE];
+};
+
+__device__ __forceinline__ void load_row_nbrs(RowNbrs& rn, const int* __restrict__ rp, const int* __restrict__ col,
+                                              int i0, int n_i, int tid) {
+    const int rq = tid >> 3;
+#pragma unroll
+    for (int p = 0; p < BM / 32; ++p) {
+        const int gi = i0 + p * 32 + rq;
+        int b = 0, e = 0;
+        if (gi < n_i) { b = __ldg(rp + gi); e = __ldg(rp + gi + 1); }
+        rn.jb[p] = b;
+        rn.cnt[p] = e - b;
+    }
+#pragma unroll
+    for (int p = 0; p < BM / 32; ++p)
+#pragma unroll
+        for (int q = 0; q < NBR_CACHE; ++q) rn.id[p][q] = q < rn.cnt[p] ? __ldg(col + rn.jb[p] + q) : 0;
+}
+
+// K-contiguous operand: tile of ROWS rows x 32 k.  Phase 1 (prefetch): global -> registers, with the CSR
+// gather-sum when `rn` is given.  Phase 2 (store): tf32 hi/lo split -> K-major SWIZZLE_128B smem (8-row groups
+// of 1024 B, 16-byte chunks XOR-ed with the row).
 template <int ROWS>
-__device__ __forceinline__ void load_kmajor(const float* __restrict__ base, long long ld, int i0, int n_i, int k0,
-                                            int k_end, const int* __restrict__ rp, const int* __restrict__ col,
-                                            uint32_t s_hi, uint32_t s_lo, int tid) {
+__device__ __forceinline__ void km_prefetch(float4 (&v)[ROWS / 32], const float* __restrict__ base, long long ld, int i0,
+                                            int n_i, int k0, int k_end, bool gather, const RowNbrs& rn,
+                                            const int* __restrict__ col, int tid) {
     const int c = tid & 7, rq = tid >> 3;
     const int k = k0 + 4 * c;
     constexpr int P = ROWS / 32;
-    float4 v[P];
-    if (rp == nullptr) {
+    if (!gather) {
 #pragma unroll
         for (int p = 0; p < P; ++p) {
             const int gi = i0 + p * 32 + rq;
             v[p] = (gi < n_i && k < k_end) ? ld4(base + (long long)gi * ld + k) : f4zero();
         }
     } else {
-        int jb[P], je[P];
+        const bool kin = k < k_end;
+        // two rows at a time: 6 independent 128-bit loads in flight per thread, bounded register use
 #pragma unroll
-        for (int p = 0; p < P; ++p) {
-            const int gi = i0 + p * 32 + rq;
-            const bool ok = gi < n_i && k < k_end;
-            jb[p] = ok ? __ldg(rp + gi) : 0;
-            je[p] = ok ? __ldg(rp + gi + 1) : 0;
-        }
+        for (int p0 = 0; p0 < P; p0 += 2) {
+            float4 x[2][NBR_CACHE];
 #pragma unroll
-        for (int p = 0; p < P; ++p) {
-            float4 acc = f4zero();
-            int j = jb[p];
-            for (; j + 2 <= je[p]; j += 2) {
-                const int n0 = __ldg(col + j), n1 = __ldg(col + j + 1);
-                const float4 x0 = ld4(base + (long long)n0 * ld + k), x1 = ld4(base + (long long)n1 * ld + k);
-                acc += x0;
-                acc += x1;
+            for (int pp = 0; pp < 2; ++pp)
+#pragma unroll
+                for (int q = 0; q < NBR_CACHE; ++q)
+                    x[pp][q] = (kin && q < rn.cnt[p0 + pp]) ? ld4(base + (long long)rn.id[p0 + pp][q] * ld + k) : f4zero();
+#pragma unroll
+            for (int pp = 0; pp < 2; ++pp) {
+                const int p = p0 + pp;
+                float4 acc = x[pp][0];
+#pragma unroll
+                for (int q = 1; q < NBR_CACHE; ++q) acc += x[pp][q];             // slot order, like sum(dim=1)
+                if (kin)
+                    for (int j = NBR_CACHE; j < rn.cnt[p]; ++j)
+                        acc += ld4(base + (long long)__ldg(col + rn.jb[p] + j) * ld + k);
+                v[p] = acc;
             }
-            if (j < je[p]) acc += ld4(base + (long long)__ldg(col + j) * ld + k);
-            v[p] = acc;
         }
     }
+}
+
+template <int ROWS>
+__device__ __forceinline__ void km_store(const float4 (&v)[ROWS / 32], uint32_t s_hi, uint32_t s_lo, int tid) {
+    const int c = tid & 7, rq = tid >> 3;
 #pragma unroll
-    for (int p = 0; p < P; ++p) {
+    for (int p = 0; p < ROWS / 32; ++p) {
         const int r = p * 32 + rq;
         const uint32_t off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
         float4 hi, lo;
@@ -116,30 +148,63 @@ __device__ __forceinline__ void load_kmajor(const float* __restrict__ base, long
 
 // MN-contiguous operand (element (i,k) at base[k*ld + i]): tile of ROWS i x 32 k -> MN-major tf32 layout
 // SWIZZLE_128B_BASE32B: atoms of 4 k-rows x 32 i (512 B) whose 32-byte chunks are XOR-ed with the k-row,
-// i-blocks contiguous (LBO = 512 B), k-blocks at ROWS/32 * 512 B (SBO).
+// i-blocks contiguous (LBO = 512 B), k-blocks at ROWS/32 * 512 B (SBO).  With (rp, col) every k-row is the CSR
+// gather-sum of table rows (S = sum of neighbour states, recomputed for the weight gradient).
 template <int ROWS>
-__device__ __forceinline__ void load_mnmajor(const float* __restrict__ base, long long ld, int i0, int n_i, int k0,
-                                             int k_end, const int* __restrict__ rp, const int* __restrict__ col,
-                                             uint32_t s_hi, uint32_t s_lo, int tid) {
+__device__ __forceinline__ void mn_prefetch(float4 (&v)[ROWS / 32], const float* __restrict__ base, long long ld, int i0,
+                                            int n_i, int k0, int k_end, const int* __restrict__ rp,
+                                            const int* __restrict__ col, int tid) {
     constexpr int NB = ROWS / 32;
     const int c = tid & 7, q = tid >> 3;
-    float4 v[NB];
+    if (rp == nullptr) {
 #pragma unroll
-    for (int p = 0; p < NB; ++p) {
-        const int pair = p * 32 + q;
-        const int ib = pair % NB, k = pair / NB;
-        const int gi = i0 + ib * 32 + 4 * c, gk = k0 + k;
-        float4 acc = f4zero();
-        if (gi < n_i && gk < k_end) {
-            if (rp == nullptr) {
-                acc = ld4(base + (long long)gk * ld + gi);
-            } else {
-                const int jb = __ldg(rp + gk), je = __ldg(rp + gk + 1);
-                for (int j = jb; j < je; ++j) acc += ld4(base + (long long)__ldg(col + j) * ld + gi);
+        for (int p = 0; p < NB; ++p) {
+            const int pair = p * 32 + q;
+            const int ib = pair % NB, k = pair / NB;
+            const int gi = i0 + ib * 32 + 4 * c, gk = k0 + k;
+            v[p] = (gi < n_i && gk < k_end) ? ld4(base + (long long)gk * ld + gi) : f4zero();
+        }
+    } else {
+        // four (k-row, i-block) pairs at a time: 8 independent 128-bit loads in flight per thread
+#pragma unroll
+        for (int p0 = 0; p0 < NB; p0 += 4) {
+            int jb[4], je[4], gi[4];
+#pragma unroll
+            for (int pp = 0; pp < 4; ++pp) {
+                const int pair = (p0 + pp) * 32 + q;
+                const int ib = pair % NB, k = pair / NB;
+                gi[pp] = i0 + ib * 32 + 4 * c;
+                const int gk = k0 + k;
+                const bool ok = gi[pp] < n_i && gk < k_end;
+                jb[pp] = ok ? __ldg(rp + gk) : 0;
+                je[pp] = ok ? __ldg(rp + gk + 1) : 0;
+            }
+            int n0[4], n1[4];
+#pragma unroll
+            for (int pp = 0; pp < 4; ++pp) {
+                n0[pp] = jb[pp] < je[pp] ? __ldg(col + jb[pp]) : 0;
+                n1[pp] = jb[pp] + 1 < je[pp] ? __ldg(col + jb[pp] + 1) : 0;
+            }
+            float4 x0[4], x1[4];
+#pragma unroll
+            for (int pp = 0; pp < 4; ++pp) {
+                x0[pp] = jb[pp] < je[pp] ? ld4(base + (long long)n0[pp] * ld + gi[pp]) : f4zero();
+                x1[pp] = jb[pp] + 1 < je[pp] ? ld4(base + (long long)n1[pp] * ld + gi[pp]) : f4zero();
+            }
+#pragma unroll
+            for (int pp = 0; pp < 4; ++pp) {
+                float4 acc = x0[pp] + x1[pp];
+                for (int j = jb[pp] + 2; j < je[pp]; ++j) acc += ld4(base + (long long)__ldg(col + j) * ld + gi[pp]);
+                v[p0 + pp] = acc;
             }
         }
-        v[p] = acc;
     }
+}
+
+template <int ROWS>
+__device__ __forceinline__ void mn_store(const float4 (&v)[ROWS / 32], uint32_t s_hi, uint32_t s_lo, int tid) {
+    constexpr int NB = ROWS / 32;
+    const int c = tid & 7, q = tid >> 3;
 #pragma unroll
     for (int p = 0; p < NB; ++p) {
         const int pair = p * 32 + q;
@@ -159,21 +224,43 @@ __device__ __forceinline__ uint64_t operand_desc(uint32_t saddr, int kstep) {
     return tc::make_sdesc(saddr + kstep * 2 * (ROWS / 32) * 512, 512, (ROWS / 32) * 512, 1);
 }
 
-struct TileCoord { int m0, n0, kb, ke, nk; };
+// Work distribution of the persistent kernel.  Tiles [0, tiles_full) (a multiple of the grid size) go round-robin,
+// whole, with a direct epilogue.  The remaining "tail" tiles — which would leave most SMs idle — are cut along K
+// into 32-deep chunks and dealt out evenly (stream-K): every CTA accumulates its chunk range of a tail tile and adds
+// it to C with vector reductions (C is pre-zeroed there, or holds the beta = 1 addend).
+struct Seg { int m0, n0, kb, ke, nk; bool partial; };
 
 template <int BN>
-__device__ __forceinline__ TileCoord tile_coord(const TcParams& p, int t) {
-    TileCoord tc_;
-    const int n_t = t % p.n_tiles;
-    const int rest = t / p.n_tiles;
-    const int m_t = rest % p.m_tiles, z = rest / p.m_tiles;
-    tc_.m0 = m_t * BM;
-    tc_.n0 = n_t * BN;
-    tc_.kb = z * p.k_chunk;
-    tc_.ke = min(p.K, tc_.kb + p.k_chunk);
-    tc_.nk = (tc_.ke - tc_.kb + BK - 1) / BK;
-    return tc_;
-}
+struct SegIter {
+    int t_next, u, u_end;
+    __device__ __forceinline__ explicit SegIter(const TcParams& p) {
+        t_next = blockIdx.x;
+        const long long ut = (long long)(p.total_tiles - p.tiles_full) * p.nk;
+        u = (int)(ut * blockIdx.x / gridDim.x);
+        u_end = (int)(ut * (blockIdx.x + 1) / gridDim.x);
+    }
+    __device__ __forceinline__ bool next(const TcParams& p, Seg& sg) {
+        int t, c0, c1;
+        if (t_next < p.tiles_full) {
+            t = t_next; c0 = 0; c1 = p.nk; sg.partial = false;
+            t_next += gridDim.x;
+        } else if (u < u_end) {
+            t = p.tiles_full + u / p.nk;
+            c0 = u % p.nk;
+            c1 = min(p.nk, c0 + (u_end - u));
+            u += c1 - c0;
+            sg.partial = true;
+        } else {
+            return false;
+        }
+        sg.m0 = (t / p.n_tiles) * BM;
+        sg.n0 = (t % p.n_tiles) * BN;
+        sg.kb = c0 * BK;
+        sg.ke = min(p.K, c1 * BK);
+        sg.nk = c1 - c0;
+        return true;
+    }
+};
 
 template <int BN, bool A_KC, bool B_KC>
 __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
@@ -209,52 +296,73 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
 
     if (warp < MMA_WARP) {
         // ---------------- producers: global -> (gather-sum) -> tf32 hi/lo -> swizzled smem ----------------
-        int chunk = 0;
-        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
-            const TileCoord tl = tile_coord<BN>(p, t);
-            const bool n_reg2 = p.split_dim == SPLIT_N && tl.n0 >= p.split_at;
-            const bool m_reg2 = p.split_dim == SPLIT_M && tl.m0 >= p.split_at;
-            for (int c = 0; c < tl.nk; ++c, ++chunk) {
-                const int s = chunk % C::NSTAGE;
-                const uint32_t ph = (uint32_t)(chunk / C::NSTAGE) & 1u;
-                tc::mbar_wait(empty_bar(s), ph ^ 1u);
-                const uint32_t sa = smem0 + s * C::STAGE;
-                const uint32_t sb = sa + 2 * A_BYTES;
-                int k0 = tl.kb + c * BK;
-                // A operand of this chunk: which table, which rows / k window, gathered or not
-                const bool k_reg2 = p.split_dim == SPLIT_K && k0 >= p.split_at;
-                const bool reg2 = n_reg2 || m_reg2 || k_reg2;
-                const float* Ab = (reg2 && p.A2 != nullptr) ? p.A2 : p.A;
-                const long long lda = (reg2 && p.A2 != nullptr) ? p.lda2 : p.lda;
-                int a_i0 = tl.m0, a_ni = p.M, a_k0 = k0, a_ke = tl.ke;
-                if (p.split_dim == SPLIT_M) {
-                    if (m_reg2) { a_i0 = tl.m0 - p.split_at; a_ni = p.M - p.split_at; }
-                    else a_ni = min(p.M, p.split_at);
-                }
-                if (p.split_dim == SPLIT_K) {
-                    if (k_reg2) { a_k0 = k0 - p.split_at; a_ke = tl.ke - p.split_at; }
-                    else a_ke = min(tl.ke, p.split_at);
-                }
-                if (A_KC)
-                    load_kmajor<BM>(Ab, lda, a_i0, a_ni, a_k0, a_ke, reg2 ? nullptr : p.a_row_ptr, p.a_col, sa, sa + A_BYTES, tid);
-                else
-                    load_mnmajor<BM>(Ab, lda, a_i0, a_ni, a_k0, a_ke, nullptr, nullptr, sa, sa + A_BYTES, tid);
-                if (B_KC)
-                    load_kmajor<BN>(p.B, p.ldb, tl.n0, p.N, k0, tl.ke, nullptr, nullptr, sb, sb + C::B_BYTES, tid);
-                else
-                    load_mnmajor<BN>(p.B, p.ldb, tl.n0, p.N, k0, tl.ke, reg2 ? nullptr : p.b_row_ptr, p.b_col, sb,
-                                     sb + C::B_BYTES, tid);
-                tc::fence_async_smem();
-                tc::mbar_arrive(full_bar(s));
+        // Software pipeline: the global loads of chunk i+1 are issued into registers right after chunk i is
+        // handed to the tensor core, so their latency hides behind the wait for a free stage.
+        float4 va[BM / 32], vb[BN / 32];
+        RowNbrs rn;
+        const bool a_gather = A_KC && p.a_row_ptr != nullptr;
+        SegIter<BN> pit(p);
+        Seg ptl;                                             // prefetch cursor: (segment, chunk)
+        int pc = 0;
+        bool more = pit.next(p, ptl);
+        bool rn_valid = false;
+        auto prefetch = [&]() {
+            const bool n_reg2 = p.split_dim == SPLIT_N && ptl.n0 >= p.split_at;
+            const bool m_reg2 = p.split_dim == SPLIT_M && ptl.m0 >= p.split_at;
+            const int k0 = ptl.kb + pc * BK;
+            const bool k_reg2 = p.split_dim == SPLIT_K && k0 >= p.split_at;
+            const bool reg2 = n_reg2 || m_reg2 || k_reg2;
+            const float* Ab = (reg2 && p.A2 != nullptr) ? p.A2 : p.A;
+            const long long lda = (reg2 && p.A2 != nullptr) ? p.lda2 : p.lda;
+            int a_i0 = ptl.m0, a_ni = p.M, a_k0 = k0, a_ke = ptl.ke;
+            if (p.split_dim == SPLIT_M) {
+                if (m_reg2) { a_i0 = ptl.m0 - p.split_at; a_ni = p.M - p.split_at; }
+                else a_ni = min(p.M, p.split_at);
             }
+            if (p.split_dim == SPLIT_K) {
+                if (k_reg2) { a_k0 = k0 - p.split_at; a_ke = ptl.ke - p.split_at; }
+                else a_ke = min(ptl.ke, p.split_at);
+            }
+            if (B_KC)
+                km_prefetch<BN>(vb, p.B, p.ldb, ptl.n0, p.N, k0, ptl.ke, false, rn, nullptr, tid);
+            else
+                mn_prefetch<BN>(vb, p.B, p.ldb, ptl.n0, p.N, k0, ptl.ke, reg2 ? nullptr : p.b_row_ptr, p.b_col, tid);
+            if (A_KC) {
+                const bool g = a_gather && !reg2;
+                if (g && !rn_valid) { load_row_nbrs(rn, p.a_row_ptr, p.a_col, a_i0, a_ni, tid); rn_valid = true; }
+                km_prefetch<BM>(va, Ab, lda, a_i0, a_ni, a_k0, a_ke, g, rn, p.a_col, tid);
+            } else {
+                mn_prefetch<BM>(va, Ab, lda, a_i0, a_ni, a_k0, a_ke, nullptr, nullptr, tid);
+            }
+        };
+        if (more) prefetch();
+        int chunk = 0;
+        while (more) {
+            const int s = chunk % C::NSTAGE;
+            const uint32_t ph = (uint32_t)(chunk / C::NSTAGE) & 1u;
+            tc::mbar_wait(empty_bar(s), ph ^ 1u);
+            const uint32_t sa = smem0 + s * C::STAGE;
+            const uint32_t sb = sa + 2 * A_BYTES;
+            if (A_KC) km_store<BM>(va, sa, sa + A_BYTES, tid); else mn_store<BM>(va, sa, sa + A_BYTES, tid);
+            if (B_KC) km_store<BN>(vb, sb, sb + C::B_BYTES, tid); else mn_store<BN>(vb, sb, sb + C::B_BYTES, tid);
+            tc::fence_async_smem();
+            tc::mbar_arrive(full_bar(s));
+            ++chunk;
+            if (++pc == ptl.nk) {                                // next segment of this CTA
+                pc = 0;
+                rn_valid = false;
+                more = pit.next(p, ptl);
+            }
+            if (more) prefetch();
         }
     } else if (warp == MMA_WARP) {
         // ---------------- MMA issuer: one lane, tcgen05.mma.kind::tf32 into TMEM ----------------
         if (lane == 0) {
             constexpr uint32_t idesc = tc::make_idesc_tf32(BM, BN, A_KC ? 0 : 1, B_KC ? 0 : 1);
             int chunk = 0, it = 0;
-            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
-                const TileCoord tl = tile_coord<BN>(p, t);
+            SegIter<BN> sit(p);
+            Seg tl;
+            for (; sit.next(p, tl); ++it) {
                 const int b = it % C::NACC;
                 const uint32_t aph = (uint32_t)(it / C::NACC) & 1u;
                 tc::mbar_wait(acc_empty_bar(b), aph ^ 1u);          // epilogue has drained this accumulator set
@@ -288,10 +396,11 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
         const int ew = warp - EPI_WARP0;
         float* scratch = reinterpret_cast<float*>(smem_raw + (smem0 - tc::smem_u32(smem_raw)) + C::NSTAGE * C::STAGE) +
                          ew * (32 * SCR_LD);
-        const int epi_mode = p.epi_mode;
         int it = 0;
-        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
-            const TileCoord tl = tile_coord<BN>(p, t);
+        SegIter<BN> sit(p);
+        Seg tl;
+        for (; sit.next(p, tl); ++it) {
+            const int epi_mode = tl.partial ? (p.epi_mode == EPI_SCALAR ? EPI_SCALAR_ATOMIC : EPI_ATOMIC) : p.epi_mode;
             const int b = it % C::NACC;
             const uint32_t aph = (uint32_t)(it / C::NACC) & 1u;
             tc::mbar_wait(acc_full_bar(b), aph);
@@ -316,7 +425,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
                                     __uint_as_float(v[4 * j + 3]) + __uint_as_float(w[4 * j + 3])));
                 __syncwarp();
                 const int n = tl.n0 + col0 + 4 * (lane & 7);
-                if (epi_mode != EPI_SCALAR) {
+                if (epi_mode != EPI_SCALAR && epi_mode != EPI_SCALAR_ATOMIC) {
                     // lanes 0-7 cover the 128 bytes of one row: 4 rows per instruction, fully coalesced
                     if (n < p.N) {
                         float4 bias4 = f4zero();
@@ -353,7 +462,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
                         if (ns >= p.N) break;
                         float x = scratch[rr * SCR_LD + lane];
                         float* cp = p.C + (long long)(row_base + rr) * p.ldc + ns;
-                        if (p.splits > 1) {
+                        if (epi_mode == EPI_SCALAR_ATOMIC) {
                             atomicAdd(cp, x);
                         } else {
                             if (p.beta != 0.f) x += p.beta * (*cp);
@@ -419,39 +528,47 @@ int launch_gemm_tc(const GemmArgs& g, cudaStream_t st) {
     p.b_row_ptr = g.b_row_ptr; p.b_col = g.b_col;
     p.split_dim = g.split_dim; p.split_at = g.split_at;
     p.beta = g.beta; p.bias = g.bias; p.act = g.act; p.zero_row0 = g.zero_row0;
-    int splits = g.split_k > 1 ? g.split_k : 1;
-    if (splits > 1) GGPM_REQUIRE(!g.bias && g.act == GGPM_ACT_NONE && !g.zero_row0, "gemm: split-K has no epilogue");
-    int k_chunk = g.K;
-    if (splits > 1) {
-        k_chunk = ceil_div(ceil_div(g.K, splits), BK) * BK;
-        splits = ceil_div(g.K, k_chunk);
-    }
-    if (splits > 1 && g.beta == 0.f)
-        GGPM_CUDA(cudaMemset2DAsync(g.C, sizeof(float) * (size_t)g.ldc, 0, sizeof(float) * (size_t)g.N, (size_t)g.M, st));
-    p.k_chunk = k_chunk; p.splits = splits;
+    // split_k > 1 is a hint from the fp32 path ("this is a long-K accumulation"): here K is cut automatically
+    const bool plain_epilogue = !g.bias && g.act == GGPM_ACT_NONE && !g.zero_row0 && (g.beta == 0.f || g.beta == 1.f);
+    if (g.split_k > 1) GGPM_REQUIRE(!g.bias && g.act == GGPM_ACT_NONE && !g.zero_row0, "gemm: split-K has no epilogue");
     bool wide = g.N > 128;
     if (g.tile_n == 128) wide = false;
     if (g.tile_n == 256) wide = true;
-    const int bn = wide ? 256 : 128;
     if (g.split_dim != SPLIT_NONE) {
         GGPM_REQUIRE(g.split_at > 0, "gemm_tcgen05: split_at must be positive");
-        if (g.split_dim == SPLIT_N && g.split_at % bn != 0) { wide = false; }
-        const int bn2 = wide ? 256 : 128;
-        GGPM_REQUIRE(g.split_dim != SPLIT_N || g.split_at % bn2 == 0, "gemm_tcgen05: N split must be a multiple of 128");
+        if (g.split_dim == SPLIT_N && g.split_at % 256 != 0) wide = false;
+        GGPM_REQUIRE(g.split_dim != SPLIT_N || g.split_at % (wide ? 256 : 128) == 0, "gemm_tcgen05: N split must be a multiple of 128");
         GGPM_REQUIRE(g.split_dim != SPLIT_M || g.split_at % BM == 0, "gemm_tcgen05: M split must be a multiple of 128");
-        GGPM_REQUIRE(g.split_dim != SPLIT_K || (g.split_at % BK == 0 && splits == 1), "gemm_tcgen05: K split must be a multiple of 32 (no split-K)");
+        GGPM_REQUIRE(g.split_dim != SPLIT_K || g.split_at % BK == 0, "gemm_tcgen05: K split must be a multiple of 32");
         GGPM_REQUIRE(g.A2 == nullptr || (aligned16(g.A2) && g.lda2 % 4 == 0), "gemm_tcgen05: A2 alignment");
     }
     const int bnf = wide ? 256 : 128;
+    p.nk = ceil_div(g.K, BK);
     p.m_tiles = ceil_div(g.M, BM);
     p.n_tiles = ceil_div(g.N, bnf);
-    p.total_tiles = p.m_tiles * p.n_tiles * splits;
+    p.total_tiles = p.m_tiles * p.n_tiles;
+    const int sms = sm_count();
+    int ctas = sms;
+    // tail tiles are cut along K (stream-K) when the epilogue is a plain store / accumulate and there is enough K
+    // to share; otherwise every tile is processed whole
+    p.tiles_full = p.total_tiles;
+    if (plain_epilogue && p.total_tiles % sms != 0 && p.nk >= 2) {
+        p.tiles_full = (p.total_tiles / sms) * sms;
+        const long long tail_units = (long long)(p.total_tiles - p.tiles_full) * p.nk;
+        if (p.tiles_full == 0 && tail_units < sms) ctas = (int)tail_units;
+    } else if (p.total_tiles < sms) {
+        ctas = p.total_tiles;
+    }
     const bool c_vec = aligned16(g.C) && g.ldc % 4 == 0 && g.N % 4 == 0 && (g.bias == nullptr || aligned16(g.bias));
     if (!c_vec) p.epi_mode = EPI_SCALAR;
-    else if (splits > 1) p.epi_mode = EPI_ATOMIC;
     else if (g.beta != 0.f || g.bias != nullptr || g.act != GGPM_ACT_NONE || g.zero_row0) p.epi_mode = EPI_GENERIC;
     else p.epi_mode = EPI_STORE;
-    int ctas = p.total_tiles < sm_count() ? p.total_tiles : sm_count();
+    if (p.tiles_full < p.total_tiles && g.beta == 0.f) {
+        // tail tiles are accumulated with reductions: zero their rows (whole-tile stores of the same rows come later)
+        const int m_first = (p.tiles_full / p.n_tiles) * BM;
+        GGPM_CUDA(cudaMemset2DAsync(g.C + (size_t)m_first * g.ldc, sizeof(float) * (size_t)g.ldc, 0,
+                                    sizeof(float) * (size_t)g.N, (size_t)(g.M - m_first), st));
+    }
     dim3 grid(ctas, 1, 1);
     ProfScope prof(a_kc ? PROF_GEMM_TC : PROF_GEMM_WGRAD, st, 2.0 * g.M * g.N * (double)g.K);
 #define GGPM_TC(BNV, AK, BKC) return launch_variant<BNV, AK, BKC>(p, grid, st)

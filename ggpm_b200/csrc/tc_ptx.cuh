@@ -95,9 +95,9 @@ __device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr, uint32_t lbo_byte
 // (round-to-nearest here, so the tensor core's own truncation of the operand is a no-op and the residual
 // |v - hi - lo| <= 2^-22 |v| is unbiased).  a*b ~ hi_a*hi_b + lo_a*hi_b + hi_a*lo_b.
 __device__ __forceinline__ float tf32_hi(float v) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
-    return __uint_as_float(r);
+    // round-to-nearest (ties away) to a 10-bit mantissa with two integer ops; cvt.rna.tf32.f32 compiles to a
+    // ~5-instruction sequence with inf/nan guards, and the producer warps are issue-bound.  Inf stays inf, NaN NaN.
+    return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u);
 }
 __device__ __forceinline__ void split4(float4 v, float4& hi, float4& lo) {
     hi.x = tf32_hi(v.x); hi.y = tf32_hi(v.y); hi.z = tf32_hi(v.z); hi.w = tf32_hi(v.w);
