@@ -168,7 +168,8 @@ extern "C" int ggpm_gemm_fused(const float* A, long long sam, long long sak, con
                                float* C, int ldc, int M, int N, int K, float beta, const float* bias, int act,
                                int zero_row0, int split_k, const int32_t* a_row_ptr, const int32_t* a_col,
                                const int32_t* b_row_ptr, const int32_t* b_col, int split_dim, int split_at,
-                               const float* A2, long long lda2, int tile_n, void* stream) {
+                               const float* A2, long long lda2, int tile_n, const float* B_hi, const float* B_lo,
+                               void* stream) {
     GGPM_REQUIRE(A && B && C, "gemm_fused: null pointer");
     GGPM_REQUIRE((a_row_ptr == nullptr) == (a_col == nullptr) && (b_row_ptr == nullptr) == (b_col == nullptr),
                  "gemm_fused: CSR arrays come in pairs");
@@ -178,8 +179,14 @@ extern "C" int ggpm_gemm_fused(const float* A, long long sam, long long sak, con
     g.M = M; g.N = N; g.K = K; g.beta = beta; g.bias = bias; g.act = act; g.zero_row0 = zero_row0; g.split_k = split_k;
     g.a_row_ptr = a_row_ptr; g.a_col = a_col; g.b_row_ptr = b_row_ptr; g.b_col = b_col;
     g.split_dim = split_dim; g.split_at = split_at; g.A2 = A2; g.lda2 = lda2; g.tile_n = tile_n;
+    g.B_hi = B_hi; g.B_lo = B_lo;
     GGPM_REQUIRE(gemm_tc_eligible(g), "gemm_fused: needs the tcgen05 engine and 16-byte aligned, 4-float strided operands");
     return launch_gemm_tc(g, (cudaStream_t)stream);
+}
+
+extern "C" int ggpm_tf32_split(const float* w, long long n, float* hi, float* lo, void* stream) {
+    GGPM_REQUIRE(w && hi && lo && n >= 0, "tf32_split: null pointer");
+    return launch_tf32_split(w, n, hi, lo, (cudaStream_t)stream);
 }
 
 // ----------------------------------------------------------------------------------------------------
@@ -194,7 +201,7 @@ static int check_dims(const char* who, int E1, int H, int Hp, int depth) {
 extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                              const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
                              const float* Ug, const float* Uf, float* hist_h, float* hist_c, float* hist_gp,
-                             float* s_scratch, int keep_history, void* stream) {
+                             float* s_scratch, float* w_split, int keep_history, void* stream) {
     GGPM_TRY(check_dims("lstm_fwd", E1, H, Hp, depth));
     GGPM_REQUIRE(b_ptr && b_col && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp && s_scratch,
                  "lstm_fwd: null pointer");
@@ -203,6 +210,10 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
     const XTabArgs x{Yn, src, T, k1, k2};
     const bool tc_ok = tc_layer_ok(Hp, {hist_h, hist_c, hist_gp, Ug, Uf});
     const bool fused_w = tc_ok && Uf == Ug + (size_t)3 * Hp * Hp && Hp % 128 == 0;
+    // weights are split into tf32 hi / lo planes once per call and then streamed by TMA in every round
+    const size_t wn = (size_t)4 * Hp * Hp;
+    const bool w_tma = fused_w && w_split != nullptr && ((uintptr_t)w_split & 15) == 0 && depth > 1;
+    if (w_tma) GGPM_TRY(launch_tf32_split(Ug, (long long)wn, w_split, w_split + wn, st));
     for (int t = 1; t <= depth; ++t) {
         const int cur = keep_history ? (t - 1) : ((t - 1) & 1);
         const int prev = keep_history ? (t - 2) : ((t - 2) & 1);
@@ -223,6 +234,7 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
             g.M = E1; g.K = Hp; g.a_row_ptr = b_ptr; g.a_col = b_col;
             if (fused_w) {   // one launch: columns >= 3Hp (the forget projection) read h_prev un-gathered
                 g.N = 4 * Hp; g.split_dim = 1; g.split_at = 3 * Hp;
+                if (w_tma) { g.B_hi = w_split; g.B_lo = w_split + wn; }
                 GGPM_TRY(launch_gemm_tc(g, st));
             } else {
                 g.N = 3 * Hp;
@@ -244,7 +256,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
                              const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
                              const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
                              float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
-                             void* stream) {
+                             float* w_split, void* stream) {
     GGPM_TRY(check_dims("lstm_bwd", E1, H, Hp, depth));
     GGPM_REQUIRE(b_ptr && b_col && bt_ptr && bt_row && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp &&
                      dH_final && dX && dUg && dUf && dA && dC && dP && dS && S && dHn,
@@ -257,6 +269,10 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     const float* dC_cur = nullptr;   // dL/dc^depth = 0
     const bool tc_ok = tc_layer_ok(Hp, {hist_h, hist_c, hist_gp, Ug, Uf, dUg, dUf, dA, dP, dH_final, dHn});
     const bool fused_w = tc_ok && Uf == Ug + (size_t)3 * Hp * Hp && dUf == dUg + (size_t)3 * Hp * Hp && Hp % 128 == 0;
+    // state gradient dH = [..] [Ug; Uf]: the transposed weights [Hp, 4Hp] are split into tf32 planes once, then TMA-fed
+    const size_t wn = (size_t)4 * Hp * Hp;
+    const bool w_tma = fused_w && w_split != nullptr && ((uintptr_t)w_split & 15) == 0 && depth > 1;
+    if (w_tma) GGPM_TRY(launch_tf32_split_transpose(Ug, 4 * Hp, Hp, w_split, w_split + wn, st));
     for (int t = depth; t >= 1; --t) {
         const float* c_cur = hist_c + (size_t)(t - 1) * row;
         const float* gp = hist_gp + (size_t)(t - 1) * 4 * row;
@@ -295,6 +311,9 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
             d.M = E1; d.N = Hp; d.a_row_ptr = bt_ptr; d.a_col = bt_row;
             if (fused_w) {
                 d.K = 4 * Hp; d.split_dim = 2; d.split_at = 3 * Hp; d.A2 = dP; d.lda2 = Hp;
+                if (w_tma) {   // B(k, n) = W^T[n][k]: k-contiguous planes
+                    d.B = w_split; d.sbk = 1; d.sbn = 4 * Hp; d.B_hi = w_split; d.B_lo = w_split + wn;
+                }
                 GGPM_TRY(launch_gemm_tc(d, st));
             } else {
                 d.K = 3 * Hp;

@@ -17,6 +17,9 @@
 //              lo*hi, hi*lo, hi*hi) into a fp32 accumulator of BN TMEM columns; tcgen05.commit releases stages.
 // Operands pass through registers (not TMA) because the A operand is computed (gather-sum + split), and the
 // split of B rides the same path.
+#include <cuda.h>
+#include <string.h>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "tc_ptx.cuh"
@@ -262,8 +265,13 @@ struct SegIter {
     }
 };
 
-template <int BN, bool A_KC, bool B_KC>
-__global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
+// B_MODE: 0 = n-contiguous B through registers (MN-major), 1 = k-contiguous B through registers (K-major),
+//         2 = k-contiguous B already split into tf32 hi/lo planes, loaded by TMA (weights)
+template <int BN, bool A_KC, int B_MODE>
+__global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tm_hi,
+                                                             const __grid_constant__ CUtensorMap tm_lo) {
+    constexpr bool B_KC = B_MODE != 0;
+    constexpr bool B_TMA = B_MODE == 2;
     using C = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * C::NSTAGE + 2 * C::NACC];
@@ -289,6 +297,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
         tc::mbar_fence_init();
     }
     if (warp == MMA_WARP) tc::tmem_alloc<TMEM_COLS>(tc::smem_u32(&tmem_slot));
+    if (B_TMA && tid == 32) { tc::tma_prefetch_desc(&tm_hi); tc::tma_prefetch_desc(&tm_lo); }
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
@@ -306,6 +315,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
         int pc = 0;
         bool more = pit.next(p, ptl);
         bool rn_valid = false;
+        int st_k0 = 0, st_n0 = 0;                            // coordinates of the chunk held in registers
         auto prefetch = [&]() {
             const bool n_reg2 = p.split_dim == SPLIT_N && ptl.n0 >= p.split_at;
             const bool m_reg2 = p.split_dim == SPLIT_M && ptl.m0 >= p.split_at;
@@ -323,7 +333,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
                 if (k_reg2) { a_k0 = k0 - p.split_at; a_ke = ptl.ke - p.split_at; }
                 else a_ke = min(ptl.ke, p.split_at);
             }
-            if (B_KC)
+            st_k0 = k0; st_n0 = ptl.n0;
+            if (B_TMA) {
+            } else if (B_KC)
                 km_prefetch<BN>(vb, p.B, p.ldb, ptl.n0, p.N, k0, ptl.ke, false, rn, nullptr, tid);
             else
                 mn_prefetch<BN>(vb, p.B, p.ldb, ptl.n0, p.N, k0, ptl.ke, reg2 ? nullptr : p.b_row_ptr, p.b_col, tid);
@@ -343,8 +355,17 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
             tc::mbar_wait(empty_bar(s), ph ^ 1u);
             const uint32_t sa = smem0 + s * C::STAGE;
             const uint32_t sb = sa + 2 * A_BYTES;
+            if (B_TMA) {
+                if (tid == 0) {                                  // weights: two bulk tensor copies straight into the stage
+                    tc::mbar_expect_tx(full_bar(s), 2 * C::B_BYTES);
+                    tc::tma_load_2d(sb, &tm_hi, full_bar(s), st_k0, st_n0);
+                    tc::tma_load_2d(sb + C::B_BYTES, &tm_lo, full_bar(s), st_k0, st_n0);
+                }
+            }
             if (A_KC) km_store<BM>(va, sa, sa + A_BYTES, tid); else mn_store<BM>(va, sa, sa + A_BYTES, tid);
-            if (B_KC) km_store<BN>(vb, sb, sb + C::B_BYTES, tid); else mn_store<BN>(vb, sb, sb + C::B_BYTES, tid);
+            if (!B_TMA) {
+                if (B_KC) km_store<BN>(vb, sb, sb + C::B_BYTES, tid); else mn_store<BN>(vb, sb, sb + C::B_BYTES, tid);
+            }
             tc::fence_async_smem();
             tc::mbar_arrive(full_bar(s));
             ++chunk;
@@ -488,15 +509,47 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p) {
 
 bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 
-template <int BN, bool A_KC, bool B_KC>
-int launch_variant(const TcParams& p, dim3 grid, cudaStream_t st) {
+typedef CUresult (*TmapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+TmapEncodeFn tmap_encoder() {
+    static TmapEncodeFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (TmapEncodeFn)ptr;
+    }
+    return fn;
+}
+
+// fp32 [rows, cols] row-major plane (leading stride ld floats), box = 32 columns (one 128-byte swizzle row) x box_rows
+int make_plane_tmap(CUtensorMap* tm, const float* base, int rows, int cols, long long ld, int box_rows) {
+    TmapEncodeFn enc = tmap_encoder();
+    GGPM_REQUIRE(enc != nullptr, "gemm_tcgen05: cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
+    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    GGPM_REQUIRE(r == CUDA_SUCCESS, "gemm_tcgen05: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return 0;
+}
+
+template <int BN, bool A_KC, int B_MODE>
+int launch_variant(const TcParams& p, dim3 grid, const CUtensorMap& tm_hi, const CUtensorMap& tm_lo, cudaStream_t st) {
     static bool configured = false;
-    auto kern = gemm_tc_kernel<BN, A_KC, B_KC>;
+    auto kern = gemm_tc_kernel<BN, A_KC, B_MODE>;
     if (!configured) {
         GGPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM));
         configured = true;
     }
-    kern<<<grid, THREADS, Cfg<BN>::SMEM, st>>>(p);
+    kern<<<grid, THREADS, Cfg<BN>::SMEM, st>>>(p, tm_hi, tm_lo);
     return check_launch("gemm_tcgen05");
 }
 
@@ -571,19 +624,76 @@ int launch_gemm_tc(const GemmArgs& g, cudaStream_t st) {
     }
     dim3 grid(ctas, 1, 1);
     ProfScope prof(a_kc ? PROF_GEMM_TC : PROF_GEMM_WGRAD, st, 2.0 * g.M * g.N * (double)g.K);
-#define GGPM_TC(BNV, AK, BKC) return launch_variant<BNV, AK, BKC>(p, grid, st)
+    CUtensorMap tm_hi, tm_lo;
+    memset(&tm_hi, 0, sizeof(tm_hi));
+    memset(&tm_lo, 0, sizeof(tm_lo));
+    const bool b_tma = g.B_hi != nullptr && g.B_lo != nullptr && b_kc && a_kc && g.b_row_ptr == nullptr;
+    if (b_tma) {
+        GGPM_REQUIRE(aligned16(g.B_hi) && aligned16(g.B_lo), "gemm_tcgen05: split weight planes must be 16-byte aligned");
+        GGPM_TRY(make_plane_tmap(&tm_hi, g.B_hi, g.N, g.K, g.sbn, bnf));
+        GGPM_TRY(make_plane_tmap(&tm_lo, g.B_lo, g.N, g.K, g.sbn, bnf));
+    }
+#define GGPM_TC(BNV, AK, BM_) return launch_variant<BNV, AK, BM_>(p, grid, tm_hi, tm_lo, st)
     if (wide) {
-        if (a_kc && b_kc) GGPM_TC(256, true, true);
-        if (a_kc && !b_kc) GGPM_TC(256, true, false);
-        if (!a_kc && b_kc) GGPM_TC(256, false, true);
-        GGPM_TC(256, false, false);
+        if (b_tma) GGPM_TC(256, true, 2);
+        if (a_kc && b_kc) GGPM_TC(256, true, 1);
+        if (a_kc && !b_kc) GGPM_TC(256, true, 0);
+        if (!a_kc && b_kc) GGPM_TC(256, false, 1);
+        GGPM_TC(256, false, 0);
     } else {
-        if (a_kc && b_kc) GGPM_TC(128, true, true);
-        if (a_kc && !b_kc) GGPM_TC(128, true, false);
-        if (!a_kc && b_kc) GGPM_TC(128, false, true);
-        GGPM_TC(128, false, false);
+        if (b_tma) GGPM_TC(128, true, 2);
+        if (a_kc && b_kc) GGPM_TC(128, true, 1);
+        if (a_kc && !b_kc) GGPM_TC(128, true, 0);
+        if (!a_kc && b_kc) GGPM_TC(128, false, 1);
+        GGPM_TC(128, false, 0);
     }
 #undef GGPM_TC
+}
+
+__global__ void tf32_split_kernel(const float* __restrict__ w, long long n4, float* __restrict__ hi, float* __restrict__ lo) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    float4 h, l;
+    tc::split4(ld4(w + 4 * i), h, l);
+    st4(hi + 4 * i, h);
+    st4(lo + 4 * i, l);
+}
+
+int launch_tf32_split(const float* w, long long n, float* hi, float* lo, cudaStream_t st) {
+    GGPM_REQUIRE(n % 4 == 0 && (((uintptr_t)w | (uintptr_t)hi | (uintptr_t)lo) & 15) == 0, "tf32_split: needs 16-byte alignment");
+    if (n == 0) return 0;
+    ProfScope prof(PROF_MISC, st, 0.0);
+    tf32_split_kernel<<<(unsigned)ceil_div_ll(n / 4, 256), 256, 0, st>>>(w, n / 4, hi, lo);
+    return check_launch("tf32_split");
+}
+
+// hi/lo planes of the TRANSPOSE of w [rows, cols] (row-major): planes are [cols, rows]
+__global__ void tf32_split_transpose_kernel(const float* __restrict__ w, int rows, int cols, float* __restrict__ hi,
+                                            float* __restrict__ lo) {
+    __shared__ float tile[32][33];
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < rows && c < cols) ? w[(size_t)r * cols + c] : 0.f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (c < cols && r < rows) {
+            const float v = tile[threadIdx.x][i];
+            const float h = tc::tf32_hi(v);
+            hi[(size_t)c * rows + r] = h;
+            lo[(size_t)c * rows + r] = tc::tf32_hi(v - h);
+        }
+    }
+}
+
+int launch_tf32_split_transpose(const float* w, int rows, int cols, float* hi, float* lo, cudaStream_t st) {
+    if (rows <= 0 || cols <= 0) return 0;
+    ProfScope prof(PROF_MISC, st, 0.0);
+    dim3 grid(ceil_div(cols, 32), ceil_div(rows, 32)), block(32, 8);
+    tf32_split_transpose_kernel<<<grid, block, 0, st>>>(w, rows, cols, hi, lo);
+    return check_launch("tf32_split_transpose");
 }
 
 // generic entry: tensor cores when the layout allows, else the fp32 CUDA-core kernel

@@ -26,6 +26,8 @@ struct GemmArgs {
     int split_dim = 0, split_at = 0;
     const float* A2 = nullptr; long long lda2 = 0;
     int tile_n = 0;   // 0 = automatic, 128 or 256 forces the N tile
+    // k-contiguous B (weights) already split into tf32 hi / lo planes (same shape and strides as B): loaded by TMA
+    const float* B_hi = nullptr; const float* B_lo = nullptr;
 };
 
 int launch_gemm_simt(const GemmArgs& g, cudaStream_t st);
@@ -33,6 +35,9 @@ int launch_gemm_simt(const GemmArgs& g, cudaStream_t st);
 int launch_gemm_nt(const GemmArgs& g, cudaStream_t st);
 int launch_gemm_tc(const GemmArgs& g, cudaStream_t st);
 bool gemm_tc_eligible(const GemmArgs& g);
+// hi = rn_tf32(w), lo = rn_tf32(w - hi), element-wise over n floats (weights are split once per layer call)
+int launch_tf32_split(const float* w, long long n, float* hi, float* lo, cudaStream_t st);
+int launch_tf32_split_transpose(const float* w, int rows, int cols, float* hi, float* lo, cudaStream_t st);
 
 struct XTabArgs {   // hoisted x-projection: X_g[e] = Yn[src[e], g] + T[k1[e], g] (+ T[k2[e], g])
     const float* Yn; const int* src; const float* T; const int* k1; const int* k2;

@@ -197,7 +197,7 @@ def gemm_tn(A, B, out=None, beta=0.0):
 
 
 def gemm_fused(A, sam, sak, B, sbk, sbn, C, M, N, K, beta=0.0, a_csr: Optional[CSR] = None, b_csr: Optional[CSR] = None,
-               split_dim=0, split_at=0, A2=None, lda2=0, split_k=1, tile_n=0):
+               split_dim=0, split_at=0, A2=None, lda2=0, split_k=1, tile_n=0, B_planes=None):
     """Raw tcgen05 entry (ggpm_gemm_fused): C[M,N] (+)= A(M,K) B(K,N) with CSR gather-sum operand prologues and
     the second-region switch; see include/ggpm_b200.h.  Used by the library internally for the LSTM layer; exposed
     for tests and profiling."""
@@ -205,8 +205,18 @@ def gemm_fused(A, sam, sak, B, sbk, sbn, C, M, N, K, beta=0.0, a_csr: Optional[C
          None, ACT_NONE, 0, split_k,
          None if a_csr is None else iptr(a_csr.row_ptr), None if a_csr is None else iptr(a_csr.col),
          None if b_csr is None else iptr(b_csr.row_ptr), None if b_csr is None else iptr(b_csr.col),
-         split_dim, split_at, None if A2 is None else fptr_any(A2), lda2, tile_n, stream_ptr(C.device))
+         split_dim, split_at, None if A2 is None else fptr_any(A2), lda2, tile_n,
+         None if B_planes is None else fptr(B_planes[0]), None if B_planes is None else fptr(B_planes[1]),
+         stream_ptr(C.device))
     return C
+
+
+def tf32_split(W: torch.Tensor):
+    """(hi, lo) tf32 planes of a contiguous fp32 weight matrix (ggpm_tf32_split)"""
+    W = W.contiguous()
+    planes = torch.empty((2,) + tuple(W.shape), dtype=torch.float32, device=W.device)
+    call("ggpm_tf32_split", fptr(W), W.numel(), fptr(planes[0]), fptr(planes[1]), stream_ptr(W.device))
+    return planes
 
 
 class LinearAct(torch.autograd.Function):
@@ -299,10 +309,11 @@ class LSTMMessages(torch.autograd.Function):
         hist_h, hist_c = _empty(slots, E1, Hp, device=dev), _empty(slots, E1, Hp, device=dev)
         hist_gp = _empty(slots, E1, 4 * Hp, device=dev)
         scratch = _empty(E1, Hp, device=dev)
+        w_split = _empty(2, 4 * Hp, Hp, device=dev)               # tf32 hi / lo planes of [Ug; Uf] for the TMA path
         T, Ug, Uf = T.contiguous(), Ug.contiguous(), Uf.contiguous()
         call("ggpm_lstm_fwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), fptr(Yn), iptr(mg.src), fptr(T),
              iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf), fptr(hist_h), fptr(hist_c),
-             fptr(hist_gp), fptr(scratch), int(keep), stream_ptr(dev))
+             fptr(hist_gp), fptr(scratch), fptr(w_split), int(keep), stream_ptr(dev))
         last = (depth - 1) if keep else ((depth - 1) & 1)
         ctx.mg, ctx.depth, ctx.H, ctx.Hp = mg, depth, H, Hp
         ctx.hist = (hist_h, hist_c, hist_gp, Yn) if keep else None
@@ -328,7 +339,7 @@ class LSTMMessages(torch.autograd.Function):
         call("ggpm_lstm_bwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), iptr(bt.row_ptr), iptr(bt.col),
              fptr(Yn), iptr(mg.src), fptr(T), iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf),
              fptr(hist_h), fptr(hist_c), fptr(hist_gp), fptr(dH), fptr(dX), fptr(dUg), fptr(dUf), fptr(dA), fptr(dC),
-             fptr(dP), fptr(dS), fptr(S), fptr(dHn), stream_ptr(dev))
+             fptr(dP), fptr(dS), fptr(S), fptr(dHn), fptr(_empty(2, Hp, 4 * Hp, device=dev)), stream_ptr(dev))
         dphi, dWx, dT = _xproj_backward(ctx, dX, phi_x, Wx, T, mg)
         return dphi, dWx, dT, dUg, dUf, None, None, None
 

@@ -91,12 +91,17 @@ int ggpm_gemm(const float* A, long long sam, long long sak, const float* B, long
  * gather and read A from A2 (leading stride lda2; k resp. m counted from split_at) when A2 is given.  Used to
  * run [S U_g^T | h U_f^T], [gather^T(dA) | dP] [U_g; U_f] and [dA | dP]^T [S | h] as single launches.
  * split_at must be a multiple of the tile (128 rows / 128 columns / 32 k).  tile_n: 0 auto, 128 or 256.
+ * B_hi/B_lo (optional, k-contiguous B only): pre-split planes of B, loaded by TMA instead of through registers.
  * Fails (no fallback) unless the engine is tcgen05-capable and operands are 16-byte aligned with strides % 4 == 0. */
 int ggpm_gemm_fused(const float* A, long long sam, long long sak, const float* B, long long sbk, long long sbn,
                     float* C, int ldc, int M, int N, int K, float beta, const float* bias, int act, int zero_row0,
                     int split_k, const int32_t* a_row_ptr, const int32_t* a_col, const int32_t* b_row_ptr,
                     const int32_t* b_col, int split_dim, int split_at, const float* A2, long long lda2, int tile_n,
-                    void* stream);
+                    const float* B_hi, const float* B_lo, void* stream);
+
+/* hi = tf32(w) (round to nearest), lo = tf32(w - hi), element-wise: the 3xTF32 operand split of a weight matrix, done
+ * once so that ggpm_gemm_fused can stream the planes by TMA (B_hi/B_lo: same shape and strides as a k-contiguous B). */
+int ggpm_tf32_split(const float* w, long long n, float* hi, float* lo, void* stream);
 
 /* dZ = dY * act'(Y) with row 0 optionally zeroed (backward of the fused epilogue above). */
 int ggpm_act_bwd(const float* dY, int ld_dy, const float* Y, int ld_y, float* dZ, int ld_dz, int rows,
@@ -120,23 +125,26 @@ int ggpm_table_wgrad(const float* dX, int ld_dx, int rows, int width, const int3
  * weights), Uf [Hp, Hp].  The forget gate is factored per SOURCE message: P = h U_f^T, f_en = s(Xf_e + P_n).
  * History buffers (saved for backward): hist_h, hist_c: [slots, E1, Hp]; hist_gp: [slots, E1, 4Hp]
  * ([G_i|G_o|G_u|P]); slots = depth when keep_history, else 2 (ping-pong).  s_scratch: [E1, Hp].
+ * w_split: optional workspace [2, 4Hp, Hp] (may be NULL): when Uf directly follows Ug in memory ([U_i;U_o;U_u;U_f] in
+ * one buffer) the weights are split once into tf32 hi/lo planes there and streamed by TMA in every round.
  * The final hidden state is slot (depth-1) (keep_history) or slot ((depth-1) & 1). */
 int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                   const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
                   const float* Ug, const float* Uf, float* hist_h, float* hist_c, float* hist_gp,
-                  float* s_scratch, int keep_history, void* stream);
+                  float* s_scratch, float* w_split, int keep_history, void* stream);
 
 /* Back-propagation through time of the above (what autograd does for ggpm/rnn.py:96-108).
  * dH_final: [E1, Hp] gradient w.r.t. the final hidden state (consumed, used as scratch).
  * Outputs: dX [E1, 4Hp] = accumulated gradient of the hoisted x-projection (zeroed here), dUg [3Hp, Hp] and
  * dUf [Hp, Hp] (accumulated into: caller zeroes).  bt_*: reverse CSR of (b_ptr, b_col).
- * Scratch: dA [E1, 4Hp], dC [2, E1, Hp], dP [E1, Hp], dS [E1, Hp], S [E1, Hp], dHn [E1, Hp]. */
+ * Scratch: dA [E1, 4Hp], dC [2, E1, Hp], dP [E1, Hp], dS [E1, Hp], S [E1, Hp], dHn [E1, Hp];
+ * w_split: optional [2, Hp, 4Hp] (may be NULL) for the tf32 planes of [Ug; Uf]^T streamed by TMA. */
 int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                   const int32_t* bt_ptr, const int32_t* bt_row, const float* Yn, const int32_t* src,
                   const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
                   const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
                   float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
-                  void* stream);
+                  float* w_split, void* stream);
 
 /* ---- graph GRU over a message graph ----------------------------------------------------------------
  * GRU.forward (ggpm/rnn.py:41-50) with the cell of ggpm/rnn.py:25-39.  x-gates packed [z | h | r] (3*Hp

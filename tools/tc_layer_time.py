@@ -22,7 +22,11 @@ for E, Hp, kbar in [(18965, 256, 1.58), (5617, 256, 1.36), (254000, 512, 1.58)]:
     csr = Fn.csr_from_padded(torch.from_numpy(idx).to("cuda"), E); bt = csr.T
     fl = 2.0 * E * 4 * Hp * Hp
     splits = max(1, min(-(-148 // (4 * Hp // 128 * -(-Hp // 256))), -(-E // 256)))
-    for tile in (0, 128):
+    planes = Fn.tf32_split(U4)
+    for tile in (0,):
+        tt = timeit(lambda: Fn.gemm_fused(h, Hp, 1, U4, 1, Hp, out, E, 4 * Hp, Hp, a_csr=csr, split_dim=1, split_at=3 * Hp, tile_n=tile, B_planes=planes))
+        tp = timeit(lambda: Fn.gemm_fused(h, Hp, 1, U4, 1, Hp, out, E, 4 * Hp, Hp, tile_n=tile, B_planes=planes))
+        print('   TMA weights: fwd plain %.3f (%.0f) fwd gather %.3f (%.0f)' % (tp, fl / tp / 1e9, tt, fl / tt / 1e9))
         t1 = timeit(lambda: Fn.gemm_fused(h, Hp, 1, U4, 1, Hp, out, E, 4 * Hp, Hp, a_csr=csr, split_dim=1, split_at=3 * Hp, tile_n=tile))
         t0 = timeit(lambda: Fn.gemm_fused(h, Hp, 1, U4, 1, Hp, out, E, 4 * Hp, Hp, tile_n=tile))
         t2 = timeit(lambda: Fn.gemm_fused(dA, 4 * Hp, 1, U4, Hp, 1, dH, E, Hp, 4 * Hp, a_csr=bt, split_dim=2, split_at=3 * Hp, A2=dP, lda2=Hp, tile_n=tile))
