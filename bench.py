@@ -250,6 +250,13 @@ def run_ours(args, workload):
     launches = (_lib.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
     clocks = sampler.stop() if rank == 0 else None
     mols_per_step = workload["batch"] * world
+    if args.profile_step:
+        # one extra step inside cudaProfilerStart/Stop: `ncu --profile-from-start off` captures exactly one step
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        step(*dev_batches[0])
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     value = mols_per_step * args.steps / (ms / 1e3)
 
     # ---- end to end from pinned host buffers ("e2e") ------------------------------------------------
@@ -352,6 +359,8 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--engine", type=int, default=None, help="0 auto, 1 fp32 CUDA cores, 2 tcgen05 3xTF32")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-step", action="store_true",
+                    help="run one extra step between cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     args = ap.parse_args()
     workload = WORKLOADS[args.workload]
     if args.impl == "reference":

@@ -57,12 +57,12 @@ class MPNEncoder(nn.Module):
         incoming [N1, Hp]) where incoming[v] = sum of final messages into v."""
         H = self.hidden_size
         F = self.W_o[0].in_features - H
-        out = self.rnn.messages(phi_x[:, :n_feat_x], mg, n_feat_x, n_bias_rows)
+        out = self.rnn.messages(phi_x, mg, n_feat_x, n_bias_rows)
         h = out[0] if isinstance(out, tuple) else out
         incoming = Fn.gather_sum(h, a_csr)                                    # ggpm/encoder.py:31-32
         w = self.W_o[0].weight
-        node = Fn.linear_act([phi_n[:, :F], incoming[:, :H]], [w[:, :F], w[:, F:]], self.W_o[0].bias,
-                             act=ACT_RELU, zero_row0=True, out_width=h.shape[1])   # :33-38 (mask commutes with dropout)
+        node = Fn.linear_act_padded([phi_n, incoming], [w[:, :F], w[:, F:]], self.W_o[0].bias,
+                                    act=ACT_RELU, zero_row0=True)             # :33-38 (mask commutes with dropout)
         node = self.W_o[2](node)
         return node, h, incoming
 
@@ -79,9 +79,9 @@ class MPNEncoder(nn.Module):
         h = out[0] if isinstance(out, tuple) else out
         incoming = Fn.gather_sum(h, a_csr)
         w = self.W_o[0].weight
-        node = Fn.linear_act([fnode[:, :F], incoming[:, :H]], [w[:, :F], w[:, F:]], self.W_o[0].bias,
-                             act=ACT_RELU, zero_row0=True)
-        return self.W_o[2](node), _public(h, H)
+        node = Fn.linear_act_padded([fnode, incoming], [w[:, :F], w[:, F:]], self.W_o[0].bias,
+                                    act=ACT_RELU, zero_row0=True)
+        return self.W_o[2](_public(node, H)), _public(h, H)
 
 
 class _TreeBatch:
@@ -103,7 +103,7 @@ def _root_vectors(W_root, feat, incoming, roots, H):
     w = W_root[0].weight
     f = feat.index_select(0, roots)
     m = incoming.index_select(0, roots)
-    return Fn.linear_act([f[:, :H], m[:, :H]], [w[:, :H], w[:, H:]], W_root[0].bias, act=ACT_TANH)
+    return _public(Fn.linear_act_padded([f, m], [w[:, :H], w[:, H:]], W_root[0].bias, act=ACT_TANH), H)
 
 
 class HierMPNEncoder(nn.Module):
@@ -143,7 +143,8 @@ class HierMPNEncoder(nn.Module):
 
         # atom layer: x_e = [E_a[atom(src_e)] | E_b[bond_e] | E_apos[pos_e]]  (embed_graph, :119-126)
         n_atoms, n_bonds = g_fnode.shape[0], g_fmess.shape[0]
-        atom_feat = self.E_a.index_select(0, g_fnode)
+        pad = (-self.atom_size) % 4                       # 16-byte rows: both uses below read it at this width
+        atom_feat = nn.functional.pad(self.E_a, (0, pad)).index_select(0, g_fnode)
         mg = Fn.MessageGraph(Fn.csr_from_padded(g_bgraph, n_bonds), _i32(g_fmess[:, 0]), _i32(g_fmess[:, 2]),
                              _i32(g_fmess[:, 3] + N_BOND_TYPES), n_atoms, N_BOND_TYPES + MAX_POS)
         hatom, _, _ = self.graph_encoder.encode(atom_feat, atom_feat, mg, Fn.csr_from_padded(g_agraph, n_bonds),
@@ -154,8 +155,8 @@ class HierMPNEncoder(nn.Module):
         atoms_of_motif = Fn.gather_sum(hatom, Fn.csr_from_padded(tb.cgraph, n_atoms))
         wi = self.W_i[0].weight
         E = attach_emb.shape[1]
-        inter_feat = Fn.linear_act([attach_emb, atoms_of_motif[:, :H]], [wi[:, :E], wi[:, E:]], self.W_i[0].bias,
-                                   act=ACT_RELU, out_width=hatom.shape[1])
+        inter_feat = Fn.linear_act_padded([attach_emb, atoms_of_motif], [wi[:, :E], wi[:, E:]], self.W_i[0].bias,
+                                          act=ACT_RELU)
         inter_feat = self.W_i[2](inter_feat)
         hinter, _, _ = self.inter_encoder.encode(inter_feat, inter_feat, tb.mg, tb.a, H, MAX_POS)
 
@@ -163,8 +164,8 @@ class HierMPNEncoder(nn.Module):
         motif_emb = self.E_c(tb.fnode[:, 0])
         wc = self.W_c[0].weight
         E = motif_emb.shape[1]
-        tree_feat = Fn.linear_act([motif_emb, hinter[:, :H]], [wc[:, :E], wc[:, E:]], self.W_c[0].bias,
-                                  act=ACT_RELU, out_width=hatom.shape[1])
+        tree_feat = Fn.linear_act_padded([motif_emb, hinter], [wc[:, :E], wc[:, E:]], self.W_c[0].bias,
+                                         act=ACT_RELU)
         tree_feat = self.W_c[2](tree_feat)
         hnode, _, incoming = self.tree_encoder.encode(tree_feat, tree_feat, tb.mg, tb.a, H, MAX_POS)
 

@@ -264,6 +264,31 @@ def linear_act(As: Sequence[torch.Tensor], Ws: Sequence[torch.Tensor], bias, act
     return LinearAct.apply(bias, act, zero_row0, out_width, *As, *Ws)
 
 
+def linear_act_padded(As: Sequence[torch.Tensor], Ws: Sequence[torch.Tensor], bias, act=ACT_NONE, zero_row0=False):
+    """linear_act with every operand brought to tensor-core friendly shapes: each weight piece W_i [N, K_i] is
+    zero-padded to [Np, Kp_i] (Np = N rounded up to 32, Kp_i = K_i rounded up to 4) and A_i is used at width Kp_i
+    (its extra columns meet zero weight columns, so only their finiteness matters).  Returns [M, Np]; columns
+    >= N are act(0) = 0 for the activations on this path (ReLU, tanh, none).  The padding is autograd-tracked
+    torch, so parameter gradients come back at the reference shapes."""
+    import torch.nn.functional as F_
+    N = Ws[0].shape[0]
+    Np = round_up(N, 32)
+    As_p, Ws_p = [], []
+    for A, W in zip(As, Ws):
+        K = W.shape[1]
+        Kp = round_up(K, 4)
+        if A.shape[1] >= Kp:
+            A = A[:, :Kp]
+        else:
+            A = F_.pad(A[:, :K], (0, Kp - K))
+        if A.stride(1) != 1 or _row_stride(A) % 4 != 0 or A.data_ptr() % 16 != 0:
+            A = A.contiguous()
+        As_p.append(A)
+        Ws_p.append(F_.pad(W, (0, Kp - K, 0, Np - N)))
+    bias_p = None if bias is None else F_.pad(bias, (0, Np - N))
+    return LinearAct.apply(bias_p, act, zero_row0, None, *As_p, *Ws_p)
+
+
 # ----------------------------------------------------------------------------------------------
 # message passing
 # ----------------------------------------------------------------------------------------------

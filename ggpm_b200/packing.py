@@ -4,7 +4,7 @@ The reference stores every gate as nn.Linear(IN + H -> H) applied to the concate
 (ggpm/rnn.py:13-16, 69-72), with x = [node feature of the source (F columns) | one-hot columns]
 (ggpm/encoder.py:103-106, 114-116, 121-125).  The kernels want, per layer:
 
-  Wx  [G*Hp, F]     x-columns that multiply the node feature, gates stacked along rows
+  Wx  [G*Hp, Fp]    x-columns that multiply the node feature, gates stacked along rows (Fp = F rounded up to 4)
   T   [ntab, G*Hp]  the one-hot columns transposed into lookup rows; rows [0, n_bias_rows) (the ones
                     indexed by k1, exactly one of which every message selects) also carry the biases
   U*  [.., Hp]      the h-columns, zero padded from H to Hp = multiple of 32
@@ -19,11 +19,30 @@ import torch
 import torch.nn.functional as F_
 
 
+def feature_width(F: int) -> int:
+    """K of the hoisted x-projection GEMM: F rounded up to 4 floats (16-byte rows for the tensor-core path)"""
+    return (F + 3) // 4 * 4
+
+
+def feature_columns(phi: torch.Tensor, F: int) -> torch.Tensor:
+    """node-feature table at the width Wx is packed for: [N1, feature_width(F)].  Columns >= F multiply zero
+    weight columns; a table that is already wider is used in place (a view), a narrower one is zero-padded."""
+    Fp = feature_width(F)
+    if phi.shape[1] >= Fp:
+        out = phi[:, :Fp]
+    else:
+        out = F_.pad(phi[:, :F], (0, Fp - F))
+    if out.stride(1) != 1 or (out.shape[0] > 1 and out.stride(0) % 4 != 0) or out.data_ptr() % 16 != 0:
+        out = out.contiguous()
+    return out
+
+
 def _pack_common(weights, biases, F, IN, H, Hp, n_bias_rows):
     """weights: list of [H, IN(+H)] gate matrices; biases: list of [H] or None (same length)."""
     G = len(weights)
+    Fp = feature_width(F)
     Wall = torch.stack([w[:, :IN] for w in weights])                        # [G, H, IN]
-    Wx = F_.pad(Wall[:, :, :F], (0, 0, 0, Hp - H)).reshape(G * Hp, F)       # [G*Hp, F]
+    Wx = F_.pad(Wall[:, :, :F], (0, Fp - F, 0, Hp - H)).reshape(G * Hp, Fp)  # [G*Hp, Fp], zero pad columns
     ntab = IN - F
     ball = torch.stack([b if b is not None else torch.zeros_like(weights[0][:, 0]) for b in biases])  # [G, H]
     if ntab == 0:

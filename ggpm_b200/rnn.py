@@ -59,7 +59,8 @@ class GRU(_GraphRNN):
         returns the padded final state [E1, Hp]"""
         Hp = self.padded_hidden
         Wx, T, Uz, Ur, br, Uh = packing.pack_gru(self, n_feat, Hp, n_bias_rows)
-        return Fn.GRUMessages.apply(phi_x, Wx, T, Uz, Ur, br, Uh, mg, self.depth, self.hidden_size)
+        return Fn.GRUMessages.apply(packing.feature_columns(phi_x, n_feat), Wx, T, Uz, Ur, br, Uh, mg, self.depth,
+                                    self.hidden_size)
 
     def forward(self, fmess, bgraph):
         self._check(fmess, bgraph)
@@ -90,7 +91,8 @@ class LSTM(_GraphRNN):
     def messages(self, phi_x, mg: Fn.MessageGraph, n_feat: int, n_bias_rows: int):
         Hp = self.padded_hidden
         Wx, T, Ug, Uf = packing.pack_lstm(self, n_feat, Hp, n_bias_rows)
-        return Fn.LSTMMessages.apply(phi_x, Wx, T, Ug, Uf, mg, self.depth, self.hidden_size)
+        return Fn.LSTMMessages.apply(packing.feature_columns(phi_x, n_feat), Wx, T, Ug, Uf, mg, self.depth,
+                                     self.hidden_size)
 
     def forward(self, fmess, bgraph):
         self._check(fmess, bgraph)
