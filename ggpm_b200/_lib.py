@@ -14,7 +14,7 @@ import torch
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libggpm_b200.so")
 
 ACT_NONE, ACT_RELU, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3
-ENGINE_AUTO, ENGINE_SIMT_FP32, ENGINE_TCGEN05_3XTF32 = 0, 1, 2
+ENGINE_AUTO, ENGINE_SIMT_FP32, ENGINE_TCGEN05_3XTF32, ENGINE_TCGEN05_F16X3 = 0, 1, 2, 3
 
 P = c_void_p
 I = c_int
@@ -34,6 +34,9 @@ SIGNATURES = {
     "ggpm_gemm_fused": (I, [P, c_longlong, c_longlong, P, c_longlong, c_longlong, P, I, I, I, I, c_float, P, I, I, I,
                             P, P, P, P, I, I, P, c_longlong, I, P, P, P]),
     "ggpm_tf32_split": (I, [P, c_longlong, P, P, P]),
+    "ggpm_f16_prepare_weights": (I, [P, I, I, I, P, P, P, P]),
+    "ggpm_gemm_f16x3": (I, [P, c_longlong, P, P, P, c_longlong, P, I, I, I, I, c_float, P, I, I, P, P, I, I, P, c_longlong,
+                            P, I, c_float, P, I, P]),
     "ggpm_act_bwd": (I, [P, I, P, I, P, I, I, I, I, I, P]),
     "ggpm_colsum": (I, [P, I, I, I, P, I, P]),
     "ggpm_table_wgrad": (I, [P, I, I, I, P, P, P, I, I, P]),

@@ -115,6 +115,24 @@ static bool tc_layer_ok(int Hp, std::initializer_list<const void*> ptrs) {
     return true;
 }
 
+// f16x3 engine workspace inside the caller's w_split buffer (8 Hp^2 floats): fp16 hi plane, fp16 lo plane
+// (4 Hp^2 halves each), then scalars: [0] max|W|, [1] weight scale, [2] max neighbour count (int),
+// [16 + 16 t + slot] max |gate-gradient term| of backward round t
+struct F16Work { void* hi; void* lo; float* scal; };
+static F16Work f16_work(float* w_split, int Hp) {
+    F16Work w;
+    const size_t plane_floats = (size_t)2 * Hp * Hp;      // 4 Hp^2 halves
+    w.hi = w_split;
+    w.lo = w_split ? w_split + plane_floats : nullptr;
+    w.scal = w_split ? w_split + 2 * plane_floats : nullptr;
+    return w;
+}
+static bool f16_scalars_fit(int Hp, int depth) { return (size_t)16 + 16 * (size_t)(depth + 1) <= (size_t)4 * Hp * Hp; }
+static bool f16_engine_on() {
+    const int e = gemm_engine();
+    return e == GGPM_ENGINE_AUTO || e == GGPM_ENGINE_TCGEN05_F16X3;
+}
+
 }  // namespace ggpm
 
 using namespace ggpm;
@@ -124,7 +142,7 @@ extern "C" int ggpm_abi_version(void) { return 1; }
 extern "C" long long ggpm_launch_count(void) { return g_launches.load(); }
 extern "C" int ggpm_get_gemm_engine(void) { return g_engine.load(); }
 extern "C" int ggpm_set_gemm_engine(int engine) {
-    GGPM_REQUIRE(engine >= GGPM_ENGINE_AUTO && engine <= GGPM_ENGINE_TCGEN05_3XTF32, "unknown GEMM engine %d", engine);
+    GGPM_REQUIRE(engine >= GGPM_ENGINE_AUTO && engine <= GGPM_ENGINE_TCGEN05_F16X3, "unknown GEMM engine %d", engine);
     g_engine.store(engine);
     return 0;
 }
@@ -184,6 +202,34 @@ extern "C" int ggpm_gemm_fused(const float* A, long long sam, long long sak, con
     return launch_gemm_tc(g, (cudaStream_t)stream);
 }
 
+extern "C" int ggpm_f16_prepare_weights(const float* W, int rows, int cols, int transpose, void* hi, void* lo, float* scal,
+                                        void* stream) {
+    GGPM_REQUIRE(W && hi && lo && scal && rows > 0 && cols > 0, "f16_prepare_weights: bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    GGPM_CUDA(cudaMemsetAsync(scal, 0, 2 * sizeof(float), st));
+    GGPM_TRY(launch_absmax(W, (long long)rows * cols, scal, st));
+    if (transpose) return launch_f16_split_transpose(W, rows, cols, scal, hi, lo, scal + 1, st);
+    return launch_f16_split(W, (long long)rows * cols, scal, hi, lo, scal + 1, st);
+}
+
+extern "C" int ggpm_gemm_f16x3(const float* A, long long lda, const void* B_hi, const void* B_lo, const float* b_scale,
+                               long long ldb, float* C, int ldc, int M, int N, int K, float beta, const float* bias,
+                               int act, int zero_row0, const int32_t* a_row_ptr, const int32_t* a_col, int split_dim,
+                               int split_at, const float* A2, long long lda2, const float* a_amax, int a_amax_n,
+                               float a_amax_const, const int32_t* a_deg, int tile_n, void* stream) {
+    GGPM_REQUIRE(A && B_hi && B_lo && b_scale && C, "gemm_f16x3: null pointer");
+    GGPM_REQUIRE((a_row_ptr == nullptr) == (a_col == nullptr), "gemm_f16x3: CSR arrays come in pairs");
+    GGPM_REQUIRE(split_dim >= 0 && split_dim <= 2, "gemm_f16x3: split_dim must be 0..2");
+    GemmArgs g;
+    g.A = A; g.sam = lda; g.sak = 1; g.B = nullptr; g.sbk = 1; g.sbn = ldb; g.C = C; g.ldc = ldc;
+    g.M = M; g.N = N; g.K = K; g.beta = beta; g.bias = bias; g.act = act; g.zero_row0 = zero_row0;
+    g.a_row_ptr = a_row_ptr; g.a_col = a_col; g.split_dim = split_dim; g.split_at = split_at; g.A2 = A2; g.lda2 = lda2;
+    g.tile_n = tile_n; g.Bh_hi = B_hi; g.Bh_lo = B_lo; g.b_scale = b_scale;
+    g.a_amax = a_amax; g.a_amax_n = a_amax_n; g.a_amax_const = a_amax_const; g.a_deg = a_deg;
+    GGPM_REQUIRE(gemm_f16_eligible(g), "gemm_f16x3: needs the f16x3 engine, 16-byte aligned operands, K %% 4 == 0, ldb %% 8 == 0");
+    return launch_gemm_f16(g, (cudaStream_t)stream);
+}
+
 extern "C" int ggpm_tf32_split(const float* w, long long n, float* hi, float* lo, void* stream) {
     GGPM_REQUIRE(w && hi && lo && n >= 0, "tf32_split: null pointer");
     return launch_tf32_split(w, n, hi, lo, (cudaStream_t)stream);
@@ -213,7 +259,17 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
     // weights are split into tf32 hi / lo planes once per call and then streamed by TMA in every round
     const size_t wn = (size_t)4 * Hp * Hp;
     const bool w_tma = fused_w && w_split != nullptr && ((uintptr_t)w_split & 15) == 0 && depth > 1;
-    if (w_tma) GGPM_TRY(launch_tf32_split(Ug, (long long)wn, w_split, w_split + wn, st));
+    // f16x3 engine: fp16 hi / lo planes of the scaled weights in the first half of w_split, scalars behind them
+    const bool f16 = w_tma && f16_engine_on() && f16_scalars_fit(Hp, depth);
+    F16Work fw = f16_work(w_split, Hp);
+    if (f16) {
+        GGPM_CUDA(cudaMemsetAsync(fw.scal, 0, sizeof(float) * 16, st));
+        GGPM_TRY(launch_absmax(Ug, (long long)wn, fw.scal + 0, st));
+        GGPM_TRY(launch_f16_split(Ug, (long long)wn, fw.scal + 0, fw.hi, fw.lo, fw.scal + 1, st));
+        GGPM_TRY(launch_max_degree(b_ptr, E1, reinterpret_cast<int*>(fw.scal + 2), st));
+    } else if (w_tma) {
+        GGPM_TRY(launch_tf32_split(Ug, (long long)wn, w_split, w_split + wn, st));
+    }
     for (int t = 1; t <= depth; ++t) {
         const int cur = keep_history ? (t - 1) : ((t - 1) & 1);
         const int prev = keep_history ? (t - 2) : ((t - 2) & 1);
@@ -234,8 +290,14 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
             g.M = E1; g.K = Hp; g.a_row_ptr = b_ptr; g.a_col = b_col;
             if (fused_w) {   // one launch: columns >= 3Hp (the forget projection) read h_prev un-gathered
                 g.N = 4 * Hp; g.split_dim = 1; g.split_at = 3 * Hp;
-                if (w_tma) { g.B_hi = w_split; g.B_lo = w_split + wn; }
-                GGPM_TRY(launch_gemm_tc(g, st));
+                if (f16) {   // |h| <= 1, so every gathered row is bounded by the largest neighbour count
+                    g.Bh_hi = fw.hi; g.Bh_lo = fw.lo; g.b_scale = fw.scal + 1;
+                    g.a_amax_const = 1.f; g.a_deg = reinterpret_cast<const int*>(fw.scal + 2);
+                    GGPM_TRY(launch_gemm_f16(g, st));
+                } else {
+                    if (w_tma) { g.B_hi = w_split; g.B_lo = w_split + wn; }
+                    GGPM_TRY(launch_gemm_tc(g, st));
+                }
             } else {
                 g.N = 3 * Hp;
                 GGPM_TRY(launch_gemm_tc(g, st));
@@ -272,14 +334,23 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     // state gradient dH = [..] [Ug; Uf]: the transposed weights [Hp, 4Hp] are split into tf32 planes once, then TMA-fed
     const size_t wn = (size_t)4 * Hp * Hp;
     const bool w_tma = fused_w && w_split != nullptr && ((uintptr_t)w_split & 15) == 0 && depth > 1;
-    if (w_tma) GGPM_TRY(launch_tf32_split_transpose(Ug, 4 * Hp, Hp, w_split, w_split + wn, st));
+    const bool f16 = w_tma && f16_engine_on() && f16_scalars_fit(Hp, depth);
+    F16Work fw = f16_work(w_split, Hp);
+    if (f16) {
+        GGPM_CUDA(cudaMemsetAsync(fw.scal, 0, sizeof(float) * (16 + 16 * (size_t)(depth + 1)), st));
+        GGPM_TRY(launch_absmax(Ug, (long long)wn, fw.scal + 0, st));
+        GGPM_TRY(launch_f16_split_transpose(Ug, 4 * Hp, Hp, fw.scal + 0, fw.hi, fw.lo, fw.scal + 1, st));
+        GGPM_TRY(launch_max_degree(bt_ptr, E1, reinterpret_cast<int*>(fw.scal + 2), st));
+    } else if (w_tma) {
+        GGPM_TRY(launch_tf32_split_transpose(Ug, 4 * Hp, Hp, w_split, w_split + wn, st));
+    }
     for (int t = depth; t >= 1; --t) {
         const float* c_cur = hist_c + (size_t)(t - 1) * row;
         const float* gp = hist_gp + (size_t)(t - 1) * 4 * row;
         const bool overwrite = (t == depth);
         if (t == 1) {
             GGPM_TRY(launch_lstm_cell_bwd(true, E1, H, Hp, b_ptr, b_col, x, nullptr, nullptr, c_cur, dH, dC_cur, dA, dX,
-                                          overwrite, nullptr, nullptr, st));
+                                          overwrite, nullptr, nullptr, nullptr, st));
             break;
         }
         const float* h_prev = hist_h + (size_t)(t - 2) * row;
@@ -287,8 +358,10 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
         float* dC_prev = dC + (size_t)(t & 1) * row;
         GGPM_CUDA(cudaMemsetAsync(dP, 0, sizeof(float) * row, st));
         GGPM_CUDA(cudaMemsetAsync(dC_prev, 0, sizeof(float) * row, st));
+        // the cell kernel also records max |gate-gradient term| of this round (16 slots): the scale of the f16x3 GEMM
+        float* amax_t = f16 ? fw.scal + 16 + 16 * (size_t)t : nullptr;
         GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_cur, dA, dX, overwrite,
-                                      dP, dC_prev, st));
+                                      dP, dC_prev, amax_t, st));
         if (tc_ok) {
             // weight gradients: dUg += dA[:, :3Hp]^T S^t (S re-gathered inside the B-operand prologue) ;
             // dUf += dP^T h^{t-1}
@@ -311,10 +384,16 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
             d.M = E1; d.N = Hp; d.a_row_ptr = bt_ptr; d.a_col = bt_row;
             if (fused_w) {
                 d.K = 4 * Hp; d.split_dim = 2; d.split_at = 3 * Hp; d.A2 = dP; d.lda2 = Hp;
-                if (w_tma) {   // B(k, n) = W^T[n][k]: k-contiguous planes
-                    d.B = w_split; d.sbk = 1; d.sbn = 4 * Hp; d.B_hi = w_split; d.B_lo = w_split + wn;
+                if (f16) {     // rows are sums of <= (largest reverse-neighbour count) terms, each <= amax_t in magnitude
+                    d.B = Ug; d.sbk = 1; d.sbn = 4 * Hp; d.Bh_hi = fw.hi; d.Bh_lo = fw.lo; d.b_scale = fw.scal + 1;
+                    d.a_amax = amax_t; d.a_amax_n = 16; d.a_deg = reinterpret_cast<const int*>(fw.scal + 2);
+                    GGPM_TRY(launch_gemm_f16(d, st));
+                } else {
+                    if (w_tma) {   // B(k, n) = W^T[n][k]: k-contiguous planes
+                        d.B = w_split; d.sbk = 1; d.sbn = 4 * Hp; d.B_hi = w_split; d.B_lo = w_split + wn;
+                    }
+                    GGPM_TRY(launch_gemm_tc(d, st));
                 }
-                GGPM_TRY(launch_gemm_tc(d, st));
             } else {
                 d.K = 3 * Hp;
                 GGPM_TRY(launch_gemm_tc(d, st));

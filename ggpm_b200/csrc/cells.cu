@@ -96,11 +96,13 @@ __global__ void __launch_bounds__(kCellWarps * 32)
 lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
                      const float* __restrict__ gp, const float* __restrict__ c_prev, const float* __restrict__ c_cur,
                      const float* __restrict__ dH, const float* __restrict__ dC, float* __restrict__ dA,
-                     float* __restrict__ dX, int dx_overwrite, float* __restrict__ dP, float* __restrict__ dC_prev) {
+                     float* __restrict__ dX, int dx_overwrite, float* __restrict__ dP, float* __restrict__ dC_prev,
+                     float* __restrict__ amax16) {
     const int lane = threadIdx.x & 31;
     const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (e >= E1) return;
     const int ld4h = 4 * Hp;
+    float tmax = 0.f;      // max |dai|, |dao|, |dau|, |daf_en| seen by this thread (scale of the f16x3 state-gradient GEMM)
     float* dAe = dA + (size_t)e * ld4h;
     float* dXe = dX + (size_t)e * ld4h;
     if (e == 0) {
@@ -137,11 +139,13 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
                 const float4 f = sigmoid4(xf + ld4(gp + (size_t)n * ld4h + 3 * Hp + c));
                 const float4 cn = ld4(c_prev + (size_t)n * Hp + c);
                 const float4 daf = dchat * cn * f * (one - f);
+                tmax = fmaxf(tmax, amax4(daf));
                 dafs += daf;
                 red_add4(dP + (size_t)n * Hp + c, daf);
                 red_add4(dC_prev + (size_t)n * Hp + c, dchat * f);
             }
         }
+        tmax = fmaxf(tmax, fmaxf(amax4(dai), fmaxf(amax4(dao), amax4(dau))));
         st4(dAe + c, dai);
         st4(dAe + Hp + c, dao);
         st4(dAe + 2 * Hp + c, dau);
@@ -157,6 +161,11 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
             st4(dXe + 2 * Hp + c, ld4(dXe + 2 * Hp + c) + dau);
             st4(dXe + 3 * Hp + c, ld4(dXe + 3 * Hp + c) + dafs);
         }
+    }
+    if (amax16 != nullptr) {
+        // non-negative floats order like their bit patterns
+        const unsigned u = __reduce_max_sync(0xffffffffu, __float_as_uint(tmax));
+        if (lane == 0 && u != 0) atomicMax(reinterpret_cast<unsigned*>(amax16) + (blockIdx.x & 15), u);
     }
 }
 
@@ -369,13 +378,14 @@ int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const
 
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          const float* gp, const float* c_prev, const float* c_cur, const float* dH, const float* dC,
-                         float* dA, float* dX, bool dx_overwrite, float* dP, float* dC_prev, cudaStream_t st) {
+                         float* dA, float* dX, bool dx_overwrite, float* dP, float* dC_prev, float* amax16,
+                         cudaStream_t st) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_BWD, st, 0.0);
     if (first)
-        lstm_cell_bwd_kernel<true><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, dx_overwrite, dP, dC_prev);
+        lstm_cell_bwd_kernel<true><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, dx_overwrite, dP, dC_prev, amax16);
     else
-        lstm_cell_bwd_kernel<false><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, dx_overwrite, dP, dC_prev);
+        lstm_cell_bwd_kernel<false><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, dx_overwrite, dP, dC_prev, amax16);
     return check_launch("lstm_cell_bwd");
 }
 

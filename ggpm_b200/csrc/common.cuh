@@ -71,6 +71,9 @@ __device__ __forceinline__ float4& operator+=(float4& a, float4 b) {
 __device__ __forceinline__ float4 fma4(float4 a, float4 b, float4 c) {
     return make_float4(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y), fmaf(a.z, b.z, c.z), fmaf(a.w, b.w, c.w));
 }
+__device__ __forceinline__ float amax4(float4 a) {
+    return fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(a.z), fabsf(a.w)));
+}
 // accurate fp32 transcendental forms (parity bar is 1e-5 against an fp64 oracle: no fast-math)
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 __device__ __forceinline__ float4 sigmoid4(float4 a) {

@@ -233,7 +233,7 @@ __device__ __forceinline__ uint64_t operand_desc(uint32_t saddr, int kstep) {
 // it to C with vector reductions (C is pre-zeroed there, or holds the beta = 1 addend).
 struct Seg { int m0, n0, kb, ke, nk; bool partial; };
 
-template <int BN>
+template <int BN, int BKE = BK>
 struct SegIter {
     int t_next, u, u_end;
     __device__ __forceinline__ explicit SegIter(const TcParams& p) {
@@ -258,8 +258,8 @@ struct SegIter {
         }
         sg.m0 = (t / p.n_tiles) * BM;
         sg.n0 = (t % p.n_tiles) * BN;
-        sg.kb = c0 * BK;
-        sg.ke = min(p.K, c1 * BK);
+        sg.kb = c0 * BKE;
+        sg.ke = min(p.K, c1 * BKE);
         sg.nk = c1 - c0;
         return true;
     }
@@ -507,6 +507,294 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tc_kernel(const TcParams p, c
     if (warp == MMA_WARP) tc::tmem_dealloc<TMEM_COLS>(tmem);
 }
 
+// ====================================================================================================
+// fp16 two-term split engine ("f16x3"): same structure as gemm_tc_kernel<BN, true, 2>, but operands are
+// fp16 hi / lo pairs of power-of-two scaled values and the MMAs are kind::f16 (K = 16 per instruction, twice
+// the tf32 rate, half the shared-memory bytes per FLOP).  A: fp32 K-major rows through registers (optional CSR
+// gather-sum, optional second region), B: pre-split fp16 weight planes by TMA.  One stage = 64 k.
+// ====================================================================================================
+constexpr int BK16 = 64;
+
+struct F16Params {
+    TcParams t;
+    const float* a_amax; int a_amax_n; float a_amax_const;
+    const int* a_deg;
+    const float* b_scale;
+};
+
+__device__ __forceinline__ float f16_a_scale(const F16Params& p) {
+    float amax = p.a_amax_const;
+    if (p.a_amax != nullptr) {
+        amax = 0.f;
+        for (int i = 0; i < p.a_amax_n; ++i) amax = fmaxf(amax, __ldg(p.a_amax + i));
+    }
+    const int deg = p.a_deg != nullptr ? max(1, __ldg(p.a_deg)) : 1;
+    return tc::pow2_scale(amax * (float)deg);
+}
+
+// K-contiguous fp32 operand, tile of ROWS rows x 64 k: thread (rq = tid >> 3, c = tid & 7) holds k = k0 + 8c .. +7
+// of rows p*32 + rq.
+template <int ROWS>
+__device__ __forceinline__ void km_prefetch16(float4 (&v)[ROWS / 32][2], const float* __restrict__ base, long long ld,
+                                              int i0, int n_i, int k0, int k_end, bool gather, const RowNbrs& rn,
+                                              const int* __restrict__ col, int tid) {
+    const int c = tid & 7, rq = tid >> 3;
+    const int k = k0 + 8 * c;
+    const bool kin0 = k < k_end, kin1 = k + 4 < k_end;
+    constexpr int P = ROWS / 32;
+    if (!gather) {
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const int gi = i0 + p * 32 + rq;
+            const float* r = base + (long long)gi * ld + k;
+            v[p][0] = (gi < n_i && kin0) ? ld4(r) : f4zero();
+            v[p][1] = (gi < n_i && kin1) ? ld4(r + 4) : f4zero();
+        }
+    } else {
+        // two rows at a time: 12 independent 128-bit loads in flight per thread
+#pragma unroll
+        for (int p0 = 0; p0 < P; p0 += 2) {
+            float4 x[2][NBR_CACHE][2];
+#pragma unroll
+            for (int pp = 0; pp < 2; ++pp)
+#pragma unroll
+                for (int q = 0; q < NBR_CACHE; ++q) {
+                    const bool ok = q < rn.cnt[p0 + pp];
+                    const float* r = base + (long long)rn.id[p0 + pp][q] * ld + k;
+                    x[pp][q][0] = (ok && kin0) ? ld4(r) : f4zero();
+                    x[pp][q][1] = (ok && kin1) ? ld4(r + 4) : f4zero();
+                }
+#pragma unroll
+            for (int pp = 0; pp < 2; ++pp) {
+                const int p = p0 + pp;
+                float4 a0 = x[pp][0][0], a1 = x[pp][0][1];
+#pragma unroll
+                for (int q = 1; q < NBR_CACHE; ++q) { a0 += x[pp][q][0]; a1 += x[pp][q][1]; }   // slot order
+                if (kin0)
+                    for (int j = NBR_CACHE; j < rn.cnt[p]; ++j) {
+                        const float* r = base + (long long)__ldg(col + rn.jb[p] + j) * ld + k;
+                        a0 += ld4(r);
+                        if (kin1) a1 += ld4(r + 4);
+                    }
+                v[p][0] = a0;
+                v[p][1] = a1;
+            }
+        }
+    }
+}
+
+// scale, split into fp16 hi / lo, store to the K-major SWIZZLE_128B stage (rows of 128 B = 64 fp16)
+template <int ROWS>
+__device__ __forceinline__ void km_store16(const float4 (&v)[ROWS / 32][2], uint32_t s_hi, uint32_t s_lo, float scale,
+                                           int tid) {
+    const int c = tid & 7, rq = tid >> 3;
+#pragma unroll
+    for (int p = 0; p < ROWS / 32; ++p) {
+        const int r = p * 32 + rq;
+        const uint32_t off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+        uint4 hi, lo;
+        tc::split8_f16(v[p][0], v[p][1], scale, hi, lo);
+        tc::sts4u(s_hi + off, hi);
+        tc::sts4u(s_lo + off, lo);
+    }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp, const __grid_constant__ CUtensorMap tm_hi,
+                                                              const __grid_constant__ CUtensorMap tm_lo) {
+    using C = Cfg<BN>;
+    using Iter = SegIter<BN, BK16>;
+    const TcParams& p = fp.t;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * C::NSTAGE + 2 * C::NACC];
+    __shared__ uint32_t tmem_slot;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t smem0 = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar0 = tc::smem_u32(bars);
+    auto full_bar = [&](int s) { return bar0 + 8u * s; };
+    auto empty_bar = [&](int s) { return bar0 + 8u * (C::NSTAGE + s); };
+    auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * C::NSTAGE + b); };
+    auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * C::NSTAGE + C::NACC + b); };
+
+    if (tid == 0) {
+        for (int s = 0; s < C::NSTAGE; ++s) {
+            tc::mbar_init(full_bar(s), PRODUCERS);
+            tc::mbar_init(empty_bar(s), 1);
+        }
+        for (int b = 0; b < C::NACC; ++b) {
+            tc::mbar_init(acc_full_bar(b), 1);
+            tc::mbar_init(acc_empty_bar(b), EPI_THREADS);
+        }
+        tc::mbar_fence_init();
+    }
+    if (warp == MMA_WARP) tc::tmem_alloc<TMEM_COLS>(tc::smem_u32(&tmem_slot));
+    if (tid == 32) { tc::tma_prefetch_desc(&tm_hi); tc::tma_prefetch_desc(&tm_lo); }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(&tmem_slot);
+
+    if (warp < MMA_WARP) {
+        // ---------------- producers: global -> (gather-sum) -> scaled fp16 hi/lo -> swizzled smem ----------------
+        float4 va[BM / 32][2];
+        RowNbrs rn;
+        const float a_scale = f16_a_scale(fp);
+        const bool a_gather = p.a_row_ptr != nullptr;
+        Iter pit(p);
+        Seg ptl;
+        int pc = 0;
+        bool more = pit.next(p, ptl);
+        bool rn_valid = false;
+        int st_k0 = 0, st_n0 = 0;
+        auto prefetch = [&]() {
+            const bool n_reg2 = p.split_dim == SPLIT_N && ptl.n0 >= p.split_at;
+            const int k0 = ptl.kb + pc * BK16;
+            const bool k_reg2 = p.split_dim == SPLIT_K && k0 >= p.split_at;
+            const bool reg2 = n_reg2 || k_reg2;
+            const float* Ab = (reg2 && p.A2 != nullptr) ? p.A2 : p.A;
+            const long long lda = (reg2 && p.A2 != nullptr) ? p.lda2 : p.lda;
+            int a_k0 = k0, a_ke = ptl.ke;
+            if (p.split_dim == SPLIT_K) {
+                if (k_reg2) { a_k0 = k0 - p.split_at; a_ke = ptl.ke - p.split_at; }
+                else a_ke = min(ptl.ke, p.split_at);
+            }
+            st_k0 = k0; st_n0 = ptl.n0;
+            const bool g = a_gather && !reg2;
+            if (g && !rn_valid) { load_row_nbrs(rn, p.a_row_ptr, p.a_col, ptl.m0, p.M, tid); rn_valid = true; }
+            km_prefetch16<BM>(va, Ab, lda, ptl.m0, p.M, a_k0, a_ke, g, rn, p.a_col, tid);
+        };
+        if (more) prefetch();
+        int chunk = 0;
+        while (more) {
+            const int s = chunk % C::NSTAGE;
+            const uint32_t ph = (uint32_t)(chunk / C::NSTAGE) & 1u;
+            tc::mbar_wait(empty_bar(s), ph ^ 1u);
+            const uint32_t sa = smem0 + s * C::STAGE;
+            const uint32_t sb = sa + 2 * A_BYTES;
+            if (tid == 0) {                                      // weights: two bulk tensor copies straight into the stage
+                tc::mbar_expect_tx(full_bar(s), 2 * C::B_BYTES);
+                tc::tma_load_2d(sb, &tm_hi, full_bar(s), st_k0, st_n0);
+                tc::tma_load_2d(sb + C::B_BYTES, &tm_lo, full_bar(s), st_k0, st_n0);
+            }
+            km_store16<BM>(va, sa, sa + A_BYTES, a_scale, tid);
+            tc::fence_async_smem();
+            tc::mbar_arrive(full_bar(s));
+            ++chunk;
+            if (++pc == ptl.nk) {
+                pc = 0;
+                rn_valid = false;
+                more = pit.next(p, ptl);
+            }
+            if (more) prefetch();
+        }
+    } else if (warp == MMA_WARP) {
+        // ---------------- MMA issuer: one lane, tcgen05.mma.kind::f16 into TMEM ----------------
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc::make_idesc_f16(BM, BN, 0, 0);
+            int chunk = 0, it = 0;
+            Iter sit(p);
+            Seg tl;
+            for (; sit.next(p, tl); ++it) {
+                const int b = it % C::NACC;
+                const uint32_t aph = (uint32_t)(it / C::NACC) & 1u;
+                tc::mbar_wait(acc_empty_bar(b), aph ^ 1u);
+                tc::fence_after_sync();
+                const uint32_t d_main = tmem + (uint32_t)(b * 2 * BN), d_corr = d_main + BN;
+                for (int c = 0; c < tl.nk; ++c, ++chunk) {
+                    const int s = chunk % C::NSTAGE;
+                    const uint32_t ph = (uint32_t)(chunk / C::NSTAGE) & 1u;
+                    tc::mbar_wait(full_bar(s), ph);
+                    tc::fence_after_sync();
+                    const uint32_t sa = smem0 + s * C::STAGE;
+                    const uint32_t sb = sa + 2 * A_BYTES;
+#pragma unroll
+                    for (int j = 0; j < BK16 / 16; ++j) {          // 16 fp16 = 32 bytes along the swizzled row
+                        const uint64_t a_hi = operand_desc<BM, true>(sa, j), a_lo = operand_desc<BM, true>(sa + A_BYTES, j);
+                        const uint64_t b_hi = operand_desc<BN, true>(sb, j), b_lo = operand_desc<BN, true>(sb + C::B_BYTES, j);
+                        tc::mma_f16(d_corr, a_lo, b_hi, idesc, (c | j) != 0);
+                        tc::mma_f16(d_corr, a_hi, b_lo, idesc, 1u);
+                        tc::mma_f16(d_main, a_hi, b_hi, idesc, (c | j) != 0);
+                    }
+                    tc::mma_commit(empty_bar(s));
+                }
+                tc::mma_commit(acc_full_bar(b));
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---------------- epilogue warps: TMEM -> registers (x 1/scales) -> smem transpose -> coalesced global ----
+        const int q = warp & 3;
+        const int ew = warp - EPI_WARP0;
+        const float inv = 1.0f / (f16_a_scale(fp) * __ldg(fp.b_scale));
+        float* scratch = reinterpret_cast<float*>(smem_raw + (smem0 - tc::smem_u32(smem_raw)) + C::NSTAGE * C::STAGE) +
+                         ew * (32 * SCR_LD);
+        int it = 0;
+        Iter sit(p);
+        Seg tl;
+        for (; sit.next(p, tl); ++it) {
+            const int epi_mode = tl.partial ? EPI_ATOMIC : p.epi_mode;
+            const int b = it % C::NACC;
+            const uint32_t aph = (uint32_t)(it / C::NACC) & 1u;
+            tc::mbar_wait(acc_full_bar(b), aph);
+            tc::fence_after_sync();
+            const uint32_t d_main = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * 2 * BN);
+            const int row_base = tl.m0 + q * 32;
+            const int rows_valid = min(32, p.M - row_base);
+            for (int g = 0; g < BN / 32; ++g) {
+                const int col0 = g * 32;
+                if (tl.n0 + col0 >= p.N) break;
+                uint32_t v[32], w[32];
+                tc::tmem_ld32(d_main + (uint32_t)col0, v);
+                tc::tmem_ld32(d_main + (uint32_t)(BN + col0), w);
+                tc::tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    st4(scratch + lane * SCR_LD + 4 * j,
+                        make_float4((__uint_as_float(v[4 * j]) + __uint_as_float(w[4 * j])) * inv,
+                                    (__uint_as_float(v[4 * j + 1]) + __uint_as_float(w[4 * j + 1])) * inv,
+                                    (__uint_as_float(v[4 * j + 2]) + __uint_as_float(w[4 * j + 2])) * inv,
+                                    (__uint_as_float(v[4 * j + 3]) + __uint_as_float(w[4 * j + 3])) * inv));
+                __syncwarp();
+                const int n = tl.n0 + col0 + 4 * (lane & 7);
+                if (n < p.N) {
+                    float4 bias4 = f4zero();
+                    if (epi_mode == EPI_GENERIC && p.bias != nullptr) bias4 = ldg4(p.bias + n);
+#pragma unroll 2
+                    for (int r4 = 0; r4 < 8; ++r4) {
+                        const int rr = r4 * 4 + (lane >> 3);
+                        if (rr >= rows_valid) break;
+                        float4 x = ld4(scratch + rr * SCR_LD + 4 * (lane & 7));
+                        float* cp = p.C + (long long)(row_base + rr) * p.ldc + n;
+                        if (epi_mode == EPI_STORE) {
+                            st4(cp, x);
+                        } else if (epi_mode == EPI_ATOMIC) {
+                            red_add4(cp, x);
+                        } else {
+                            if (p.beta != 0.f) {
+                                const float4 o = ld4(cp);
+                                x.x += p.beta * o.x; x.y += p.beta * o.y; x.z += p.beta * o.z; x.w += p.beta * o.w;
+                            }
+                            x += bias4;
+                            if (p.act == GGPM_ACT_RELU) x = make_float4(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f), fmaxf(x.z, 0.f), fmaxf(x.w, 0.f));
+                            else if (p.act == GGPM_ACT_TANH) x = tanh4(x);
+                            else if (p.act == GGPM_ACT_SIGMOID) x = sigmoid4(x);
+                            if (p.zero_row0 && row_base + rr == 0) x = f4zero();
+                            st4(cp, x);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            tc::fence_before_sync();
+            tc::mbar_arrive(acc_empty_bar(b));
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == MMA_WARP) tc::tmem_dealloc<TMEM_COLS>(tmem);
+}
+
 bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 
 typedef CUresult (*TmapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -539,6 +827,33 @@ int make_plane_tmap(CUtensorMap* tm, const float* base, int rows, int cols, long
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     GGPM_REQUIRE(r == CUDA_SUCCESS, "gemm_tcgen05: cuTensorMapEncodeTiled failed (%d)", (int)r);
     return 0;
+}
+
+// fp16 [rows, cols] row-major plane (leading stride ld halves), box = 64 columns (one 128-byte swizzle row) x box_rows
+int make_plane_tmap16(CUtensorMap* tm, const void* base, int rows, int cols, long long ld, int box_rows) {
+    TmapEncodeFn enc = tmap_encoder();
+    GGPM_REQUIRE(enc != nullptr, "gemm_f16: cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)BK16, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    GGPM_REQUIRE(r == CUDA_SUCCESS, "gemm_f16: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return 0;
+}
+
+template <int BN>
+int launch_f16_variant(const F16Params& p, dim3 grid, const CUtensorMap& tm_hi, const CUtensorMap& tm_lo, cudaStream_t st) {
+    static bool configured = false;
+    auto kern = gemm_f16_kernel<BN>;
+    if (!configured) {
+        GGPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM));
+        configured = true;
+    }
+    kern<<<grid, THREADS, Cfg<BN>::SMEM, st>>>(p, tm_hi, tm_lo);
+    return check_launch("gemm_f16x3");
 }
 
 template <int BN, bool A_KC, int B_MODE>
@@ -648,6 +963,154 @@ int launch_gemm_tc(const GemmArgs& g, cudaStream_t st) {
         GGPM_TC(128, false, 0);
     }
 #undef GGPM_TC
+}
+
+bool gemm_f16_eligible(const GemmArgs& g) {
+    const int e = gemm_engine();
+    if (e == GGPM_ENGINE_SIMT_FP32 || e == GGPM_ENGINE_TCGEN05_3XTF32) return false;
+    if (g.M <= 0 || g.N <= 0 || g.K <= 0 || g.sak != 1) return false;
+    if (!g.Bh_hi || !g.Bh_lo || !g.b_scale || g.sbk != 1 || g.b_row_ptr) return false;
+    if (!aligned16(g.A) || !aligned16(g.Bh_hi) || !aligned16(g.Bh_lo)) return false;
+    if (g.sam % 4 != 0 || g.K % 4 != 0 || g.sbn % 8 != 0) return false;
+    if (g.split_dim == SPLIT_M) return false;
+    if (g.split_dim == SPLIT_K && g.split_at % BK16 != 0) return false;
+    if (g.split_dim == SPLIT_N && g.split_at % 128 != 0) return false;
+    if (g.A2 && (!aligned16(g.A2) || g.lda2 % 4 != 0)) return false;
+    return aligned16(g.C) && g.ldc % 4 == 0 && g.N % 4 == 0 && (g.bias == nullptr || aligned16(g.bias));
+}
+
+int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
+    GGPM_REQUIRE(gemm_f16_eligible(g), "gemm_f16x3: operand layout not supported");
+    F16Params fp;
+    TcParams& p = fp.t;
+    p.A = g.A; p.lda = g.sam; p.A2 = g.A2; p.lda2 = g.lda2;
+    p.B = nullptr; p.ldb = g.sbn;
+    p.C = g.C; p.ldc = g.ldc; p.M = g.M; p.N = g.N; p.K = g.K;
+    p.a_row_ptr = g.a_row_ptr; p.a_col = g.a_col; p.b_row_ptr = nullptr; p.b_col = nullptr;
+    p.split_dim = g.split_dim; p.split_at = g.split_at;
+    p.beta = g.beta; p.bias = g.bias; p.act = g.act; p.zero_row0 = g.zero_row0;
+    fp.a_amax = g.a_amax; fp.a_amax_n = g.a_amax_n; fp.a_amax_const = g.a_amax_const; fp.a_deg = g.a_deg;
+    fp.b_scale = g.b_scale;
+    const bool plain_epilogue = !g.bias && g.act == GGPM_ACT_NONE && !g.zero_row0 && (g.beta == 0.f || g.beta == 1.f);
+    bool wide = g.N > 128;
+    if (g.tile_n == 128) wide = false;
+    if (g.tile_n == 256) wide = true;
+    if (g.split_dim == SPLIT_N && g.split_at % 256 != 0) wide = false;
+    const int bnf = wide ? 256 : 128;
+    p.nk = ceil_div(g.K, BK16);
+    p.m_tiles = ceil_div(g.M, BM);
+    p.n_tiles = ceil_div(g.N, bnf);
+    p.total_tiles = p.m_tiles * p.n_tiles;
+    const int sms = sm_count();
+    int ctas = sms;
+    p.tiles_full = p.total_tiles;
+    if (plain_epilogue && p.total_tiles % sms != 0 && p.nk >= 2) {
+        p.tiles_full = (p.total_tiles / sms) * sms;
+        const long long tail_units = (long long)(p.total_tiles - p.tiles_full) * p.nk;
+        if (p.tiles_full == 0 && tail_units < sms) ctas = (int)tail_units;
+    } else if (p.total_tiles < sms) {
+        ctas = p.total_tiles;
+    }
+    if (g.beta != 0.f || g.bias != nullptr || g.act != GGPM_ACT_NONE || g.zero_row0) p.epi_mode = EPI_GENERIC;
+    else p.epi_mode = EPI_STORE;
+    if (p.tiles_full < p.total_tiles && g.beta == 0.f) {
+        const int m_first = (p.tiles_full / p.n_tiles) * BM;
+        GGPM_CUDA(cudaMemset2DAsync(g.C + (size_t)m_first * g.ldc, sizeof(float) * (size_t)g.ldc, 0,
+                                    sizeof(float) * (size_t)g.N, (size_t)(g.M - m_first), st));
+    }
+    ProfScope prof(PROF_GEMM_TC, st, 2.0 * g.M * g.N * (double)g.K);
+    CUtensorMap tm_hi, tm_lo;
+    GGPM_TRY(make_plane_tmap16(&tm_hi, g.Bh_hi, g.N, g.K, g.sbn, bnf));
+    GGPM_TRY(make_plane_tmap16(&tm_lo, g.Bh_lo, g.N, g.K, g.sbn, bnf));
+    dim3 grid(ctas, 1, 1);
+    if (wide) return launch_f16_variant<256>(fp, grid, tm_hi, tm_lo, st);
+    return launch_f16_variant<128>(fp, grid, tm_hi, tm_lo, st);
+}
+
+// ---- helpers of the f16x3 engine: max|w|, scaled fp16 hi / lo planes, max CSR row length ------------------
+__global__ void absmax_kernel(const float* __restrict__ w, long long n, float* __restrict__ amax) {
+    float m = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        m = fmaxf(m, fabsf(w[i]));
+    unsigned u = __reduce_max_sync(0xffffffffu, __float_as_uint(m));     // non-negative floats order like their bits
+    if ((threadIdx.x & 31) == 0 && u != 0) atomicMax(reinterpret_cast<unsigned*>(amax), u);
+}
+
+int launch_absmax(const float* w, long long n, float* amax, cudaStream_t st) {
+    if (n <= 0) return 0;
+    ProfScope prof(PROF_MISC, st, 0.0);
+    const int blocks = (int)(ceil_div_ll(n, 256 * 8) < 592 ? ceil_div_ll(n, 256 * 8) : 592);
+    absmax_kernel<<<blocks, 256, 0, st>>>(w, n, amax);
+    return check_launch("absmax");
+}
+
+__global__ void f16_split_kernel(const float* __restrict__ w, long long n2, const float* __restrict__ amax,
+                                 uint32_t* __restrict__ hi, uint32_t* __restrict__ lo, float* __restrict__ scale) {
+    const float s = tc::pow2_scale(__ldg(amax));
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *scale = s;
+    if (i >= n2) return;
+    const float2 v = *reinterpret_cast<const float2*>(w + 2 * i);
+    uint32_t h, l;
+    tc::split2_f16(v.x * s, v.y * s, h, l);
+    hi[i] = h;
+    lo[i] = l;
+}
+
+int launch_f16_split(const float* w, long long n, const float* amax, void* hi, void* lo, float* scale, cudaStream_t st) {
+    GGPM_REQUIRE(n % 2 == 0 && (((uintptr_t)w | (uintptr_t)hi | (uintptr_t)lo) & 7) == 0, "f16_split: needs 8-byte alignment");
+    if (n == 0) return 0;
+    ProfScope prof(PROF_MISC, st, 0.0);
+    f16_split_kernel<<<(unsigned)ceil_div_ll(n / 2, 256), 256, 0, st>>>(w, n / 2, amax, (uint32_t*)hi, (uint32_t*)lo, scale);
+    return check_launch("f16_split");
+}
+
+// planes of the TRANSPOSE of w [rows, cols]: [cols, rows] fp16
+__global__ void f16_split_transpose_kernel(const float* __restrict__ w, int rows, int cols, const float* __restrict__ amax,
+                                           __half* __restrict__ hi, __half* __restrict__ lo, float* __restrict__ scale) {
+    __shared__ float tile[32][33];
+    const float s = tc::pow2_scale(__ldg(amax));
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && threadIdx.y == 0) *scale = s;
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < rows && c < cols) ? w[(size_t)r * cols + c] : 0.f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (c < cols && r < rows) {
+            const float v = tile[threadIdx.x][i] * s;
+            const __half h = __float2half_rn(v);
+            hi[(size_t)c * rows + r] = h;
+            lo[(size_t)c * rows + r] = __float2half_rn(v - __half2float(h));
+        }
+    }
+}
+
+int launch_f16_split_transpose(const float* w, int rows, int cols, const float* amax, void* hi, void* lo, float* scale,
+                               cudaStream_t st) {
+    if (rows <= 0 || cols <= 0) return 0;
+    ProfScope prof(PROF_MISC, st, 0.0);
+    dim3 grid(ceil_div(cols, 32), ceil_div(rows, 32)), block(32, 8);
+    f16_split_transpose_kernel<<<grid, block, 0, st>>>(w, rows, cols, amax, (__half*)hi, (__half*)lo, scale);
+    return check_launch("f16_split_transpose");
+}
+
+__global__ void max_degree_kernel(const int* __restrict__ rp, int rows, int* __restrict__ out) {
+    int m = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += gridDim.x * blockDim.x)
+        m = max(m, __ldg(rp + i + 1) - __ldg(rp + i));
+    m = __reduce_max_sync(0xffffffffu, m);
+    if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
+}
+
+int launch_max_degree(const int* row_ptr, int rows, int* out, cudaStream_t st) {
+    if (rows <= 0) return 0;
+    ProfScope prof(PROF_MISC, st, 0.0);
+    const int blocks = ceil_div(rows, 256) < 296 ? ceil_div(rows, 256) : 296;
+    max_degree_kernel<<<blocks, 256, 0, st>>>(row_ptr, rows, out);
+    return check_launch("max_degree");
 }
 
 __global__ void tf32_split_kernel(const float* __restrict__ w, long long n4, float* __restrict__ hi, float* __restrict__ lo) {

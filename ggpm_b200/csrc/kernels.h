@@ -28,6 +28,14 @@ struct GemmArgs {
     int tile_n = 0;   // 0 = automatic, 128 or 256 forces the N tile
     // k-contiguous B (weights) already split into tf32 hi / lo planes (same shape and strides as B): loaded by TMA
     const float* B_hi = nullptr; const float* B_lo = nullptr;
+    // ---- fp16 two-term split engine ("f16x3", launch_gemm_f16) ----
+    // k-contiguous B as fp16 hi / lo planes of B * (*b_scale) (same shape, row stride sbn elements): loaded by TMA.
+    // A (fp32, K-major) is scaled in the producers by a power of two derived from the bound
+    //   max|A row| <= amax * max(1, *a_deg),  amax = a_amax ? max(a_amax[0..a_amax_n)) : a_amax_const
+    const void* Bh_hi = nullptr; const void* Bh_lo = nullptr;
+    const float* b_scale = nullptr;
+    const float* a_amax = nullptr; int a_amax_n = 0; float a_amax_const = 1.f;
+    const int* a_deg = nullptr;
 };
 
 int launch_gemm_simt(const GemmArgs& g, cudaStream_t st);
@@ -35,6 +43,15 @@ int launch_gemm_simt(const GemmArgs& g, cudaStream_t st);
 int launch_gemm_nt(const GemmArgs& g, cudaStream_t st);
 int launch_gemm_tc(const GemmArgs& g, cudaStream_t st);
 bool gemm_tc_eligible(const GemmArgs& g);
+int launch_gemm_f16(const GemmArgs& g, cudaStream_t st);
+bool gemm_f16_eligible(const GemmArgs& g);
+// fp16 planes of w * s (or of its transpose), s = the power of two that brings *amax into [2^13, 2^14); *scale = s.
+// launch_absmax accumulates max|w| into *amax (zero it first); n_slots > 1 spreads the atomics.
+int launch_absmax(const float* w, long long n, float* amax, cudaStream_t st);
+int launch_f16_split(const float* w, long long n, const float* amax, void* hi, void* lo, float* scale, cudaStream_t st);
+int launch_f16_split_transpose(const float* w, int rows, int cols, const float* amax, void* hi, void* lo, float* scale,
+                               cudaStream_t st);
+int launch_max_degree(const int* row_ptr, int rows, int* out, cudaStream_t st);   // *out = max(*out, max row length)
 // hi = rn_tf32(w), lo = rn_tf32(w - hi), element-wise over n floats (weights are split once per layer call)
 int launch_tf32_split(const float* w, long long n, float* hi, float* lo, cudaStream_t st);
 int launch_tf32_split_transpose(const float* w, int rows, int cols, float* hi, float* lo, cudaStream_t st);
@@ -47,7 +64,8 @@ int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const
                          const float* gp, const float* c_prev, float* h_out, float* c_out, cudaStream_t st);
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          const float* gp, const float* c_prev, const float* c_cur, const float* dH, const float* dC,
-                         float* dA, float* dX, bool dx_overwrite, float* dP, float* dC_prev, cudaStream_t st);
+                         float* dA, float* dX, bool dx_overwrite, float* dP, float* dC_prev, float* amax16,
+                         cudaStream_t st);
 int launch_gru_gate(int E1, int Hp, const int* rp, const int* col, const XTabArgs& x, const float* h_prev, float* aux,
                     cudaStream_t st);
 int launch_gru_out(int E1, int H, int Hp, const XTabArgs& x, const float* aux, float* h_out, cudaStream_t st);

@@ -1,6 +1,7 @@
 // Thin inline-PTX wrappers for the Blackwell (sm_100a) tensor-core path: mbarrier, tcgen05 (TMEM alloc,
 // MMA, commit, TMEM load), shared-memory matrix descriptors and the 3xTF32 operand split.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -88,6 +89,15 @@ __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint6
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// kind::f16 (fp16 operands, 16 K-elements per instruction, fp32 accumulate): twice the tf32 rate
+__device__ __forceinline__ void mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // arrive on an mbarrier when every MMA issued so far by this thread has completed (implies fence::before_thread_sync)
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -97,6 +107,11 @@ __device__ __forceinline__ void mma_commit(uint32_t bar) {
 __host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N, int a_mn_major, int b_mn_major) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
            ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// same for fp16 x fp16 operands (format code 0), fp32 accumulate
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N, int a_mn_major, int b_mn_major) {
+    return (1u << 4) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) |
+           ((uint32_t)(M >> 4) << 24);
 }
 // shared-memory matrix descriptor, 128-byte swizzle, version 1 (Blackwell); byte offsets are stored >> 4
 // layout: 2 = SWIZZLE_128B (16-byte swizzle unit), 1 = SWIZZLE_128B_BASE32B (32-byte unit: MN-major tf32 operands)
@@ -120,6 +135,39 @@ __device__ __forceinline__ void split4(float4 v, float4& hi, float4& lo) {
 }
 __device__ __forceinline__ void sts4(uint32_t saddr, float4 v) {
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ void sts4u(uint32_t saddr, uint4 v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// ---- fp16 two-term split ("f16x3") --------------------------------------------------------------------
+// v*s ~ hi + lo with hi = rn_fp16(v*s), lo = rn_fp16(v*s - hi): 11 + 11 significant bits, the same as the tf32
+// split, at twice the tensor-core rate and half the shared-memory bytes.  fp16 has a 5-bit exponent, so every
+// operand is first multiplied by a power of two `s` that brings its largest possible magnitude into
+// [2^13, 2^14); the residual is then <= max(|v| 2^-22, max|v| 2^-38) and the epilogue divides the scales out
+// (exactly: they are powers of two).
+__device__ __forceinline__ float pow2_scale(float bound) {
+    if (!(bound > 0.f) || bound > 3.0e38f) return 1.f;
+    int e;
+    frexpf(bound, &e);                 // bound = m * 2^e, m in [0.5, 1)
+    e = 14 - e;
+    e = e < -60 ? -60 : (e > 60 ? 60 : e);
+    return ldexpf(1.f, e);
+}
+__device__ __forceinline__ uint32_t h2_bits(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
+__device__ __forceinline__ void split2_f16(float a, float b, uint32_t& hi, uint32_t& lo) {
+    const __half2 h = __floats2half2_rn(a, b);
+    const float2 f = __half22float2(h);
+    hi = h2_bits(h);
+    lo = h2_bits(__floats2half2_rn(a - f.x, b - f.y));
+}
+// 8 consecutive k (two float4) -> 16 bytes of hi and 16 bytes of lo
+__device__ __forceinline__ void split8_f16(float4 a, float4 b, float s, uint4& hi, uint4& lo) {
+    split2_f16(a.x * s, a.y * s, hi.x, lo.x);
+    split2_f16(a.z * s, a.w * s, hi.y, lo.y);
+    split2_f16(b.x * s, b.y * s, hi.z, lo.z);
+    split2_f16(b.z * s, b.w * s, hi.w, lo.w);
 }
 
 }  // namespace tc

@@ -211,6 +211,32 @@ def gemm_fused(A, sam, sak, B, sbk, sbn, C, M, N, K, beta=0.0, a_csr: Optional[C
     return C
 
 
+def f16_prepare_weights(W: torch.Tensor, transpose: bool = False):
+    """(planes, scal): fp16 hi / lo planes [2, N, K] of W * scale (of W^T when `transpose`) and the device scalars
+    [max|W|, scale] (ggpm_f16_prepare_weights)"""
+    W = W.contiguous()
+    rows, cols = W.shape
+    shape = (cols, rows) if transpose else (rows, cols)
+    planes = torch.empty((2,) + shape, dtype=torch.float16, device=W.device)
+    scal = torch.empty(2, dtype=torch.float32, device=W.device)
+    call("ggpm_f16_prepare_weights", fptr(W), rows, cols, int(transpose), planes[0].data_ptr(), planes[1].data_ptr(),
+         fptr(scal), stream_ptr(W.device))
+    return planes, scal
+
+
+def gemm_f16x3(A, lda, planes, scal, C, M, N, K, beta=0.0, bias=None, act=ACT_NONE, zero_row0=False,
+               a_csr: Optional[CSR] = None, split_dim=0, split_at=0, A2=None, lda2=0, a_amax=None, a_amax_const=1.0,
+               a_deg=None, tile_n=0):
+    """Raw f16x3 entry (ggpm_gemm_f16x3): C = epilogue(A(M,K) @ B(K,N)) with B the prepared fp16 planes [2, N, K]"""
+    call("ggpm_gemm_f16x3", fptr_any(A), lda, planes[0].data_ptr(), planes[1].data_ptr(), scal[1:].data_ptr(),
+         planes.stride(1), fptr(C), _row_stride(C), M, N, K, float(beta), None if bias is None else fptr(bias), act,
+         int(zero_row0), None if a_csr is None else iptr(a_csr.row_ptr), None if a_csr is None else iptr(a_csr.col),
+         split_dim, split_at, None if A2 is None else fptr_any(A2), lda2,
+         None if a_amax is None else fptr(a_amax), 0 if a_amax is None else a_amax.numel(), float(a_amax_const),
+         None if a_deg is None else iptr(a_deg), tile_n, stream_ptr(C.device))
+    return C
+
+
 def tf32_split(W: torch.Tensor):
     """(hi, lo) tf32 planes of a contiguous fp32 weight matrix (ggpm_tf32_split)"""
     W = W.contiguous()

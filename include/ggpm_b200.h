@@ -30,10 +30,11 @@ extern "C" {
 #define GGPM_ACT_TANH 2
 #define GGPM_ACT_SIGMOID 3
 
-/* GEMM engines (ggpm_set_gemm_engine): AUTO picks tcgen05 3xTF32 whenever the shape allows it */
+/* GEMM engines (ggpm_set_gemm_engine): AUTO picks f16x3 where it is wired (graph LSTM gate / state-gradient GEMMs), tcgen05 3xTF32 wherever else the shape allows */
 #define GGPM_ENGINE_AUTO 0
 #define GGPM_ENGINE_SIMT_FP32 1
 #define GGPM_ENGINE_TCGEN05_3XTF32 2
+#define GGPM_ENGINE_TCGEN05_F16X3 3   /* fp16 two-term split (kind::f16) where supported, 3xTF32 elsewhere */
 
 const char* ggpm_last_error(void);
 int ggpm_abi_version(void);
@@ -102,6 +103,27 @@ int ggpm_gemm_fused(const float* A, long long sam, long long sak, const float* B
 /* hi = tf32(w) (round to nearest), lo = tf32(w - hi), element-wise: the 3xTF32 operand split of a weight matrix, done
  * once so that ggpm_gemm_fused can stream the planes by TMA (B_hi/B_lo: same shape and strides as a k-contiguous B). */
 int ggpm_tf32_split(const float* w, long long n, float* hi, float* lo, void* stream);
+
+/* ---- fp16 two-term split engine ("f16x3"): tcgen05.mma.kind::f16 at twice the tf32 rate, same 22-bit operands ----
+ * v * s ~ hi + lo with hi = fp16(v s), lo = fp16(v s - hi); s is a power of two that brings the operand's largest
+ * magnitude into [2^13, 2^14) (fp16 has a 5-bit exponent), divided out exactly in the epilogue.
+ * ggpm_f16_prepare_weights: planes of W [rows, cols] (transpose = 0: planes [rows, cols]; 1: planes [cols, rows]) as
+ * fp16 hi / lo of W * scale; scal[0] <- max|W|, scal[1] <- scale (both device floats). */
+int ggpm_f16_prepare_weights(const float* W, int rows, int cols, int transpose, void* hi, void* lo, float* scal,
+                             void* stream);
+
+/* C[M,N] = epilogue(A(M,K) * B(K,N)) with A fp32 k-contiguous (row stride lda; optional CSR gather-sum a_row_ptr/a_col
+ * and second region along n (split_dim 1) or k (split_dim 2, A2/lda2) exactly as in ggpm_gemm_fused) and B given as
+ * the k-contiguous fp16 planes B_hi/B_lo [N, K] (row stride ldb halves) made by ggpm_f16_prepare_weights with
+ * *b_scale their scale.  The A scale is derived on the device from the bound
+ *   max|A(m, k)| <= amax * max(1, *a_deg),   amax = a_amax ? max(a_amax[0 .. a_amax_n)) : a_amax_const
+ * (a_deg: largest CSR row length when rows are gather-sums, else NULL).  The graph LSTM uses it for the gate /
+ * forget projections (|h| <= 1) and for the state gradient (amax recorded by the cell backward kernel). */
+int ggpm_gemm_f16x3(const float* A, long long lda, const void* B_hi, const void* B_lo, const float* b_scale,
+                    long long ldb, float* C, int ldc, int M, int N, int K, float beta, const float* bias, int act,
+                    int zero_row0, const int32_t* a_row_ptr, const int32_t* a_col, int split_dim, int split_at,
+                    const float* A2, long long lda2, const float* a_amax, int a_amax_n, float a_amax_const,
+                    const int32_t* a_deg, int tile_n, void* stream);
 
 /* dZ = dY * act'(Y) with row 0 optionally zeroed (backward of the fused epilogue above). */
 int ggpm_act_bwd(const float* dY, int ld_dy, const float* Y, int ld_y, float* dZ, int ld_dz, int rows,

@@ -33,7 +33,7 @@ def test_ctypes_table_matches_header(root_dir, lib_path):
     lib = _lib._load()
     assert lib.ggpm_abi_version() == 1
     assert lib.ggpm_launch_count() == 0 or lib.ggpm_launch_count() > 0
-    assert lib.ggpm_get_gemm_engine() in (0, 1, 2)
+    assert lib.ggpm_get_gemm_engine() in (0, 1, 2, 3)
 
 
 def test_argument_validation_needs_no_gpu(lib_path):

@@ -14,10 +14,10 @@ import _checks as C                                                    # noqa: E
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
 SMALL = [n for n in golden_names() if n != "hier_lstm_cfg1"]
-ENGINES = [1, 0]      # 1 = fp32 CUDA cores only, 0 = auto (tcgen05 3xTF32 where the shape allows)
+ENGINES = [1, 2, 0]   # 1 = fp32 CUDA cores only, 2 = tcgen05 3xTF32, 0 = auto (f16x3 for the LSTM gate GEMMs, 3xTF32 elsewhere)
 
 
-@pytest.fixture(params=ENGINES, ids=["simt", "auto"])
+@pytest.fixture(params=ENGINES, ids=["simt", "tf32x3", "auto"])
 def engine(request):
     from ggpm_b200 import _lib
     assert _lib._TEST_BACKEND is None

@@ -23,7 +23,7 @@ def rel(a, b):
     return float((a - b).abs().max()) / max(float(b.abs().max()), 1e-30)
 
 
-@pytest.fixture(params=[1, 0], ids=["simt", "auto"])
+@pytest.fixture(params=[1, 2, 0], ids=["simt", "tf32x3", "auto"])
 def engine(request):
     _lib.set_gemm_engine(request.param)
     yield request.param
@@ -220,6 +220,87 @@ def test_fused_weight_gradient(E, Hp):
     S = _gsum(h, idx)
     ref = torch.cat([dA[:, :3 * Hp].double().t() @ S, dP.double().t() @ h.double()], 0) + 1.0
     assert rel(out, ref) <= 1e-5, rel(out, ref)
+
+
+# ---------------------------------------------------------------------------------------------------
+# f16x3 engine (fp16 two-term split, tcgen05.mma.kind::f16)
+# ---------------------------------------------------------------------------------------------------
+def _max_deg(csr):
+    rp = csr.row_ptr
+    return (rp[1:] - rp[:-1]).max().to(torch.int32).reshape(1).contiguous()
+
+
+@pytest.mark.parametrize("M,N,K,scale_a,scale_w", [(300, 128, 64, 1.0, 1.0), (1000, 1024, 256, 1.0, 0.05),
+                                                   (4100, 512, 512, 1e-6, 30.0), (129, 256, 96, 1e4, 1e-3),
+                                                   (20000, 1024, 256, 1.0, 0.06)])
+def test_f16x3_plain_gemm(M, N, K, scale_a, scale_w):
+    torch.manual_seed(M + N)
+    A = torch.randn(M, K, device=DEV) * scale_a
+    A[::7] *= 1e-4                                      # rows far below the tensor max keep absolute accuracy
+    W = torch.randn(N, K, device=DEV) * scale_w
+    planes, scal = Fn.f16_prepare_weights(W)
+    amax = A.abs().max().reshape(1)
+    out = torch.full((M, N), 7.0, device=DEV)
+    Fn.gemm_f16x3(A, K, planes, scal, out, M, N, K, a_amax=amax)
+    ref = A.double() @ W.double().t()
+    assert rel(out, ref) <= 2e-6, rel(out, ref)
+    assert float(scal[0]) == float(W.abs().max())
+
+
+def test_f16x3_epilogue_and_transposed_planes():
+    torch.manual_seed(5)
+    M, N, K = 777, 384, 160
+    A = torch.rand(M, K, device=DEV) * 2 - 1
+    W = torch.randn(K, N, device=DEV) * 0.1              # B(k, n) = W[k, n]: planes of the transpose
+    planes, scal = Fn.f16_prepare_weights(W, transpose=True)
+    assert planes.shape == (2, N, K)
+    bias = torch.randn(N, device=DEV)
+    out = torch.randn(M, N, device=DEV)
+    ref = torch.tanh(A.double() @ W.double() + out.double() + bias.double())
+    ref[0] = 0
+    Fn.gemm_f16x3(A, K, planes, scal, out, M, N, K, beta=1.0, bias=bias, act=_lib.ACT_TANH, zero_row0=True,
+                  a_amax_const=1.0)
+    assert rel(out, ref) <= 2e-6, rel(out, ref)
+
+
+@pytest.mark.parametrize("E,Hp,tile_n", [(300, 128, 0), (1000, 256, 0), (1000, 256, 128), (2500, 512, 0), (19000, 256, 0)])
+def test_f16x3_fused_gate_projection_forward(E, Hp, tile_n):
+    rng = np.random.default_rng(E + Hp)
+    h = torch.rand(E, Hp, device=DEV) * 2 - 1            # |h| <= 1 like o * tanh(c)
+    h[0] = 0
+    U4 = torch.randn(4 * Hp, Hp, device=DEV) / Hp ** 0.5
+    idx, csr = _rand_csr(rng, E, E)
+    planes, scal = Fn.f16_prepare_weights(U4)
+    out = torch.empty(E, 4 * Hp, device=DEV)
+    Fn.gemm_f16x3(h, Hp, planes, scal, out, E, 4 * Hp, Hp, a_csr=csr, split_dim=1, split_at=3 * Hp, a_amax_const=1.0,
+                  a_deg=_max_deg(csr), tile_n=tile_n)
+    S = _gsum(h, idx)
+    ref = torch.cat([S @ U4[:3 * Hp].double().t(), h.double() @ U4[3 * Hp:].double().t()], 1)
+    assert rel(out, ref) <= 2e-6, rel(out, ref)
+
+
+@pytest.mark.parametrize("E,Hp,gscale", [(300, 128, 1.0), (1000, 256, 1e-7), (5000, 256, 1.0), (19000, 256, 3e3)])
+def test_f16x3_fused_state_gradient(E, Hp, gscale):
+    rng = np.random.default_rng(E)
+    dA = torch.randn(E, 4 * Hp, device=DEV) * gscale
+    dP = torch.randn(E, Hp, device=DEV) * gscale
+    U4 = torch.randn(4 * Hp, Hp, device=DEV) / Hp ** 0.5
+    idx, csr = _rand_csr(rng, E, E)
+    bt = csr.T
+    planes, scal = Fn.f16_prepare_weights(U4, transpose=True)        # [Hp, 4Hp]
+    amax = torch.zeros(16, device=DEV)
+    amax[3] = max(float(dA.abs().max()), float(dP.abs().max()) / max(1, int(_max_deg(bt))))
+    out = torch.empty(E, Hp, device=DEV)
+    Fn.gemm_f16x3(dA, 4 * Hp, planes, scal, out, E, Hp, 4 * Hp, a_csr=bt, split_dim=2, split_at=3 * Hp, A2=dP, lda2=Hp,
+                  a_amax=amax, a_deg=_max_deg(bt))
+    dS = dA[:, :3 * Hp].double() @ U4[:3 * Hp].double()
+    scat = torch.zeros(E, Hp, dtype=torch.float64, device=DEV)
+    flat = idx.reshape(-1)
+    rows = torch.arange(E, device=DEV).repeat_interleave(idx.shape[1])
+    keep = flat != 0
+    scat.index_add_(0, flat[keep], dS[rows[keep]])
+    ref = scat + dP.double() @ U4[3 * Hp:].double()
+    assert rel(out, ref) <= 2e-6, rel(out, ref)
 
 
 def test_linear_act_autograd(engine):
