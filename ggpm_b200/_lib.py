@@ -33,6 +33,7 @@ SIGNATURES = {
     "ggpm_gemm": (I, [P, c_longlong, c_longlong, P, c_longlong, c_longlong, P, I, I, I, I, c_float, P, I, I, I, P]),
     "ggpm_gemm_fused": (I, [P, c_longlong, c_longlong, P, c_longlong, c_longlong, P, I, I, I, I, c_float, P, I, I, I,
                             P, P, P, P, I, I, P, c_longlong, I, P, P, P]),
+    "ggpm_gemm_f16x3_planes": (I, [P, P, P, c_longlong, P, P, P, c_longlong, P, I, I, I, I, c_float, I, P]),
     "ggpm_tf32_split": (I, [P, c_longlong, P, P, P]),
     "ggpm_f16_prepare_weights": (I, [P, I, I, I, P, P, P, P]),
     "ggpm_gemm_f16x3": (I, [P, c_longlong, P, P, P, c_longlong, P, I, I, I, I, c_float, P, I, I, P, P, I, I, P, c_longlong,
@@ -40,8 +41,8 @@ SIGNATURES = {
     "ggpm_act_bwd": (I, [P, I, P, I, P, I, I, I, I, I, P]),
     "ggpm_colsum": (I, [P, I, I, I, P, I, P]),
     "ggpm_table_wgrad": (I, [P, I, I, I, P, P, P, I, I, P]),
-    "ggpm_lstm_fwd": (I, [I, I, I, I, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, P]),
-    "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 26),
+    "ggpm_lstm_fwd": (I, [I, I, I, I, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, P]),
+    "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 28),
     "ggpm_gru_fwd": (I, [I, I, I, I] + [P] * 13 + [I, P]),
     "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
 }

@@ -230,6 +230,19 @@ extern "C" int ggpm_gemm_f16x3(const float* A, long long lda, const void* B_hi, 
     return launch_gemm_f16(g, (cudaStream_t)stream);
 }
 
+extern "C" int ggpm_gemm_f16x3_planes(const void* A_hi, const void* A_lo, const float* a_scale, long long lda,
+                                      const void* B_hi, const void* B_lo, const float* b_scale, long long ldb, float* C,
+                                      int ldc, int M, int N, int K, float beta, int tn, void* stream) {
+    GGPM_REQUIRE(A_hi && A_lo && a_scale && B_hi && B_lo && b_scale && C, "gemm_f16x3_planes: null pointer");
+    GGPM_REQUIRE(beta == 0.f || beta == 1.f, "gemm_f16x3_planes: beta must be 0 or 1");
+    GemmArgs g;
+    g.Ah_hi = A_hi; g.Ah_lo = A_lo; g.a_scale = a_scale; g.lda_h = lda; g.f16_tn = tn ? 1 : 0;
+    g.Bh_hi = B_hi; g.Bh_lo = B_lo; g.b_scale = b_scale; g.sbn = ldb;
+    g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K; g.beta = beta;
+    GGPM_REQUIRE(gemm_f16_eligible(g), "gemm_f16x3_planes: needs the f16x3 engine, 16-byte aligned planes, strides %% 8 == 0");
+    return launch_gemm_f16(g, (cudaStream_t)stream);
+}
+
 extern "C" int ggpm_tf32_split(const float* w, long long n, float* hi, float* lo, void* stream) {
     GGPM_REQUIRE(w && hi && lo && n >= 0, "tf32_split: null pointer");
     return launch_tf32_split(w, n, hi, lo, (cudaStream_t)stream);
@@ -247,7 +260,7 @@ static int check_dims(const char* who, int E1, int H, int Hp, int depth) {
 extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                              const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
                              const float* Ug, const float* Uf, float* hist_h, float* hist_c, float* hist_gp,
-                             float* s_scratch, float* w_split, int keep_history, void* stream) {
+                             float* s_scratch, float* w_split, void* hist_h16, int keep_history, void* stream) {
     GGPM_TRY(check_dims("lstm_fwd", E1, H, Hp, depth));
     GGPM_REQUIRE(b_ptr && b_col && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp && s_scratch,
                  "lstm_fwd: null pointer");
@@ -270,14 +283,18 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
     } else if (w_tma) {
         GGPM_TRY(launch_tf32_split(Ug, (long long)wn, w_split, w_split + wn, st));
     }
+    const bool h16 = f16 && keep_history && hist_h16 != nullptr && ((uintptr_t)hist_h16 & 15) == 0;
     for (int t = 1; t <= depth; ++t) {
         const int cur = keep_history ? (t - 1) : ((t - 1) & 1);
         const int prev = keep_history ? (t - 2) : ((t - 2) & 1);
         float* h_cur = hist_h + cur * row;
         float* c_cur = hist_c + cur * row;
         float* gp = hist_gp + (size_t)cur * 4 * row;
+        // fp16 planes of h^t (2 bytes per element): [cur][hi | lo][E1 * Hp]
+        char* h16_hi = h16 ? (char*)hist_h16 + (size_t)cur * 4 * row : nullptr;
+        char* h16_lo = h16 ? h16_hi + 2 * row : nullptr;
         if (t == 1) {
-            GGPM_TRY(launch_lstm_cell_fwd(true, E1, H, Hp, b_ptr, b_col, x, nullptr, nullptr, h_cur, c_cur, st));
+            GGPM_TRY(launch_lstm_cell_fwd(true, E1, H, Hp, b_ptr, b_col, x, nullptr, nullptr, h_cur, c_cur, h16_hi, h16_lo, st));
             continue;
         }
         const float* h_prev = hist_h + prev * row;
@@ -308,7 +325,7 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
             GGPM_TRY(gemm_nt(s_scratch, Hp, Ug, Hp, gp, 4 * Hp, E1, 3 * Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
             GGPM_TRY(gemm_nt(h_prev, Hp, Uf, Hp, gp + 3 * Hp, 4 * Hp, E1, Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
         }
-        GGPM_TRY(launch_lstm_cell_fwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, h_cur, c_cur, st));
+        GGPM_TRY(launch_lstm_cell_fwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, h_cur, c_cur, h16_hi, h16_lo, st));
     }
     return 0;
 }
@@ -318,7 +335,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
                              const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
                              const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
                              float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
-                             float* w_split, void* stream) {
+                             float* w_split, const void* hist_h16, void* z_planes, void* stream) {
     GGPM_TRY(check_dims("lstm_bwd", E1, H, Hp, depth));
     GGPM_REQUIRE(b_ptr && b_col && bt_ptr && bt_row && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp &&
                      dH_final && dX && dUg && dUf && dA && dC && dP && dS && S && dHn,
@@ -344,6 +361,11 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     } else if (w_tma) {
         GGPM_TRY(launch_tf32_split_transpose(Ug, 4 * Hp, Hp, w_split, w_split + wn, st));
     }
+    // fully TMA-fed backward GEMMs: Z planes (written by the zgather kernel) and the h planes saved by the forward
+    const bool zmode = f16 && hist_h16 != nullptr && z_planes != nullptr && Hp % 64 == 0 &&
+                       (((uintptr_t)hist_h16 | (uintptr_t)z_planes) & 15) == 0;
+    char* z_hi = (char*)z_planes;
+    char* z_lo = z_hi + (size_t)8 * row;                  // 4 * row halves
     for (int t = depth; t >= 1; --t) {
         const float* c_cur = hist_c + (size_t)(t - 1) * row;
         const float* gp = hist_gp + (size_t)(t - 1) * 4 * row;
@@ -362,7 +384,24 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
         float* amax_t = f16 ? fw.scal + 16 + 16 * (size_t)t : nullptr;
         GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_cur, dA, dX, overwrite,
                                       dP, dC_prev, amax_t, st));
-        if (tc_ok) {
+        if (zmode) {
+            // Z = [gather^T(dA[:, :3Hp]) | dP] as scaled fp16 planes; then dH^{t-1} = Z [Ug; Uf] and
+            // [dUg; dUf] += Z^T h^{t-1}: two plain GEMMs whose operands all arrive by TMA
+            float* z_scale = fw.scal + 4;
+            GGPM_TRY(launch_lstm_zgather(E1, Hp, bt_ptr, bt_row, dA, dP, amax_t, reinterpret_cast<const int*>(fw.scal + 2),
+                                         z_hi, z_lo, z_scale, st));
+            GemmArgs w;
+            w.f16_tn = 1; w.Ah_hi = z_hi; w.Ah_lo = z_lo; w.lda_h = 4 * Hp; w.a_scale = z_scale;
+            w.Bh_hi = (const char*)hist_h16 + (size_t)(t - 2) * 4 * row; w.Bh_lo = (const char*)w.Bh_hi + 2 * row;
+            w.sbn = Hp; w.b_scale_const = 8192.f;          // GGPM_H16_SCALE of the forward cell kernel
+            w.C = dUg; w.ldc = Hp; w.M = 4 * Hp; w.N = Hp; w.K = E1; w.beta = 1.f;
+            GGPM_TRY(launch_gemm_f16(w, st));
+            GemmArgs d;
+            d.Ah_hi = z_hi; d.Ah_lo = z_lo; d.lda_h = 4 * Hp; d.a_scale = z_scale;
+            d.Bh_hi = fw.hi; d.Bh_lo = fw.lo; d.sbn = 4 * Hp; d.b_scale = fw.scal + 1;
+            d.C = dH_next; d.ldc = Hp; d.M = E1; d.N = Hp; d.K = 4 * Hp;
+            GGPM_TRY(launch_gemm_f16(d, st));
+        } else if (tc_ok) {
             // weight gradients: dUg += dA[:, :3Hp]^T S^t (S re-gathered inside the B-operand prologue) ;
             // dUf += dP^T h^{t-1}
             GemmArgs w;

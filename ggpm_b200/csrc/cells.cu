@@ -7,10 +7,12 @@
 // Math: SURVEY.md Appendix A (restated and checked against autograd in tests/_proto.py).
 #include "common.cuh"
 #include "kernels.h"
+#include "tc_ptx.cuh"
 
 namespace ggpm {
 
 constexpr int kCellWarps = 8;
+constexpr float kH16Scale = 8192.f;      // 2^13: fp16 planes of h (|h| <= 1), GGPM_H16_SCALE
 
 struct XTab {
     const float* Yn; const int* src; const float* T; const int* k1; const int* k2; int ld;   // ld = G*Hp
@@ -40,7 +42,7 @@ template <bool FIRST>
 __global__ void __launch_bounds__(kCellWarps * 32)
 lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
                      const float* __restrict__ gp, const float* __restrict__ c_prev, float* __restrict__ h_out,
-                     float* __restrict__ c_out) {
+                     float* __restrict__ c_out, uint2* __restrict__ h16_hi, uint2* __restrict__ h16_lo) {
     const int lane = threadIdx.x & 31;
     const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (e >= E1) return;
@@ -49,6 +51,7 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
         for (int c = lane * 4; c < Hp; c += 128) {
             st4(h_out + c, f4zero());
             st4(c_out + c, f4zero());
+            if (h16_hi) { h16_hi[c >> 2] = make_uint2(0u, 0u); h16_lo[c >> 2] = make_uint2(0u, 0u); }
         }
         return;
     }
@@ -85,6 +88,58 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
         float4 h = clip_cols(sigmoid4(ao) * tanh4(chat), c, H);
         st4(c_out + (size_t)e * Hp + c, chat);
         st4(h_out + (size_t)e * Hp + c, h);
+        if (h16_hi) {   // fp16 hi / lo planes of h * 2^13 (|h| <= 1): the B operand of the f16x3 weight-gradient GEMM
+            uint2 hi, lo;
+            tc::split2_f16(h.x * kH16Scale, h.y * kH16Scale, hi.x, lo.x);
+            tc::split2_f16(h.z * kH16Scale, h.w * kH16Scale, hi.y, lo.y);
+            h16_hi[((size_t)e * Hp + c) >> 2] = hi;
+            h16_lo[((size_t)e * Hp + c) >> 2] = lo;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Z = [gather^T(dA[:, :3Hp]) | dP]  ->  fp16 hi / lo planes [E1, 4Hp], scaled.  Both backward GEMMs of a round
+// consume it: dH^{t-1} = Z [Ug; Uf] and [dUg; dUf] += Z^T h^{t-1} (the neighbour sum moved onto the gradient side
+// by linearity), so neither needs a gather in its operand path and both are fed by TMA alone.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCellWarps * 32)
+lstm_zgather_kernel(int E1, int Hp, const int* __restrict__ tp, const int* __restrict__ trow,
+                    const float* __restrict__ dA, const float* __restrict__ dP, const float* __restrict__ amax16,
+                    const int* __restrict__ deg, uint4* __restrict__ z_hi, uint4* __restrict__ z_lo,
+                    float* __restrict__ scale_out) {
+    const int lane = threadIdx.x & 31;
+    const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) amax = fmaxf(amax, __ldg(amax16 + i));
+    const float s = tc::pow2_scale(amax * (float)max(1, __ldg(deg)));
+    if (blockIdx.x == 0 && threadIdx.x == 0) *scale_out = s;
+    if (n >= E1) return;
+    const int ld4h = 4 * Hp;
+    const int b = __ldg(tp + n), en = __ldg(tp + n + 1);
+    for (int c = lane * 8; c < ld4h; c += 256) {
+        float4 a0 = f4zero(), a1 = f4zero();
+        if (c < 3 * Hp) {
+            int j = b;
+            for (; j + 2 <= en; j += 2) {
+                const float* r0 = dA + (size_t)__ldg(trow + j) * ld4h + c;
+                const float* r1 = dA + (size_t)__ldg(trow + j + 1) * ld4h + c;
+                const float4 x0 = ld4(r0), x1 = ld4(r0 + 4), y0 = ld4(r1), y1 = ld4(r1 + 4);
+                a0 += x0; a1 += x1; a0 += y0; a1 += y1;
+            }
+            if (j < en) {
+                const float* r0 = dA + (size_t)__ldg(trow + j) * ld4h + c;
+                a0 += ld4(r0); a1 += ld4(r0 + 4);
+            }
+        } else {
+            const float* r = dP + (size_t)n * Hp + (c - 3 * Hp);
+            a0 = ld4(r); a1 = ld4(r + 4);
+        }
+        uint4 hi, lo;
+        tc::split8_f16(a0, a1, s, hi, lo);
+        z_hi[((size_t)n * ld4h + c) >> 3] = hi;
+        z_lo[((size_t)n * ld4h + c) >> 3] = lo;
     }
 }
 
@@ -366,14 +421,25 @@ table_wgrad_kernel(const float* __restrict__ dX, int ld_dx, int rows, int width,
 static inline int cell_blocks(int E1) { return ceil_div(E1, kCellWarps); }
 
 int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
-                         const float* gp, const float* c_prev, float* h_out, float* c_out, cudaStream_t st) {
+                         const float* gp, const float* c_prev, float* h_out, float* c_out, void* h16_hi, void* h16_lo,
+                         cudaStream_t st) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_FWD, st, 0.0);
     if (first)
-        lstm_cell_fwd_kernel<true><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out);
+        lstm_cell_fwd_kernel<true><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out,
+                                                                                (uint2*)h16_hi, (uint2*)h16_lo);
     else
-        lstm_cell_fwd_kernel<false><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out);
+        lstm_cell_fwd_kernel<false><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out,
+                                                                                 (uint2*)h16_hi, (uint2*)h16_lo);
     return check_launch("lstm_cell_fwd");
+}
+
+int launch_lstm_zgather(int E1, int Hp, const int* t_ptr, const int* t_row, const float* dA, const float* dP,
+                        const float* amax16, const int* deg, void* z_hi, void* z_lo, float* scale_out, cudaStream_t st) {
+    ProfScope prof(PROF_GATHER, st, 0.0);
+    lstm_zgather_kernel<<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, Hp, t_ptr, t_row, dA, dP, amax16, deg, (uint4*)z_hi,
+                                                                      (uint4*)z_lo, scale_out);
+    return check_launch("lstm_zgather");
 }
 
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,

@@ -519,10 +519,21 @@ struct F16Params {
     TcParams t;
     const float* a_amax; int a_amax_n; float a_amax_const;
     const int* a_deg;
-    const float* b_scale;
+    const float* a_scale;                  // when given: the A scale itself (A already is fp16 planes)
+    const float* b_scale; float b_scale_const;
 };
 
+// modes of gemm_f16_kernel
+enum { F16_A_REGS = 0,      // A: fp32 K-major rows through registers (gather-sum, scaling, split); B: K-major planes by TMA
+       F16_A_TMA = 1,       // A and B: K-major fp16 hi / lo planes by TMA (no producer arithmetic at all)
+       F16_TN_TMA = 2 };    // A(m,k) and B(k,n) both stored k-row-major (MN-major operands), planes by TMA: weight gradients
+
+__device__ __forceinline__ float f16_b_scale(const F16Params& p) {
+    return p.b_scale != nullptr ? __ldg(p.b_scale) : p.b_scale_const;
+}
+
 __device__ __forceinline__ float f16_a_scale(const F16Params& p) {
+    if (p.a_scale != nullptr) return __ldg(p.a_scale);
     float amax = p.a_amax_const;
     if (p.a_amax != nullptr) {
         amax = 0.f;
@@ -599,10 +610,24 @@ __device__ __forceinline__ void km_store16(const float4 (&v)[ROWS / 32][2], uint
     }
 }
 
-template <int BN>
+// shared-memory descriptor of the 16-deep K step `j` of one fp16 plane of a stage.
+//   K-major (rows of 64 k = 128 B, 8-row groups of 1024 B): the step advances 32 B inside the swizzled row.
+//   MN-major (TN): swizzle atoms of 64 mn x 8 k (1024 B); a TMA box lays the 8 k-atoms of one 64-wide mn block
+//   contiguously (8192 B), mn blocks one after the other: LBO (mn-atom stride) = 8192, SBO (k-atom stride) = 1024,
+//   and a step (16 k = 2 atoms) advances 2048 B.
+template <bool TN>
+__device__ __forceinline__ uint64_t f16_desc(uint32_t saddr, int kstep) {
+    if (TN) return tc::make_sdesc(saddr + kstep * 2048, 8192, 1024, 2);
+    return tc::make_sdesc(saddr + kstep * 32, 16, 1024, 2);
+}
+
+template <int BN, int MODE>
 __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp, const __grid_constant__ CUtensorMap tm_hi,
-                                                              const __grid_constant__ CUtensorMap tm_lo) {
+                                                              const __grid_constant__ CUtensorMap tm_lo,
+                                                              const __grid_constant__ CUtensorMap ta_hi,
+                                                              const __grid_constant__ CUtensorMap ta_lo) {
     using C = Cfg<BN>;
+    constexpr bool TN = MODE == F16_TN_TMA;
     using Iter = SegIter<BN, BK16>;
     const TcParams& p = fp.t;
     extern __shared__ uint8_t smem_raw[];
@@ -619,7 +644,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
 
     if (tid == 0) {
         for (int s = 0; s < C::NSTAGE; ++s) {
-            tc::mbar_init(full_bar(s), PRODUCERS);
+            tc::mbar_init(full_bar(s), MODE == F16_A_REGS ? PRODUCERS : 1);
             tc::mbar_init(empty_bar(s), 1);
         }
         for (int b = 0; b < C::NACC; ++b) {
@@ -629,13 +654,47 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
         tc::mbar_fence_init();
     }
     if (warp == MMA_WARP) tc::tmem_alloc<TMEM_COLS>(tc::smem_u32(&tmem_slot));
-    if (tid == 32) { tc::tma_prefetch_desc(&tm_hi); tc::tma_prefetch_desc(&tm_lo); }
+    if (tid == 32) {
+        tc::tma_prefetch_desc(&tm_hi); tc::tma_prefetch_desc(&tm_lo);
+        if (MODE != F16_A_REGS) { tc::tma_prefetch_desc(&ta_hi); tc::tma_prefetch_desc(&ta_lo); }
+    }
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(&tmem_slot);
 
-    if (warp < MMA_WARP) {
+    if (MODE != F16_A_REGS && warp < MMA_WARP) {
+        // ---------------- TMA-only producer: one thread streams both operands' planes into the stages ----------------
+        if (tid == 0) {
+            Iter pit(p);
+            Seg tl;
+            int chunk = 0;
+            while (pit.next(p, tl)) {
+                for (int c = 0; c < tl.nk; ++c, ++chunk) {
+                    const int s = chunk % C::NSTAGE;
+                    const uint32_t ph = (uint32_t)(chunk / C::NSTAGE) & 1u;
+                    tc::mbar_wait(empty_bar(s), ph ^ 1u);
+                    const uint32_t sa = smem0 + s * C::STAGE;
+                    const uint32_t sb = sa + 2 * A_BYTES;
+                    const int k0 = tl.kb + c * BK16;
+                    tc::mbar_expect_tx(full_bar(s), 2 * A_BYTES + 2 * C::B_BYTES);
+                    if (TN) {
+                        // 3-D maps (64 mn, k rows, mn / 64): one box = all swizzle atoms of the tile, atom-major in smem
+                        tc::tma_load_3d(sa, &ta_hi, full_bar(s), 0, k0, tl.m0 / 64);
+                        tc::tma_load_3d(sa + A_BYTES, &ta_lo, full_bar(s), 0, k0, tl.m0 / 64);
+                        tc::tma_load_3d(sb, &tm_hi, full_bar(s), 0, k0, tl.n0 / 64);
+                        tc::tma_load_3d(sb + C::B_BYTES, &tm_lo, full_bar(s), 0, k0, tl.n0 / 64);
+                    } else {
+                        tc::tma_load_2d(sa, &ta_hi, full_bar(s), k0, tl.m0);
+                        tc::tma_load_2d(sa + A_BYTES, &ta_lo, full_bar(s), k0, tl.m0);
+                        tc::tma_load_2d(sb, &tm_hi, full_bar(s), k0, tl.n0);
+                        tc::tma_load_2d(sb + C::B_BYTES, &tm_lo, full_bar(s), k0, tl.n0);
+                    }
+                    tc::mbar_arrive(full_bar(s));
+                }
+            }
+        }
+    } else if (warp < MMA_WARP) {
         // ---------------- producers: global -> (gather-sum) -> scaled fp16 hi/lo -> swizzled smem ----------------
         float4 va[BM / 32][2];
         RowNbrs rn;
@@ -691,7 +750,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
     } else if (warp == MMA_WARP) {
         // ---------------- MMA issuer: one lane, tcgen05.mma.kind::f16 into TMEM ----------------
         if (lane == 0) {
-            constexpr uint32_t idesc = tc::make_idesc_f16(BM, BN, 0, 0);
+            constexpr uint32_t idesc = tc::make_idesc_f16(BM, BN, TN ? 1 : 0, TN ? 1 : 0);
             int chunk = 0, it = 0;
             Iter sit(p);
             Seg tl;
@@ -710,8 +769,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
                     const uint32_t sb = sa + 2 * A_BYTES;
 #pragma unroll
                     for (int j = 0; j < BK16 / 16; ++j) {          // 16 fp16 = 32 bytes along the swizzled row
-                        const uint64_t a_hi = operand_desc<BM, true>(sa, j), a_lo = operand_desc<BM, true>(sa + A_BYTES, j);
-                        const uint64_t b_hi = operand_desc<BN, true>(sb, j), b_lo = operand_desc<BN, true>(sb + C::B_BYTES, j);
+                        const uint64_t a_hi = f16_desc<TN>(sa, j), a_lo = f16_desc<TN>(sa + A_BYTES, j);
+                        const uint64_t b_hi = f16_desc<TN>(sb, j), b_lo = f16_desc<TN>(sb + C::B_BYTES, j);
                         tc::mma_f16(d_corr, a_lo, b_hi, idesc, (c | j) != 0);
                         tc::mma_f16(d_corr, a_hi, b_lo, idesc, 1u);
                         tc::mma_f16(d_main, a_hi, b_hi, idesc, (c | j) != 0);
@@ -726,7 +785,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
         // ---------------- epilogue warps: TMEM -> registers (x 1/scales) -> smem transpose -> coalesced global ----
         const int q = warp & 3;
         const int ew = warp - EPI_WARP0;
-        const float inv = 1.0f / (f16_a_scale(fp) * __ldg(fp.b_scale));
+        const float inv = 1.0f / (f16_a_scale(fp) * f16_b_scale(fp));
         float* scratch = reinterpret_cast<float*>(smem_raw + (smem0 - tc::smem_u32(smem_raw)) + C::NSTAGE * C::STAGE) +
                          ew * (32 * SCR_LD);
         int it = 0;
@@ -844,15 +903,32 @@ int make_plane_tmap16(CUtensorMap* tm, const void* base, int rows, int cols, lon
     return 0;
 }
 
-template <int BN>
-int launch_f16_variant(const F16Params& p, dim3 grid, const CUtensorMap& tm_hi, const CUtensorMap& tm_lo, cudaStream_t st) {
+// 3-D view of a k-row-major fp16 plane [k_rows, mn] (row stride ld halves) for MN-major operand tiles:
+// dims (64 mn, k rows, mn / 64), box (64, 64, mn_blocks): one box = mn_blocks swizzle-atom columns of 64 k rows each
+int make_plane_tmap16_tn(CUtensorMap* tm, const void* base, int k_rows, int mn, long long ld, int mn_blocks) {
+    TmapEncodeFn enc = tmap_encoder();
+    GGPM_REQUIRE(enc != nullptr, "gemm_f16: cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[3] = {64, (cuuint64_t)k_rows, (cuuint64_t)(mn / 64)};
+    cuuint64_t strides[2] = {(cuuint64_t)ld * 2, 128};
+    cuuint32_t box[3] = {64, (cuuint32_t)BK16, (cuuint32_t)mn_blocks};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    GGPM_REQUIRE(r == CUDA_SUCCESS, "gemm_f16: cuTensorMapEncodeTiled (3-D) failed (%d)", (int)r);
+    return 0;
+}
+
+template <int BN, int MODE>
+int launch_f16_variant(const F16Params& p, dim3 grid, const CUtensorMap& tm_hi, const CUtensorMap& tm_lo,
+                       const CUtensorMap& ta_hi, const CUtensorMap& ta_lo, cudaStream_t st) {
     static bool configured = false;
-    auto kern = gemm_f16_kernel<BN>;
+    auto kern = gemm_f16_kernel<BN, MODE>;
     if (!configured) {
         GGPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM));
         configured = true;
     }
-    kern<<<grid, THREADS, Cfg<BN>::SMEM, st>>>(p, tm_hi, tm_lo);
+    kern<<<grid, THREADS, Cfg<BN>::SMEM, st>>>(p, tm_hi, tm_lo, ta_hi, ta_lo);
     return check_launch("gemm_f16x3");
 }
 
@@ -965,22 +1041,35 @@ int launch_gemm_tc(const GemmArgs& g, cudaStream_t st) {
 #undef GGPM_TC
 }
 
+static int f16_mode(const GemmArgs& g) { return g.f16_tn ? F16_TN_TMA : (g.Ah_hi != nullptr ? F16_A_TMA : F16_A_REGS); }
+
 bool gemm_f16_eligible(const GemmArgs& g) {
     const int e = gemm_engine();
     if (e == GGPM_ENGINE_SIMT_FP32 || e == GGPM_ENGINE_TCGEN05_3XTF32) return false;
-    if (g.M <= 0 || g.N <= 0 || g.K <= 0 || g.sak != 1) return false;
-    if (!g.Bh_hi || !g.Bh_lo || !g.b_scale || g.sbk != 1 || g.b_row_ptr) return false;
-    if (!aligned16(g.A) || !aligned16(g.Bh_hi) || !aligned16(g.Bh_lo)) return false;
-    if (g.sam % 4 != 0 || g.K % 4 != 0 || g.sbn % 8 != 0) return false;
-    if (g.split_dim == SPLIT_M) return false;
-    if (g.split_dim == SPLIT_K && g.split_at % BK16 != 0) return false;
-    if (g.split_dim == SPLIT_N && g.split_at % 128 != 0) return false;
-    if (g.A2 && (!aligned16(g.A2) || g.lda2 % 4 != 0)) return false;
-    return aligned16(g.C) && g.ldc % 4 == 0 && g.N % 4 == 0 && (g.bias == nullptr || aligned16(g.bias));
+    if (g.M <= 0 || g.N <= 0 || g.K <= 0) return false;
+    if (!g.Bh_hi || !g.Bh_lo || g.b_row_ptr) return false;
+    if (!aligned16(g.Bh_hi) || !aligned16(g.Bh_lo) || g.sbn % 8 != 0) return false;
+    if (!(aligned16(g.C) && g.ldc % 4 == 0 && g.N % 4 == 0 && (g.bias == nullptr || aligned16(g.bias)))) return false;
+    const int mode = f16_mode(g);
+    if (mode == F16_A_REGS) {
+        if (!g.b_scale || !g.A || g.sak != 1 || g.sbk != 1) return false;
+        if (!aligned16(g.A) || g.sam % 4 != 0 || g.K % 4 != 0) return false;
+        if (g.split_dim == SPLIT_M) return false;
+        if (g.split_dim == SPLIT_K && g.split_at % BK16 != 0) return false;
+        if (g.split_dim == SPLIT_N && g.split_at % 128 != 0) return false;
+        if (g.A2 && (!aligned16(g.A2) || g.lda2 % 4 != 0)) return false;
+        return true;
+    }
+    // plane modes: A is fp16 hi / lo planes with its scale on the device; no gathers, no second region
+    if (!g.Ah_hi || !g.Ah_lo || !g.a_scale || g.a_row_ptr || g.split_dim != SPLIT_NONE) return false;
+    if (!aligned16(g.Ah_hi) || !aligned16(g.Ah_lo) || g.lda_h % 8 != 0) return false;
+    if (mode == F16_TN_TMA) return g.M % 64 == 0 && g.N % 64 == 0;
+    return g.K % 8 == 0;
 }
 
 int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
     GGPM_REQUIRE(gemm_f16_eligible(g), "gemm_f16x3: operand layout not supported");
+    const int mode = f16_mode(g);
     F16Params fp;
     TcParams& p = fp.t;
     p.A = g.A; p.lda = g.sam; p.A2 = g.A2; p.lda2 = g.lda2;
@@ -990,7 +1079,7 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
     p.split_dim = g.split_dim; p.split_at = g.split_at;
     p.beta = g.beta; p.bias = g.bias; p.act = g.act; p.zero_row0 = g.zero_row0;
     fp.a_amax = g.a_amax; fp.a_amax_n = g.a_amax_n; fp.a_amax_const = g.a_amax_const; fp.a_deg = g.a_deg;
-    fp.b_scale = g.b_scale;
+    fp.a_scale = g.a_scale; fp.b_scale = g.b_scale; fp.b_scale_const = g.b_scale_const;
     const bool plain_epilogue = !g.bias && g.act == GGPM_ACT_NONE && !g.zero_row0 && (g.beta == 0.f || g.beta == 1.f);
     bool wide = g.N > 128;
     if (g.tile_n == 128) wide = false;
@@ -1018,13 +1107,29 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
         GGPM_CUDA(cudaMemset2DAsync(g.C + (size_t)m_first * g.ldc, sizeof(float) * (size_t)g.ldc, 0,
                                     sizeof(float) * (size_t)g.N, (size_t)(g.M - m_first), st));
     }
-    ProfScope prof(PROF_GEMM_TC, st, 2.0 * g.M * g.N * (double)g.K);
-    CUtensorMap tm_hi, tm_lo;
+    ProfScope prof(mode == F16_TN_TMA ? PROF_GEMM_WGRAD : PROF_GEMM_TC, st, 2.0 * g.M * g.N * (double)g.K);
+    CUtensorMap tm_hi, tm_lo, ta_hi, ta_lo;
+    memset(&ta_hi, 0, sizeof(ta_hi));
+    memset(&ta_lo, 0, sizeof(ta_lo));
+    dim3 grid(ctas, 1, 1);
+    if (mode == F16_TN_TMA) {
+        GGPM_TRY(make_plane_tmap16_tn(&tm_hi, g.Bh_hi, g.K, g.N, g.sbn, bnf / 64));
+        GGPM_TRY(make_plane_tmap16_tn(&tm_lo, g.Bh_lo, g.K, g.N, g.sbn, bnf / 64));
+        GGPM_TRY(make_plane_tmap16_tn(&ta_hi, g.Ah_hi, g.K, g.M, g.lda_h, BM / 64));
+        GGPM_TRY(make_plane_tmap16_tn(&ta_lo, g.Ah_lo, g.K, g.M, g.lda_h, BM / 64));
+        if (wide) return launch_f16_variant<256, F16_TN_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
+        return launch_f16_variant<128, F16_TN_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
+    }
     GGPM_TRY(make_plane_tmap16(&tm_hi, g.Bh_hi, g.N, g.K, g.sbn, bnf));
     GGPM_TRY(make_plane_tmap16(&tm_lo, g.Bh_lo, g.N, g.K, g.sbn, bnf));
-    dim3 grid(ctas, 1, 1);
-    if (wide) return launch_f16_variant<256>(fp, grid, tm_hi, tm_lo, st);
-    return launch_f16_variant<128>(fp, grid, tm_hi, tm_lo, st);
+    if (mode == F16_A_TMA) {
+        GGPM_TRY(make_plane_tmap16(&ta_hi, g.Ah_hi, g.M, g.K, g.lda_h, BM));
+        GGPM_TRY(make_plane_tmap16(&ta_lo, g.Ah_lo, g.M, g.K, g.lda_h, BM));
+        if (wide) return launch_f16_variant<256, F16_A_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
+        return launch_f16_variant<128, F16_A_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
+    }
+    if (wide) return launch_f16_variant<256, F16_A_REGS>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
+    return launch_f16_variant<128, F16_A_REGS>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
 }
 
 // ---- helpers of the f16x3 engine: max|w|, scaled fp16 hi / lo planes, max CSR row length ------------------

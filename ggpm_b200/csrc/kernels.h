@@ -36,6 +36,13 @@ struct GemmArgs {
     const float* b_scale = nullptr;
     const float* a_amax = nullptr; int a_amax_n = 0; float a_amax_const = 1.f;
     const int* a_deg = nullptr;
+    // A given as fp16 hi / lo planes (row stride lda_h halves) of A * (*a_scale), loaded by TMA:
+    //   f16_tn = 0: planes [M, K] (k-contiguous);  f16_tn = 1: planes [K, M] and B planes [K, N] (weight gradients:
+    //   both operands stored with the reduction index as the row)
+    const void* Ah_hi = nullptr; const void* Ah_lo = nullptr; long long lda_h = 0;
+    const float* a_scale = nullptr;
+    float b_scale_const = 1.f;   // used when b_scale is NULL
+    int f16_tn = 0;
 };
 
 int launch_gemm_simt(const GemmArgs& g, cudaStream_t st);
@@ -51,6 +58,10 @@ int launch_absmax(const float* w, long long n, float* amax, cudaStream_t st);
 int launch_f16_split(const float* w, long long n, const float* amax, void* hi, void* lo, float* scale, cudaStream_t st);
 int launch_f16_split_transpose(const float* w, int rows, int cols, const float* amax, void* hi, void* lo, float* scale,
                                cudaStream_t st);
+// Z = [gather^T(dA[:, :3Hp]) | dP] as fp16 hi / lo planes [E1, 4Hp] scaled by the power of two derived from
+// max(amax16[0..16)) * max(1, *deg); the scale is stored to *scale_out.  Z[n, :3Hp] = sum_{e in T(n)} dA[e, :3Hp].
+int launch_lstm_zgather(int E1, int Hp, const int* t_ptr, const int* t_row, const float* dA, const float* dP,
+                        const float* amax16, const int* deg, void* z_hi, void* z_lo, float* scale_out, cudaStream_t st);
 int launch_max_degree(const int* row_ptr, int rows, int* out, cudaStream_t st);   // *out = max(*out, max row length)
 // hi = rn_tf32(w), lo = rn_tf32(w - hi), element-wise over n floats (weights are split once per layer call)
 int launch_tf32_split(const float* w, long long n, float* hi, float* lo, cudaStream_t st);
@@ -61,7 +72,8 @@ struct XTabArgs {   // hoisted x-projection: X_g[e] = Yn[src[e], g] + T[k1[e], g
 };
 
 int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
-                         const float* gp, const float* c_prev, float* h_out, float* c_out, cudaStream_t st);
+                         const float* gp, const float* c_prev, float* h_out, float* c_out, void* h16_hi, void* h16_lo,
+                         cudaStream_t st);
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          const float* gp, const float* c_prev, const float* c_cur, const float* dH, const float* dC,
                          float* dA, float* dX, bool dx_overwrite, float* dP, float* dC_prev, float* amax16,

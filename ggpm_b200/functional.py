@@ -237,6 +237,15 @@ def gemm_f16x3(A, lda, planes, scal, C, M, N, K, beta=0.0, bias=None, act=ACT_NO
     return C
 
 
+def gemm_f16x3_planes(a_planes, a_scal, b_planes, b_scal, C, M, N, K, beta=0.0, tn=False):
+    """Raw entry (ggpm_gemm_f16x3_planes): both operands as prepared fp16 planes ([2, M, K] x [2, N, K], or with
+    tn=True [2, K, M] x [2, K, N] for C = A^T B)"""
+    call("ggpm_gemm_f16x3_planes", a_planes[0].data_ptr(), a_planes[1].data_ptr(), a_scal[1:].data_ptr(),
+         a_planes.stride(1), b_planes[0].data_ptr(), b_planes[1].data_ptr(), b_scal[1:].data_ptr(), b_planes.stride(1),
+         fptr(C), _row_stride(C), M, N, K, float(beta), int(tn), stream_ptr(C.device))
+    return C
+
+
 def tf32_split(W: torch.Tensor):
     """(hi, lo) tf32 planes of a contiguous fp32 weight matrix (ggpm_tf32_split)"""
     W = W.contiguous()
@@ -360,14 +369,17 @@ class LSTMMessages(torch.autograd.Function):
         hist_h, hist_c = _empty(slots, E1, Hp, device=dev), _empty(slots, E1, Hp, device=dev)
         hist_gp = _empty(slots, E1, 4 * Hp, device=dev)
         scratch = _empty(E1, Hp, device=dev)
-        w_split = _empty(2, 4 * Hp, Hp, device=dev)               # tf32 hi / lo planes of [Ug; Uf] for the TMA path
+        w_split = _empty(2, 4 * Hp, Hp, device=dev)               # weight planes (tf32 or fp16) + f16x3 engine scalars
+        # fp16 hi / lo planes of every h^t (f16x3 engine): the TMA-fed operand of the weight-gradient GEMM
+        hist_h16 = torch.empty(depth, 2, E1, Hp, dtype=torch.float16, device=dev) if keep else None
         T, Ug, Uf = T.contiguous(), Ug.contiguous(), Uf.contiguous()
         call("ggpm_lstm_fwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), fptr(Yn), iptr(mg.src), fptr(T),
              iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf), fptr(hist_h), fptr(hist_c),
-             fptr(hist_gp), fptr(scratch), fptr(w_split), int(keep), stream_ptr(dev))
+             fptr(hist_gp), fptr(scratch), fptr(w_split), None if hist_h16 is None else hist_h16.data_ptr(), int(keep),
+             stream_ptr(dev))
         last = (depth - 1) if keep else ((depth - 1) & 1)
         ctx.mg, ctx.depth, ctx.H, ctx.Hp = mg, depth, H, Hp
-        ctx.hist = (hist_h, hist_c, hist_gp, Yn) if keep else None
+        ctx.hist = (hist_h, hist_c, hist_gp, Yn, hist_h16) if keep else None
         ctx.save_for_backward(phi_x, Wx, T, Ug, Uf)
         h, c = hist_h[last], hist_c[last]
         ctx.mark_non_differentiable(c)
@@ -377,9 +389,10 @@ class LSTMMessages(torch.autograd.Function):
     def backward(ctx, dh, _dc):
         phi_x, Wx, T, Ug, Uf = ctx.saved_tensors
         mg, depth, H, Hp = ctx.mg, ctx.depth, ctx.H, ctx.Hp
-        hist_h, hist_c, hist_gp, Yn = ctx.hist
+        hist_h, hist_c, hist_gp, Yn, hist_h16 = ctx.hist
         E1, dev = mg.E1, Uf.device
         dH = dh.clone(memory_format=torch.contiguous_format)
+        z_planes = torch.empty(2, E1, 4 * Hp, dtype=torch.float16, device=dev)
         dX = _empty(E1, 4 * Hp, device=dev)
         dU4 = torch.zeros(4 * Hp, Hp, dtype=torch.float32, device=dev)     # [dUg; dUf] contiguous (single-launch wgrad)
         dUg, dUf = dU4[:3 * Hp], dU4[3 * Hp:]
@@ -390,7 +403,8 @@ class LSTMMessages(torch.autograd.Function):
         call("ggpm_lstm_bwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), iptr(bt.row_ptr), iptr(bt.col),
              fptr(Yn), iptr(mg.src), fptr(T), iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf),
              fptr(hist_h), fptr(hist_c), fptr(hist_gp), fptr(dH), fptr(dX), fptr(dUg), fptr(dUf), fptr(dA), fptr(dC),
-             fptr(dP), fptr(dS), fptr(S), fptr(dHn), fptr(_empty(2, Hp, 4 * Hp, device=dev)), stream_ptr(dev))
+             fptr(dP), fptr(dS), fptr(S), fptr(dHn), fptr(_empty(2, Hp, 4 * Hp, device=dev)), hist_h16.data_ptr(),
+             z_planes.data_ptr(), stream_ptr(dev))
         dphi, dWx, dT = _xproj_backward(ctx, dX, phi_x, Wx, T, mg)
         return dphi, dWx, dT, dUg, dUf, None, None, None
 

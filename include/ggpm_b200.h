@@ -125,6 +125,15 @@ int ggpm_gemm_f16x3(const float* A, long long lda, const void* B_hi, const void*
                     const float* A2, long long lda2, const float* a_amax, int a_amax_n, float a_amax_const,
                     const int32_t* a_deg, int tile_n, void* stream);
 
+/* Both operands as fp16 hi / lo planes (ggpm_f16_prepare_weights makes them for any matrix), all loads by TMA:
+ *   tn = 0: C[M,N] = beta C + A B^T with A planes [M, K] (row stride lda halves), B planes [N, K] (row stride ldb);
+ *   tn = 1: C[M,N] = beta C + A^T B with A planes [K, M], B planes [K, N]  (weight gradients: the reduction index is
+ *           the row of both operands; M, N multiples of 64).
+ * a_scale / b_scale: device floats holding the planes' scales.  beta is 0 or 1. */
+int ggpm_gemm_f16x3_planes(const void* A_hi, const void* A_lo, const float* a_scale, long long lda, const void* B_hi,
+                           const void* B_lo, const float* b_scale, long long ldb, float* C, int ldc, int M, int N, int K,
+                           float beta, int tn, void* stream);
+
 /* dZ = dY * act'(Y) with row 0 optionally zeroed (backward of the fused epilogue above). */
 int ggpm_act_bwd(const float* dY, int ld_dy, const float* Y, int ld_y, float* dZ, int ld_dz, int rows,
                  int width, int act, int zero_row0, void* stream);
@@ -153,7 +162,7 @@ int ggpm_table_wgrad(const float* dX, int ld_dx, int rows, int width, const int3
 int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                   const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
                   const float* Ug, const float* Uf, float* hist_h, float* hist_c, float* hist_gp,
-                  float* s_scratch, float* w_split, int keep_history, void* stream);
+                  float* s_scratch, float* w_split, void* hist_h16, int keep_history, void* stream);
 
 /* Back-propagation through time of the above (what autograd does for ggpm/rnn.py:96-108).
  * dH_final: [E1, Hp] gradient w.r.t. the final hidden state (consumed, used as scratch).
@@ -166,7 +175,13 @@ int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const 
                   const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
                   const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
                   float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
-                  float* w_split, void* stream);
+                  float* w_split, const void* hist_h16, void* z_planes, void* stream);
+
+/* f16x3 engine extras of the two calls above (all optional, NULL = not used):
+ *   hist_h16 [depth, 2, E1, Hp] fp16: hi / lo planes of h^t * 2^13 written by the forward cell kernel (keep_history)
+ *     and read by TMA as the B operand of the weight-gradient GEMM;
+ *   z_planes [2, E1, 4Hp] fp16: scratch for Z = [gather^T(dA) | dP] of one backward round (hi / lo planes);
+ *   w_split doubles as the engine's workspace: fp16 weight planes in its first half, device scalars behind them. */
 
 /* ---- graph GRU over a message graph ----------------------------------------------------------------
  * GRU.forward (ggpm/rnn.py:41-50) with the cell of ggpm/rnn.py:25-39.  x-gates packed [z | h | r] (3*Hp

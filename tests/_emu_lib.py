@@ -172,7 +172,7 @@ class EmuLib:
         return P.xproj(_tab(Yn, n1, G * Hp, G * Hp).to(DT), s, _tab(T, ntab, G * Hp, G * Hp).to(DT), a, b)
 
     def ggpm_lstm_fwd(self, E1, H, Hp, depth, b_ptr, b_col, Yn, src, T, k1, k2, Ug, Uf, hist_h, hist_c, hist_gp,
-                      s_scratch, w_split, keep, stream):
+                      s_scratch, w_split, hist_h16, keep, stream):
         self._tick("lstm_fwd")
         assert Hp % 32 == 0 and Hp >= H
         rp, col = _csr(b_ptr, b_col, E1)
@@ -197,7 +197,7 @@ class EmuLib:
         return 0
 
     def ggpm_lstm_bwd(self, E1, H, Hp, depth, b_ptr, b_col, bt_ptr, bt_row, Yn, src, T, k1, k2, Ug, Uf, hist_h,
-                      hist_c, hist_gp, dH_final, dX, dUg, dUf, dA, dC, dP, dS, S, dHn, w_split, stream):
+                      hist_c, hist_gp, dH_final, dX, dUg, dUf, dA, dC, dP, dS, S, dHn, w_split, hist_h16, z_planes, stream):
         self._tick("lstm_bwd")
         rp, col = _csr(b_ptr, b_col, E1)
         trp, tcol = _csr(bt_ptr, bt_row, E1)

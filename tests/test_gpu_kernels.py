@@ -303,6 +303,34 @@ def test_f16x3_fused_state_gradient(E, Hp, gscale):
     assert rel(out, ref) <= 2e-6, rel(out, ref)
 
 
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (300, 256, 256), (5000, 256, 1024), (1000, 512, 200)])
+def test_f16x3_planes_nt(M, N, K):
+    """all operands by TMA, k-contiguous planes (the state-gradient GEMM dH = Z [Ug; Uf])"""
+    torch.manual_seed(M)
+    A = torch.randn(M, K, device=DEV) * 3e-3
+    W = torch.randn(N, K, device=DEV) * 0.07
+    pa, sa = Fn.f16_prepare_weights(A)
+    pb, sb = Fn.f16_prepare_weights(W)
+    out = torch.full((M, N), 3.0, device=DEV)
+    Fn.gemm_f16x3_planes(pa, sa, pb, sb, out, M, N, K)
+    assert rel(out, A.double() @ W.double().t()) <= 2e-6
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1024, 256, 300), (1024, 256, 19001), (2048, 512, 5000), (512, 128, 777),
+                                   (768, 192, 1000)])
+def test_f16x3_planes_tn_weight_gradient(M, N, K):
+    """C += A^T B with the reduction index as the row of both operands (MN-major tiles by 3-D TMA boxes)"""
+    torch.manual_seed(K)
+    A = torch.randn(K, M, device=DEV) * 2.0
+    B = torch.rand(K, N, device=DEV) * 2 - 1
+    pa, sa = Fn.f16_prepare_weights(A)
+    pb, sb = Fn.f16_prepare_weights(B)
+    out = torch.ones(M, N, device=DEV)
+    Fn.gemm_f16x3_planes(pa, sa, pb, sb, out, M, N, K, beta=1.0, tn=True)
+    ref = A.double().t() @ B.double() + 1.0
+    assert rel(out, ref) <= 2e-6, rel(out, ref)
+
+
 def test_linear_act_autograd(engine):
     g = torch.Generator().manual_seed(9)
     A1 = torch.randn(400, 38, generator=g, dtype=torch.float64, requires_grad=True)
