@@ -38,11 +38,16 @@ SIGNATURES = {
     "ggpm_f16_prepare_weights": (I, [P, I, I, I, P, P, P, P]),
     "ggpm_gemm_f16x3": (I, [P, c_longlong, P, P, P, c_longlong, P, I, I, I, I, c_float, P, I, I, P, P, I, I, P, c_longlong,
                             P, I, c_float, P, I, P]),
+    "ggpm_lstm_pack": (I, [P, P, I, I, I, I, I, I, I, P, P, P, P]),
+    "ggpm_lstm_unpack": (I, [P, P, I, I, I, I, I, I, P, P, P, P]),
+    "ggpm_split_pad": (I, [P, I, I, I, I, I, P, P, P, P, P, P, P]),
+    "ggpm_split_unpad": (I, [P, I, I, I, P, P, P, P, P, P, P]),
     "ggpm_act_bwd": (I, [P, I, P, I, P, I, I, I, I, I, P]),
     "ggpm_colsum": (I, [P, I, I, I, P, I, P]),
     "ggpm_table_wgrad": (I, [P, I, I, I, P, P, P, I, I, P]),
-    "ggpm_lstm_fwd": (I, [I, I, I, I, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, P]),
-    "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 28),
+    "ggpm_lstm_plan": (I, [I, I]),
+    "ggpm_lstm_fwd": (I, [I, I, I, I, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, P]),
+    "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 27 + [I, P]),
     "ggpm_gru_fwd": (I, [I, I, I, I] + [P] * 13 + [I, P]),
     "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
 }

@@ -257,10 +257,21 @@ static int check_dims(const char* who, int E1, int H, int Hp, int depth) {
     return 0;
 }
 
+// which optional buffers the LSTM layer calls will use under the current engine (so the caller can size them):
+// bit 0: f16x3 engine for the gate / state-gradient GEMMs; bit 1: fp16 h planes + Z planes (TMA-fed backward GEMMs),
+// in which case hist_h may be a 2-slot rotating buffer (h_rotate = 1)
+extern "C" int ggpm_lstm_plan(int Hp, int depth) {
+    const int e = gemm_engine();
+    if (e == GGPM_ENGINE_SIMT_FP32 || Hp % 128 != 0 || depth <= 1) return 0;
+    if (!f16_engine_on() || !f16_scalars_fit(Hp, depth)) return 0;
+    return 3;
+}
+
 extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                              const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
                              const float* Ug, const float* Uf, float* hist_h, float* hist_c, float* hist_gp,
-                             float* s_scratch, float* w_split, void* hist_h16, int keep_history, void* stream) {
+                             float* s_scratch, float* w_split, void* hist_h16, int keep_history, int h_rotate,
+                             void* stream) {
     GGPM_TRY(check_dims("lstm_fwd", E1, H, Hp, depth));
     GGPM_REQUIRE(b_ptr && b_col && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp && s_scratch,
                  "lstm_fwd: null pointer");
@@ -284,10 +295,11 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
         GGPM_TRY(launch_tf32_split(Ug, (long long)wn, w_split, w_split + wn, st));
     }
     const bool h16 = f16 && keep_history && hist_h16 != nullptr && ((uintptr_t)hist_h16 & 15) == 0;
+    GGPM_REQUIRE(!h_rotate || !keep_history || h16, "lstm_fwd: a rotating hist_h needs the fp16 h planes (ggpm_lstm_plan bit 1)");
     for (int t = 1; t <= depth; ++t) {
         const int cur = keep_history ? (t - 1) : ((t - 1) & 1);
         const int prev = keep_history ? (t - 2) : ((t - 2) & 1);
-        float* h_cur = hist_h + cur * row;
+        float* h_cur = hist_h + (h_rotate ? (cur & 1) : cur) * row;
         float* c_cur = hist_c + cur * row;
         float* gp = hist_gp + (size_t)cur * 4 * row;
         // fp16 planes of h^t (2 bytes per element): [cur][hi | lo][E1 * Hp]
@@ -297,7 +309,7 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
             GGPM_TRY(launch_lstm_cell_fwd(true, E1, H, Hp, b_ptr, b_col, x, nullptr, nullptr, h_cur, c_cur, h16_hi, h16_lo, st));
             continue;
         }
-        const float* h_prev = hist_h + prev * row;
+        const float* h_prev = hist_h + (h_rotate ? (prev & 1) : prev) * row;
         const float* c_prev = hist_c + prev * row;
         // S = sum of neighbour states; [G_i|G_o|G_u] = S Ug^T ; P = h_prev Uf^T
         if (tc_ok) {
@@ -335,7 +347,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
                              const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
                              const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
                              float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
-                             float* w_split, const void* hist_h16, void* z_planes, void* stream) {
+                             float* w_split, const void* hist_h16, void* z_planes, int h_rotate, void* stream) {
     GGPM_TRY(check_dims("lstm_bwd", E1, H, Hp, depth));
     GGPM_REQUIRE(b_ptr && b_col && bt_ptr && bt_row && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp &&
                      dH_final && dX && dUg && dUf && dA && dC && dP && dS && S && dHn,
@@ -364,6 +376,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     // fully TMA-fed backward GEMMs: Z planes (written by the zgather kernel) and the h planes saved by the forward
     const bool zmode = f16 && hist_h16 != nullptr && z_planes != nullptr && Hp % 64 == 0 &&
                        (((uintptr_t)hist_h16 | (uintptr_t)z_planes) & 15) == 0;
+    GGPM_REQUIRE(zmode || !h_rotate, "lstm_bwd: the forward kept only a rotating hist_h, which needs the fp16-plane path");
     char* z_hi = (char*)z_planes;
     char* z_lo = z_hi + (size_t)8 * row;                  // 4 * row halves
     for (int t = depth; t >= 1; --t) {
@@ -375,7 +388,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
                                           overwrite, nullptr, nullptr, nullptr, st));
             break;
         }
-        const float* h_prev = hist_h + (size_t)(t - 2) * row;
+        const float* h_prev = h_rotate ? nullptr : hist_h + (size_t)(t - 2) * row;     // only read without the plane path
         const float* c_prev = hist_c + (size_t)(t - 2) * row;
         float* dC_prev = dC + (size_t)(t & 1) * row;
         GGPM_CUDA(cudaMemsetAsync(dP, 0, sizeof(float) * row, st));

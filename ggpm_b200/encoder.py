@@ -61,8 +61,8 @@ class MPNEncoder(nn.Module):
         h = out[0] if isinstance(out, tuple) else out
         incoming = Fn.gather_sum(h, a_csr)                                    # ggpm/encoder.py:31-32
         w = self.W_o[0].weight
-        node = Fn.linear_act_padded([phi_n, incoming], [w[:, :F], w[:, F:]], self.W_o[0].bias,
-                                    act=ACT_RELU, zero_row0=True)             # :33-38 (mask commutes with dropout)
+        node = Fn.linear_act_split([phi_n, incoming], w, [F, H], self.W_o[0].bias,
+                                   act=ACT_RELU, zero_row0=True)              # :33-38 (mask commutes with dropout)
         node = self.W_o[2](node)
         return node, h, incoming
 
@@ -79,8 +79,7 @@ class MPNEncoder(nn.Module):
         h = out[0] if isinstance(out, tuple) else out
         incoming = Fn.gather_sum(h, a_csr)
         w = self.W_o[0].weight
-        node = Fn.linear_act_padded([fnode, incoming], [w[:, :F], w[:, F:]], self.W_o[0].bias,
-                                    act=ACT_RELU, zero_row0=True)
+        node = Fn.linear_act_split([fnode, incoming], w, [F, H], self.W_o[0].bias, act=ACT_RELU, zero_row0=True)
         return self.W_o[2](_public(node, H)), _public(h, H)
 
 
@@ -103,7 +102,7 @@ def _root_vectors(W_root, feat, incoming, roots, H):
     w = W_root[0].weight
     f = feat.index_select(0, roots)
     m = incoming.index_select(0, roots)
-    return _public(Fn.linear_act_padded([f, m], [w[:, :H], w[:, H:]], W_root[0].bias, act=ACT_TANH), H)
+    return _public(Fn.linear_act_split([f, m], w, [H, H], W_root[0].bias, act=ACT_TANH), H)
 
 
 class HierMPNEncoder(nn.Module):
@@ -155,8 +154,8 @@ class HierMPNEncoder(nn.Module):
         atoms_of_motif = Fn.gather_sum(hatom, Fn.csr_from_padded(tb.cgraph, n_atoms))
         wi = self.W_i[0].weight
         E = attach_emb.shape[1]
-        inter_feat = Fn.linear_act_padded([attach_emb, atoms_of_motif], [wi[:, :E], wi[:, E:]], self.W_i[0].bias,
-                                          act=ACT_RELU)
+        inter_feat = Fn.linear_act_split([attach_emb, atoms_of_motif], wi, [E, wi.shape[1] - E], self.W_i[0].bias,
+                                         act=ACT_RELU)
         inter_feat = self.W_i[2](inter_feat)
         hinter, _, _ = self.inter_encoder.encode(inter_feat, inter_feat, tb.mg, tb.a, H, MAX_POS)
 
@@ -164,8 +163,8 @@ class HierMPNEncoder(nn.Module):
         motif_emb = self.E_c(tb.fnode[:, 0])
         wc = self.W_c[0].weight
         E = motif_emb.shape[1]
-        tree_feat = Fn.linear_act_padded([motif_emb, hinter], [wc[:, :E], wc[:, E:]], self.W_c[0].bias,
-                                         act=ACT_RELU)
+        tree_feat = Fn.linear_act_split([motif_emb, hinter], wc, [E, wc.shape[1] - E], self.W_c[0].bias,
+                                        act=ACT_RELU)
         tree_feat = self.W_c[2](tree_feat)
         hnode, _, incoming = self.tree_encoder.encode(tree_feat, tree_feat, tb.mg, tb.a, H, MAX_POS)
 

@@ -299,6 +299,69 @@ def linear_act(As: Sequence[torch.Tensor], Ws: Sequence[torch.Tensor], bias, act
     return LinearAct.apply(bias, act, zero_row0, out_width, *As, *Ws)
 
 
+class SplitPad(torch.autograd.Function):
+    """W [N, K], bias [N] -> column blocks of W zero-padded to [Np, kp_i] and bias_p [Np], one launch each way
+    (ggpm_split_pad / ggpm_split_unpad)."""
+
+    @staticmethod
+    def forward(ctx, W, bias, Np, cols, kps):
+        import ctypes
+        W = W.contiguous()
+        N, K = W.shape
+        dev = W.device
+        outs = [torch.empty(Np, kp, dtype=torch.float32, device=dev) for kp in kps]
+        bias_p = None if bias is None else torch.empty(Np, dtype=torch.float32, device=dev)
+        n = len(kps)
+        IA = ctypes.c_int * n
+        ctx.meta = (N, K, Np, n, [c[0] for c in cols], [c[1] for c in cols], list(kps), bias is not None)
+        call("ggpm_split_pad", fptr(W), K, N, K, Np, n, IA(*[c[0] for c in cols]), IA(*[c[1] for c in cols]), IA(*kps),
+             (ctypes.c_void_p * n)(*[o.data_ptr() for o in outs]), None if bias is None else fptr(bias.contiguous()),
+             None if bias_p is None else fptr(bias_p), stream_ptr(dev))
+        if bias_p is None:
+            bias_p = torch.zeros(0, device=dev)
+            ctx.mark_non_differentiable(bias_p)
+        return (bias_p, *outs)
+
+    @staticmethod
+    def backward(ctx, dbias_p, *douts):
+        import ctypes
+        N, K, Np, n, c0, c1, kps, has_bias = ctx.meta
+        dev = next(d for d in (dbias_p,) + douts if d is not None).device
+        dW = torch.empty(N, K, dtype=torch.float32, device=dev)
+        dbias = torch.empty(N, dtype=torch.float32, device=dev) if has_bias else None
+        douts = [None if d is None else d.contiguous() for d in douts]
+        IA = ctypes.c_int * n
+        call("ggpm_split_unpad", fptr(dW), N, K, n, IA(*c0), IA(*c1), IA(*kps),
+             (ctypes.c_void_p * n)(*[None if d is None else d.data_ptr() for d in douts]),
+             None if (dbias_p is None or not has_bias) else fptr(dbias_p.contiguous()), None if dbias is None else fptr(dbias),
+             stream_ptr(dev))
+        return dW, dbias, None, None, None
+
+
+def linear_act_split(As: Sequence[torch.Tensor], W: torch.Tensor, widths: Sequence[int], bias, act=ACT_NONE,
+                     zero_row0=False):
+    """act([A_0[:, :k_0] | A_1[:, :k_1] | ...] @ W^T + b) without building the concatenation: W [N, sum k_i] is cut into
+    its column blocks and zero-padded (rows to Np = N rounded up to 32, each block to a multiple of 4 columns) by ONE
+    kernel; A_i is read in place at the padded width (its extra columns meet zero weights).  Returns [M, Np]."""
+    import torch.nn.functional as F_
+    N = W.shape[0]
+    Np = round_up(N, 32)
+    cols, kps, As_p, c = [], [], [], 0
+    for A, k in zip(As, widths):
+        kp = round_up(k, 4)
+        cols.append((c, c + k))
+        kps.append(kp)
+        c += k
+        A = A[:, :kp] if A.shape[1] >= kp else F_.pad(A[:, :k], (0, kp - k))
+        if A.stride(1) != 1 or _row_stride(A) % 4 != 0 or A.data_ptr() % 16 != 0:
+            A = A.contiguous()
+        As_p.append(A)
+    if c != W.shape[1]:
+        raise ValueError("linear_act_split: widths sum to %d, weight has %d columns" % (c, W.shape[1]))
+    bias_p, *Ws_p = SplitPad.apply(W, bias, Np, cols, kps)
+    return LinearAct.apply(bias_p if bias is not None else None, act, zero_row0, None, *As_p, *Ws_p)
+
+
 def linear_act_padded(As: Sequence[torch.Tensor], Ws: Sequence[torch.Tensor], bias, act=ACT_NONE, zero_row0=False):
     """linear_act with every operand brought to tensor-core friendly shapes: each weight piece W_i [N, K_i] is
     zero-padded to [Np, Kp_i] (Np = N rounded up to 32, Kp_i = K_i rounded up to 4) and A_i is used at width Kp_i
@@ -356,43 +419,52 @@ def _empty(*shape, device):
 
 class LSTMMessages(torch.autograd.Function):
     """`depth` rounds of the graph LSTM (ggpm/rnn.py:85-108) over a message graph.
-    phi_x [N1, F]: node features feeding the message inputs; Wx [4Hp, F], T [ntab, 4Hp], Ug [3Hp, Hp],
-    Uf [Hp, Hp]: packed gate weights (ggpm_b200.packing).  Returns (h, c): [E1, Hp] final states."""
+    phi_x [N1, F]: node features feeding the message inputs; Wx [4Hp, F], T [ntab, 4Hp], U4 = [Ug; Uf] [4Hp, Hp]:
+    packed gate weights (ggpm_b200.packing).  Returns (h, c): [E1, Hp] final states."""
 
     @staticmethod
-    def forward(ctx, phi_x, Wx, T, Ug, Uf, mg: MessageGraph, depth: int, H: int):
-        Hp = Uf.shape[0]
+    def forward(ctx, phi_x, Wx, T, U4, mg: MessageGraph, depth: int, H: int):
+        Hp = U4.shape[1]
+        U4 = U4.contiguous()
+        Ug, Uf = U4[:3 * Hp], U4[3 * Hp:]
         E1, dev = mg.E1, Uf.device
         keep = any(ctx.needs_input_grad)
         Yn = gemm_nt(phi_x, Wx)                                    # [N1, 4Hp]
         slots = depth if keep else min(depth, 2)
-        hist_h, hist_c = _empty(slots, E1, Hp, device=dev), _empty(slots, E1, Hp, device=dev)
+        # with the fp16-plane path the backward reads h only through hist_h16: fp32 h needs two rotating slots
+        planes = keep and (_lib.backend().ggpm_lstm_plan(Hp, depth) & 2) != 0
+        rotate = planes and depth > 2
+        hist_h = _empty(2 if rotate else slots, E1, Hp, device=dev)
+        hist_c = _empty(slots, E1, Hp, device=dev)
         hist_gp = _empty(slots, E1, 4 * Hp, device=dev)
         scratch = _empty(E1, Hp, device=dev)
         w_split = _empty(2, 4 * Hp, Hp, device=dev)               # weight planes (tf32 or fp16) + f16x3 engine scalars
         # fp16 hi / lo planes of every h^t (f16x3 engine): the TMA-fed operand of the weight-gradient GEMM
-        hist_h16 = torch.empty(depth, 2, E1, Hp, dtype=torch.float16, device=dev) if keep else None
-        T, Ug, Uf = T.contiguous(), Ug.contiguous(), Uf.contiguous()
+        hist_h16 = torch.empty(depth, 2, E1, Hp, dtype=torch.float16, device=dev) if planes else None
+        T = T.contiguous()
         call("ggpm_lstm_fwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), fptr(Yn), iptr(mg.src), fptr(T),
              iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf), fptr(hist_h), fptr(hist_c),
              fptr(hist_gp), fptr(scratch), fptr(w_split), None if hist_h16 is None else hist_h16.data_ptr(), int(keep),
-             stream_ptr(dev))
+             int(rotate), stream_ptr(dev))
         last = (depth - 1) if keep else ((depth - 1) & 1)
+        h_last = ((depth - 1) & 1) if rotate else last
+        ctx.rotate = rotate
         ctx.mg, ctx.depth, ctx.H, ctx.Hp = mg, depth, H, Hp
         ctx.hist = (hist_h, hist_c, hist_gp, Yn, hist_h16) if keep else None
-        ctx.save_for_backward(phi_x, Wx, T, Ug, Uf)
-        h, c = hist_h[last], hist_c[last]
+        ctx.save_for_backward(phi_x, Wx, T, U4)
+        h, c = hist_h[h_last], hist_c[last]
         ctx.mark_non_differentiable(c)
         return h, c
 
     @staticmethod
     def backward(ctx, dh, _dc):
-        phi_x, Wx, T, Ug, Uf = ctx.saved_tensors
+        phi_x, Wx, T, U4 = ctx.saved_tensors
         mg, depth, H, Hp = ctx.mg, ctx.depth, ctx.H, ctx.Hp
+        Ug, Uf = U4[:3 * Hp], U4[3 * Hp:]
         hist_h, hist_c, hist_gp, Yn, hist_h16 = ctx.hist
         E1, dev = mg.E1, Uf.device
         dH = dh.clone(memory_format=torch.contiguous_format)
-        z_planes = torch.empty(2, E1, 4 * Hp, dtype=torch.float16, device=dev)
+        z_planes = None if hist_h16 is None else torch.empty(2, E1, 4 * Hp, dtype=torch.float16, device=dev)
         dX = _empty(E1, 4 * Hp, device=dev)
         dU4 = torch.zeros(4 * Hp, Hp, dtype=torch.float32, device=dev)     # [dUg; dUf] contiguous (single-launch wgrad)
         dUg, dUf = dU4[:3 * Hp], dU4[3 * Hp:]
@@ -403,10 +475,11 @@ class LSTMMessages(torch.autograd.Function):
         call("ggpm_lstm_bwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), iptr(bt.row_ptr), iptr(bt.col),
              fptr(Yn), iptr(mg.src), fptr(T), iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf),
              fptr(hist_h), fptr(hist_c), fptr(hist_gp), fptr(dH), fptr(dX), fptr(dUg), fptr(dUf), fptr(dA), fptr(dC),
-             fptr(dP), fptr(dS), fptr(S), fptr(dHn), fptr(_empty(2, Hp, 4 * Hp, device=dev)), hist_h16.data_ptr(),
-             z_planes.data_ptr(), stream_ptr(dev))
+             fptr(dP), fptr(dS), fptr(S), fptr(dHn), fptr(_empty(2, Hp, 4 * Hp, device=dev)),
+             None if hist_h16 is None else hist_h16.data_ptr(), None if z_planes is None else z_planes.data_ptr(),
+             int(ctx.rotate), stream_ptr(dev))
         dphi, dWx, dT = _xproj_backward(ctx, dX, phi_x, Wx, T, mg)
-        return dphi, dWx, dT, dUg, dUf, None, None, None
+        return dphi, dWx, dT, dU4, None, None, None
 
 
 def _xproj_backward(ctx, dX, phi_x, Wx, T, mg: MessageGraph):

@@ -61,7 +61,64 @@ def _pad_square(u, H, Hp):
     return F_.pad(u, (0, Hp - H, 0, Hp - H))
 
 
+def _ptr_array(tensors):
+    import ctypes
+    return (ctypes.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+
+
+class PackLSTM(torch.autograd.Function):
+    """(W_i, b_i, W_o, b_o, W, b, W_f, b_f) -> (Wx [4Hp, Fp], T [ntab, 4Hp], U4 [4Hp, Hp]) in ONE launch
+    (ggpm_lstm_pack); backward is one launch too (ggpm_lstm_unpack).  Same result as the torch reshuffling of
+    _pack_common (kept for the GRU), without its ~30 tiny kernels and autograd nodes per layer and step."""
+
+    @staticmethod
+    def forward(ctx, F, IN, H, Hp, n_bias_rows, *wb):
+        from ._lib import call, fptr, stream_ptr
+        ws = [w.contiguous() for w in wb[0::2]]
+        bs = [b.contiguous() for b in wb[1::2]]
+        dev = ws[0].device
+        Fp = feature_width(F)
+        ntab = IN - F if IN > F else 1
+        Wx = torch.empty(4 * Hp, Fp, dtype=torch.float32, device=dev)
+        T = torch.empty(ntab, 4 * Hp, dtype=torch.float32, device=dev)
+        U4 = torch.empty(4 * Hp, Hp, dtype=torch.float32, device=dev)
+        for t in ws + bs:
+            fptr(t, "gate parameter")
+        call("ggpm_lstm_pack", _ptr_array(ws), _ptr_array(bs), H, Hp, F, Fp, IN, ntab, n_bias_rows, fptr(Wx), fptr(T),
+             fptr(U4), stream_ptr(dev))
+        ctx.dims = (F, IN, H, Hp, n_bias_rows, Fp)
+        ctx.dev = dev
+        return Wx, T, U4
+
+    @staticmethod
+    def backward(ctx, dWx, dT, dU4):
+        from ._lib import call, fptr, stream_ptr
+        F, IN, H, Hp, n_bias_rows, Fp = ctx.dims
+        dev = ctx.dev
+        dws = [torch.empty(H, IN + H, dtype=torch.float32, device=dev) for _ in range(4)]
+        dbs = [torch.empty(H, dtype=torch.float32, device=dev) for _ in range(4)]
+        g = [None if t is None else t.contiguous() for t in (dWx, dT, dU4)]
+        call("ggpm_lstm_unpack", _ptr_array(dws), _ptr_array(dbs), H, Hp, F, Fp, IN, n_bias_rows,
+             *[None if t is None else fptr(t) for t in g], stream_ptr(dev))
+        out = [None] * 5
+        for w, b in zip(dws, dbs):
+            out += [w, b]
+        return tuple(out)
+
+
 def pack_lstm(rnn, F: int, Hp: int, n_bias_rows: int):
+    """rnn: module with W_i, W_o, W_f, W = Sequential(Linear(IN+H -> H), act).  Gate order [i | o | u | f].
+    Returns (Wx, T, U4) with U4 = [U_i; U_o; U_u; U_f] in one [4Hp, Hp] buffer, which lets the library run the gate
+    and forget projections (and their gradients) as single tensor-core launches."""
+    H, IN = rnn.hidden_size, rnn.input_size
+    lin = [rnn.W_i[0], rnn.W_o[0], rnn.W[0], rnn.W_f[0]]
+    wb = []
+    for l in lin:
+        wb += [l.weight, l.bias]
+    return PackLSTM.apply(F, IN, H, Hp, n_bias_rows, *wb)
+
+
+def pack_lstm_torch(rnn, F: int, Hp: int, n_bias_rows: int):
     """rnn: module with W_i, W_o, W_f, W = Sequential(Linear(IN+H -> H), act).  Gate order [i | o | u | f]."""
     H, IN = rnn.hidden_size, rnn.input_size
     lin = [rnn.W_i[0], rnn.W_o[0], rnn.W[0], rnn.W_f[0]]

@@ -90,8 +90,8 @@ class LSTM(_GraphRNN):
 
     def messages(self, phi_x, mg: Fn.MessageGraph, n_feat: int, n_bias_rows: int):
         Hp = self.padded_hidden
-        Wx, T, Ug, Uf = packing.pack_lstm(self, n_feat, Hp, n_bias_rows)
-        return Fn.LSTMMessages.apply(packing.feature_columns(phi_x, n_feat), Wx, T, Ug, Uf, mg, self.depth,
+        Wx, T, U4 = packing.pack_lstm(self, n_feat, Hp, n_bias_rows)
+        return Fn.LSTMMessages.apply(packing.feature_columns(phi_x, n_feat), Wx, T, U4, mg, self.depth,
                                      self.hidden_size)
 
     def forward(self, fmess, bgraph):

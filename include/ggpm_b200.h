@@ -134,6 +134,24 @@ int ggpm_gemm_f16x3_planes(const void* A_hi, const void* A_lo, const float* a_sc
                            const void* B_lo, const float* b_scale, long long ldb, float* C, int ldc, int M, int N, int K,
                            float beta, int tn, void* stream);
 
+/* ---- weight packing (one launch each way; the reference layout is nn.Linear(IN + H -> H) per gate on [x | h],
+ * ggpm/rnn.py:69-72, with x = [node feature (F) | one-hot columns (IN - F)], ggpm/encoder.py:103-106,114-116,121-125)
+ * W4 / b4: host arrays of 4 device pointers, gate order i, o, u (rnn.W), f: weights [H, IN + H] row-major, biases [H].
+ * Outputs (zero padded): Wx [4Hp, Fp] node-feature columns; T [ntab, 4Hp] one-hot columns as lookup rows, rows
+ * [0, n_bias_rows) also carry the bias (ntab = IN - F, or 1 when IN == F); U4 = [U_i; U_o; U_u; U_f] [4Hp, Hp]. */
+int ggpm_lstm_pack(const float* const* W4, const float* const* b4, int H, int Hp, int F, int Fp, int IN, int ntab,
+                   int n_bias_rows, float* Wx, float* T, float* U4, void* stream);
+/* gradients of (Wx, T, U4) (each may be NULL = zero) back to the four [H, IN + H] weights and [H] biases (overwritten) */
+int ggpm_lstm_unpack(float* const* dW4, float* const* db4, int H, int Hp, int F, int Fp, int IN, int n_bias_rows,
+                     const float* dWx, const float* dT, const float* dU4, void* stream);
+/* W [N, K] (row stride ldw) -> n_pieces (<= 4) column blocks [c0[i], c1[i]) zero padded to out[i] [Np, kp[i]], and
+ * bias [N] -> bias_p [Np] (both optional): the operands of the cat-free Linear layers (ggpm/encoder.py:33-34,101,112,138)
+ * at tensor-core friendly shapes.  c0 / c1 / kp / out are host arrays.  split_unpad is the gradient (dW contiguous). */
+int ggpm_split_pad(const float* W, int ldw, int N, int K, int Np, int n_pieces, const int* c0, const int* c1,
+                   const int* kp, float* const* out, const float* bias, float* bias_p, void* stream);
+int ggpm_split_unpad(float* dW, int N, int K, int n_pieces, const int* c0, const int* c1, const int* kp,
+                     float* const* dpieces, const float* dbias_p, float* dbias, void* stream);
+
 /* dZ = dY * act'(Y) with row 0 optionally zeroed (backward of the fused epilogue above). */
 int ggpm_act_bwd(const float* dY, int ld_dy, const float* Y, int ld_y, float* dZ, int ld_dz, int rows,
                  int width, int act, int zero_row0, void* stream);
@@ -162,7 +180,7 @@ int ggpm_table_wgrad(const float* dX, int ld_dx, int rows, int width, const int3
 int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                   const float* Yn, const int32_t* src, const float* T, const int32_t* k1, const int32_t* k2,
                   const float* Ug, const float* Uf, float* hist_h, float* hist_c, float* hist_gp,
-                  float* s_scratch, float* w_split, void* hist_h16, int keep_history, void* stream);
+                  float* s_scratch, float* w_split, void* hist_h16, int keep_history, int h_rotate, void* stream);
 
 /* Back-propagation through time of the above (what autograd does for ggpm/rnn.py:96-108).
  * dH_final: [E1, Hp] gradient w.r.t. the final hidden state (consumed, used as scratch).
@@ -175,12 +193,18 @@ int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const 
                   const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
                   const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
                   float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
-                  float* w_split, const void* hist_h16, void* z_planes, void* stream);
+                  float* w_split, const void* hist_h16, void* z_planes, int h_rotate, void* stream);
+
+/* Which optional buffers the two calls above will use under the current engine, so the caller can size them:
+ * bit 0: f16x3 gate GEMMs; bit 1: fp16 h planes + Z planes (then hist_h may be 2 rotating slots: h_rotate = 1). */
+int ggpm_lstm_plan(int Hp, int depth);
 
 /* f16x3 engine extras of the two calls above (all optional, NULL = not used):
  *   hist_h16 [depth, 2, E1, Hp] fp16: hi / lo planes of h^t * 2^13 written by the forward cell kernel (keep_history)
  *     and read by TMA as the B operand of the weight-gradient GEMM;
  *   z_planes [2, E1, 4Hp] fp16: scratch for Z = [gather^T(dA) | dP] of one backward round (hi / lo planes);
+ *   h_rotate: hist_h holds only 2 rotating slots (slot (t - 1) & 1 for h^t) although keep_history is set: the backward
+ *     then reads h only through hist_h16 (requires ggpm_lstm_plan bit 1);
  *   w_split doubles as the engine's workspace: fp16 weight planes in its first half, device scalars behind them. */
 
 /* ---- graph GRU over a message graph ----------------------------------------------------------------

@@ -129,6 +129,71 @@ class EmuLib:
         c.copy_(r.float())
         return 0
 
+    # -- weight packing ----------------------------------------------------------------------------
+    @staticmethod
+    def _ptrs(arr, n):
+        return [int(arr[i]) if arr[i] else 0 for i in range(n)]
+
+    def ggpm_lstm_pack(self, W4, b4, H, Hp, F, Fp, IN, ntab, nbr, Wx, T, U4, stream):
+        self._tick("lstm_pack")
+        ws = [_tab(p, H, IN + H, IN + H) for p in self._ptrs(W4, 4)]
+        bs = [_f(p, H) for p in self._ptrs(b4, 4)]
+        wx, t, u = _tab(Wx, 4 * Hp, Fp, Fp), _tab(T, ntab, 4 * Hp, 4 * Hp), _tab(U4, 4 * Hp, Hp, Hp)
+        wx.zero_(); t.zero_(); u.zero_()
+        for g in range(4):
+            wx[g * Hp:g * Hp + H, :F] = ws[g][:, :F]
+            u[g * Hp:g * Hp + H, :H] = ws[g][:, IN:]
+            if IN > F:
+                t[:, g * Hp:g * Hp + H] = ws[g][:, F:IN].t()
+            t[:nbr, g * Hp:g * Hp + H] += bs[g]
+        return 0
+
+    def ggpm_lstm_unpack(self, dW4, db4, H, Hp, F, Fp, IN, nbr, dWx, dT, dU4, stream):
+        self._tick("lstm_unpack")
+        ntab = IN - F if IN > F else 1
+        ws = [_tab(p, H, IN + H, IN + H) for p in self._ptrs(dW4, 4)]
+        bs = [_f(p, H) for p in self._ptrs(db4, 4)]
+        for g in range(4):
+            ws[g].zero_(); bs[g].zero_()
+            if dWx:
+                ws[g][:, :F] = _tab(dWx, 4 * Hp, Fp, Fp)[g * Hp:g * Hp + H, :F]
+            if dU4:
+                ws[g][:, IN:] = _tab(dU4, 4 * Hp, Hp, Hp)[g * Hp:g * Hp + H, :H]
+            if dT:
+                t = _tab(dT, ntab, 4 * Hp, 4 * Hp)
+                if IN > F:
+                    ws[g][:, F:IN] = t[:, g * Hp:g * Hp + H].t()
+                bs[g].copy_(t[:nbr, g * Hp:g * Hp + H].sum(0))
+        return 0
+
+    def ggpm_split_pad(self, W, ldw, N, K, Np, n, c0, c1, kp, out, bias, bias_p, stream):
+        self._tick("split_pad")
+        w = _tab(W, N, ldw, K)
+        for i, o in enumerate(self._ptrs(out, n)):
+            dst = _tab(o, Np, kp[i], kp[i])
+            dst.zero_()
+            dst[:N, :c1[i] - c0[i]] = w[:, c0[i]:c1[i]]
+        if bias_p:
+            bp = _f(bias_p, Np)
+            bp.zero_()
+            if bias:
+                bp[:N] = _f(bias, N)
+        return 0
+
+    def ggpm_split_unpad(self, dW, N, K, n, c0, c1, kp, dpieces, dbias_p, dbias, stream):
+        self._tick("split_unpad")
+        w = _tab(dW, N, K, K)
+        w.zero_()
+        for i, o in enumerate(self._ptrs(dpieces, n)):
+            if o:
+                w[:, c0[i]:c1[i]] = _tab(o, N, kp[i], kp[i])[:, :c1[i] - c0[i]]
+        if dbias:
+            d = _f(dbias, N)
+            d.zero_()
+            if dbias_p:
+                d.copy_(_f(dbias_p, N))
+        return 0
+
     def ggpm_act_bwd(self, dY, ld_dy, Y, ld_y, dZ, ld_dz, rows, width, act, zero_row0, stream):
         self._tick("act_bwd")
         g, y = _tab(dY, rows, ld_dy, width).to(DT), _tab(Y, rows, ld_y, width).to(DT)
@@ -171,8 +236,11 @@ class EmuLib:
         ntab = max(int(a.max()), int(b.max()) if b is not None else 0) + 1
         return P.xproj(_tab(Yn, n1, G * Hp, G * Hp).to(DT), s, _tab(T, ntab, G * Hp, G * Hp).to(DT), a, b)
 
+    def ggpm_lstm_plan(self, Hp, depth):
+        return 0
+
     def ggpm_lstm_fwd(self, E1, H, Hp, depth, b_ptr, b_col, Yn, src, T, k1, k2, Ug, Uf, hist_h, hist_c, hist_gp,
-                      s_scratch, w_split, hist_h16, keep, stream):
+                      s_scratch, w_split, hist_h16, keep, h_rotate, stream):
         self._tick("lstm_fwd")
         assert Hp % 32 == 0 and Hp >= H
         rp, col = _csr(b_ptr, b_col, E1)
@@ -197,7 +265,7 @@ class EmuLib:
         return 0
 
     def ggpm_lstm_bwd(self, E1, H, Hp, depth, b_ptr, b_col, bt_ptr, bt_row, Yn, src, T, k1, k2, Ug, Uf, hist_h,
-                      hist_c, hist_gp, dH_final, dX, dUg, dUf, dA, dC, dP, dS, S, dHn, w_split, hist_h16, z_planes, stream):
+                      hist_c, hist_gp, dH_final, dX, dUg, dUf, dA, dC, dP, dS, S, dHn, w_split, hist_h16, z_planes, h_rotate, stream):
         self._tick("lstm_bwd")
         rp, col = _csr(b_ptr, b_col, E1)
         trp, tcol = _csr(bt_ptr, bt_row, E1)

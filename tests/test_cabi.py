@@ -44,7 +44,7 @@ def test_argument_validation_needs_no_gpu(lib_path):
     assert b"engine" in lib.ggpm_last_error()
     assert lib.ggpm_gather_sum(None, 4, None, None, None, 4, 1, 4, 0, None) != 0
     assert b"null" in lib.ggpm_last_error()
-    assert lib.ggpm_lstm_fwd(5, 10, 33, 2, *([None] * 15), 0, None) != 0
+    assert lib.ggpm_lstm_fwd(5, 10, 33, 2, *([None] * 15), 0, 0, None) != 0
     assert b"multiple of 32" in lib.ggpm_last_error()
 
 

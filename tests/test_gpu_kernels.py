@@ -331,6 +331,39 @@ def test_f16x3_planes_tn_weight_gradient(M, N, K):
     assert rel(out, ref) <= 2e-6, rel(out, ref)
 
 
+@pytest.mark.parametrize("H,IN,F,nbr", [(20, 26, 6, 4), (250, 270, 250, 20), (37, 37, 37, 1), (250, 62, 38, 4)])
+def test_lstm_pack_matches_torch_packing_and_autograd(H, IN, F, nbr):
+    """ggpm_lstm_pack / ggpm_lstm_unpack vs the torch reshuffling they replace (bit-exact: pure data movement)"""
+    from ggpm_b200 import packing, rnn as R
+    torch.manual_seed(H + IN)
+    cell = R.LSTM(IN, H, 3).to(DEV)
+    Hp = Fn.padded_width(H)
+    got = packing.pack_lstm(cell, F, Hp, nbr)
+    Wx, T, Ug, Uf = packing.pack_lstm_torch(cell, F, Hp, nbr)
+    want = (Wx, T, torch.cat([Ug, Uf], 0))
+    cots = [torch.randn_like(w) for w in want]
+    for g, w in zip(got, want):
+        assert g.shape == w.shape and torch.equal(g, w)
+    params = list(cell.parameters())
+    g1 = torch.autograd.grad(sum((g * c).sum() for g, c in zip(got, cots)), params)
+    g2 = torch.autograd.grad(sum((w * c).sum() for w, c in zip(want, cots)), params)
+    for a, b in zip(g1, g2):
+        assert rel(a, b) <= 1e-6
+
+
+def test_split_pad_autograd():
+    torch.manual_seed(3)
+    W = torch.randn(250, 288, device=DEV, requires_grad=True)
+    b = torch.randn(250, device=DEV, requires_grad=True)
+    bias_p, w1, w2 = Fn.SplitPad.apply(W, b, 256, [(0, 38), (38, 288)], [40, 252])
+    assert w1.shape == (256, 40) and w2.shape == (256, 252) and bias_p.shape == (256,)
+    assert torch.equal(w1[:250, :38], W[:, :38]) and torch.equal(w2[:250, :250], W[:, 38:]) and torch.equal(bias_p[:250], b)
+    assert float(w1[250:].abs().max()) == 0 and float(w1[:, 38:].abs().max()) == 0 and float(w2[:, 250:].abs().max()) == 0
+    c1, c2, cb = torch.randn_like(w1), torch.randn_like(w2), torch.randn_like(bias_p)
+    ((w1 * c1).sum() + (w2 * c2).sum() + (bias_p * cb).sum()).backward()
+    assert torch.equal(W.grad, torch.cat([c1[:250, :38], c2[:250, :250]], 1)) and torch.equal(b.grad, cb[:250])
+
+
 def test_linear_act_autograd(engine):
     g = torch.Generator().manual_seed(9)
     A1 = torch.randn(400, 38, generator=g, dtype=torch.float64, requires_grad=True)
@@ -412,13 +445,13 @@ def test_lstm_layer_forward_backward(engine, H, Hp, depth, batch, with_k2):
     if d["k2"] is not None:
         dT.index_add_(0, d["k2"], dX)
     leaf = lambda t: t.float().to(DEV).requires_grad_(True)
-    phi, Wx, T, ug, uf = leaf(d["phi"]), leaf(d["Wx"]), leaf(d["T"]), leaf(Ug), leaf(Uf)
-    h, c = Fn.LSTMMessages.apply(phi, Wx, T, ug, uf, _message_graph(d), depth, H)
+    phi, Wx, T, u4 = leaf(d["phi"]), leaf(d["Wx"]), leaf(d["T"]), leaf(torch.cat([Ug, Uf], 0))
+    h, c = Fn.LSTMMessages.apply(phi, Wx, T, u4, _message_graph(d), depth, H)
     assert rel(h, h_ref) <= 1e-5
     assert rel(c, hist["c"][-1]) <= 1e-5
     assert float(h[0].abs().max()) == 0 and float(h[:, H:].abs().max()) == 0
     (h * d["cot"].float().to(DEV)).sum().backward()
-    assert rel(ug.grad, dUg) <= 2e-5 and rel(uf.grad, dUf) <= 2e-5
+    assert rel(u4.grad[:3 * Hp], dUg) <= 2e-5 and rel(u4.grad[3 * Hp:], dUf) <= 2e-5
     assert rel(T.grad, dT) <= 2e-5
     assert rel(Wx.grad, dYn.t() @ d["phi"]) <= 2e-5
     assert rel(phi.grad, dYn @ d["Wx"]) <= 2e-5
