@@ -18,6 +18,7 @@
 // Operands pass through registers (not TMA) because the A operand is computed (gather-sum + split), and the
 // split of B rides the same path.
 #include <cuda.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -57,6 +58,7 @@ struct TcParams {
     const int* b_row_ptr; const int* b_col;      // CSR gather-sum over B's k index (MN-major B only)
     float beta; const float* bias; int act; int zero_row0;
     int m_tiles, n_tiles, total_tiles, tiles_full;
+    int split_s;       // > 0 (fewer tiles than SMs): every tile is cut along K into split_s equal parts, one CTA each
     int epi_mode;
 };
 
@@ -238,6 +240,12 @@ struct SegIter {
     int t_next, u, u_end;
     __device__ __forceinline__ explicit SegIter(const TcParams& p) {
         t_next = blockIdx.x;
+        if (p.split_s > 0) {          // one K-slice of one tile per CTA: a single segment, a single epilogue
+            const int t = blockIdx.x / p.split_s, part = blockIdx.x % p.split_s;
+            u = t * p.nk + (int)((long long)p.nk * part / p.split_s);
+            u_end = t * p.nk + (int)((long long)p.nk * (part + 1) / p.split_s);
+            return;
+        }
         const long long ut = (long long)(p.total_tiles - p.tiles_full) * p.nk;
         u = (int)(ut * blockIdx.x / gridDim.x);
         u_end = (int)(ut * (blockIdx.x + 1) / gridDim.x);
@@ -521,7 +529,15 @@ struct F16Params {
     const int* a_deg;
     const float* a_scale;                  // when given: the A scale itself (A already is fp16 planes)
     const float* b_scale; float b_scale_const;
+    unsigned long long* dbg;               // optional [gridDim.x][8] globaltimer stamps (GGPM_F16_TRACE experiments)
 };
+
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define F16_STAMP(i) do { if (fp.dbg) fp.dbg[blockIdx.x * 8 + (i)] = gtimer(); } while (0)
 
 // modes of gemm_f16_kernel
 enum { F16_A_REGS = 0,      // A: fp32 K-major rows through registers (gather-sum, scaling, split); B: K-major planes by TMA
@@ -625,9 +641,11 @@ template <int BN, int MODE>
 __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp, const __grid_constant__ CUtensorMap tm_hi,
                                                               const __grid_constant__ CUtensorMap tm_lo,
                                                               const __grid_constant__ CUtensorMap ta_hi,
-                                                              const __grid_constant__ CUtensorMap ta_lo) {
+                                                              const __grid_constant__ CUtensorMap ta_lo,
+                                                              const __grid_constant__ CUtensorMap tc_out) {
     using C = Cfg<BN>;
     constexpr bool TN = MODE == F16_TN_TMA;
+    if (threadIdx.x == 0) F16_STAMP(0);
     using Iter = SegIter<BN, BK16>;
     const TcParams& p = fp.t;
     extern __shared__ uint8_t smem_raw[];
@@ -662,6 +680,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(&tmem_slot);
+    if (threadIdx.x == 0) F16_STAMP(1);
 
     if (MODE != F16_A_REGS && warp < MMA_WARP) {
         // ---------------- TMA-only producer: one thread streams both operands' planes into the stages ----------------
@@ -765,6 +784,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
                     const uint32_t ph = (uint32_t)(chunk / C::NSTAGE) & 1u;
                     tc::mbar_wait(full_bar(s), ph);
                     tc::fence_after_sync();
+                    if (chunk == 0) F16_STAMP(2);
                     const uint32_t sa = smem0 + s * C::STAGE;
                     const uint32_t sb = sa + 2 * A_BYTES;
 #pragma unroll
@@ -779,6 +799,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
                 }
                 tc::mma_commit(acc_full_bar(b));
             }
+            F16_STAMP(3);
         }
         __syncwarp();
     } else {
@@ -789,6 +810,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
         float* scratch = reinterpret_cast<float*>(smem_raw + (smem0 - tc::smem_u32(smem_raw)) + C::NSTAGE * C::STAGE) +
                          ew * (32 * SCR_LD);
         int it = 0;
+        int boxes_issued = 0;
         Iter sit(p);
         Seg tl;
         for (; sit.next(p, tl); ++it) {
@@ -797,9 +819,65 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
             const uint32_t aph = (uint32_t)(it / C::NACC) & 1u;
             tc::mbar_wait(acc_full_bar(b), aph);
             tc::fence_after_sync();
+            if (warp == EPI_WARP0 && lane == 0) F16_STAMP(4);
             const uint32_t d_main = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * 2 * BN);
             const int row_base = tl.m0 + q * 32;
             const int rows_valid = min(32, p.M - row_base);
+            if (epi_mode != EPI_GENERIC) {
+                // Plain store / accumulate: TMEM -> registers (x 1/scales) -> 128B-swizzled smem box of 32 rows x 32
+                // columns -> ONE bulk tensor store (or fp32 reduce-add: stream-K partial sums and beta = 1) per box.
+                // Rows / columns beyond the matrix are clipped by the TMA unit.  Two boxes per warp alternate; the
+                // TMEM loads of the next column group are issued before the current one is written out.
+                const bool reduce = epi_mode == EPI_ATOMIC || p.beta != 0.f;
+                const uint32_t box0 = smem0 + C::NSTAGE * C::STAGE + (uint32_t)ew * 8192u;
+                constexpr int NU = BN / 16;                      // units of 16 columns; two units fill one box
+                uint32_t v[2][16], w[2][16];
+                int nu = 0;
+                while (nu < NU && tl.n0 + nu * 16 < p.N) ++nu;   // N % 4 == 0; columns beyond N are clipped by the store
+                nu = (nu + 1) & ~1;
+                if (rows_valid > 0 && nu > 0) {
+                    tc::tmem_ld16(d_main, v[0]);
+                    tc::tmem_ld16(d_main + (uint32_t)BN, w[0]);
+#pragma unroll
+                    for (int u = 0; u < NU; ++u) {
+                        if (u < nu) {
+                            tc::tmem_ld_wait();
+                            if (u + 1 < nu) {
+                                tc::tmem_ld16(d_main + (uint32_t)((u + 1) * 16), v[(u + 1) & 1]);
+                                tc::tmem_ld16(d_main + (uint32_t)(BN + (u + 1) * 16), w[(u + 1) & 1]);
+                            }
+                            const uint32_t box = box0 + (uint32_t)(boxes_issued & 1) * 4096u;
+                            if ((u & 1) == 0 && boxes_issued >= 2) {     // the box used two stores ago must have been read out
+                                if (lane == 0) tc::bulk_wait_read<1>();
+                                __syncwarp();
+                            }
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const int jj = (u & 1) * 4 + j;          // 16-byte chunk of the 128-byte box row
+                                const uint32_t off = (uint32_t)(lane * 128 + ((jj ^ (lane & 7)) << 4));
+                                tc::sts4(box + off,
+                                         make_float4((__uint_as_float(v[u & 1][4 * j]) + __uint_as_float(w[u & 1][4 * j])) * inv,
+                                                     (__uint_as_float(v[u & 1][4 * j + 1]) + __uint_as_float(w[u & 1][4 * j + 1])) * inv,
+                                                     (__uint_as_float(v[u & 1][4 * j + 2]) + __uint_as_float(w[u & 1][4 * j + 2])) * inv,
+                                                     (__uint_as_float(v[u & 1][4 * j + 3]) + __uint_as_float(w[u & 1][4 * j + 3])) * inv));
+                            }
+                            if (u & 1) {
+                                tc::fence_async_smem();
+                                __syncwarp();
+                                if (lane == 0) {
+                                    if (reduce) tc::tma_reduce_add_2d(&tc_out, box, tl.n0 + (u >> 1) * 32, row_base);
+                                    else tc::tma_store_2d(&tc_out, box, tl.n0 + (u >> 1) * 32, row_base);
+                                    tc::bulk_commit();
+                                }
+                                ++boxes_issued;
+                            }
+                        }
+                    }
+                }
+                tc::fence_before_sync();
+                tc::mbar_arrive(acc_empty_bar(b));
+                continue;
+            }
             for (int g = 0; g < BN / 32; ++g) {
                 const int col0 = g * 32;
                 if (tl.n0 + col0 >= p.N) break;
@@ -848,10 +926,14 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
             tc::fence_before_sync();
             tc::mbar_arrive(acc_empty_bar(b));
         }
+        if (lane == 0) tc::bulk_wait_read<0>();      // the boxes have been read out; the writes complete with the grid
+        if (warp == EPI_WARP0 && lane == 0) F16_STAMP(5);
     }
     tc::fence_before_sync();
     __syncthreads();
+    if (threadIdx.x == 0) F16_STAMP(6);
     if (warp == MMA_WARP) tc::tmem_dealloc<TMEM_COLS>(tmem);
+    if (warp == MMA_WARP && lane == 0) F16_STAMP(7);
 }
 
 bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
@@ -919,16 +1001,34 @@ int make_plane_tmap16_tn(CUtensorMap* tm, const void* base, int k_rows, int mn, 
     return 0;
 }
 
+// fp32 C [M, N] (row stride ldc floats) for the epilogue's bulk stores: boxes of 32 columns (128 B, swizzled) x 32 rows
+int make_out_tmap(CUtensorMap* tm, const float* base, int M, int N, long long ldc) {
+    TmapEncodeFn enc = tmap_encoder();
+    GGPM_REQUIRE(enc != nullptr, "gemm_f16: cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[2] = {(cuuint64_t)N, (cuuint64_t)M};
+    cuuint64_t strides[1] = {(cuuint64_t)ldc * sizeof(float)};
+    cuuint32_t box[2] = {32, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    GGPM_REQUIRE(r == CUDA_SUCCESS, "gemm_f16: cuTensorMapEncodeTiled (output) failed (%d)", (int)r);
+    return 0;
+}
+
+constexpr int F16_EPI_BYTES = 4 * 2 * 4096;      // per epilogue warp: two 32 x 32 fp32 boxes
+template <int BN> constexpr int f16_smem() { return Cfg<BN>::NSTAGE * Cfg<BN>::STAGE + F16_EPI_BYTES + 1024; }
+
 template <int BN, int MODE>
 int launch_f16_variant(const F16Params& p, dim3 grid, const CUtensorMap& tm_hi, const CUtensorMap& tm_lo,
-                       const CUtensorMap& ta_hi, const CUtensorMap& ta_lo, cudaStream_t st) {
+                       const CUtensorMap& ta_hi, const CUtensorMap& ta_lo, const CUtensorMap& tc_out, cudaStream_t st) {
     static bool configured = false;
     auto kern = gemm_f16_kernel<BN, MODE>;
     if (!configured) {
-        GGPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM));
+        GGPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, f16_smem<BN>()));
         configured = true;
     }
-    kern<<<grid, THREADS, Cfg<BN>::SMEM, st>>>(p, tm_hi, tm_lo, ta_hi, ta_lo);
+    kern<<<grid, THREADS, f16_smem<BN>(), st>>>(p, tm_hi, tm_lo, ta_hi, ta_lo, tc_out);
     return check_launch("gemm_f16x3");
 }
 
@@ -987,6 +1087,7 @@ int launch_gemm_tc(const GemmArgs& g, cudaStream_t st) {
         GGPM_REQUIRE(g.A2 == nullptr || (aligned16(g.A2) && g.lda2 % 4 == 0), "gemm_tcgen05: A2 alignment");
     }
     const int bnf = wide ? 256 : 128;
+    p.split_s = 0;
     p.nk = ceil_div(g.K, BK);
     p.m_tiles = ceil_div(g.M, BM);
     p.n_tiles = ceil_div(g.N, bnf);
@@ -1080,6 +1181,8 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
     p.beta = g.beta; p.bias = g.bias; p.act = g.act; p.zero_row0 = g.zero_row0;
     fp.a_amax = g.a_amax; fp.a_amax_n = g.a_amax_n; fp.a_amax_const = g.a_amax_const; fp.a_deg = g.a_deg;
     fp.a_scale = g.a_scale; fp.b_scale = g.b_scale; fp.b_scale_const = g.b_scale_const;
+    fp.dbg = nullptr;
+    if (const char* tr = getenv("GGPM_F16_TRACE")) fp.dbg = (unsigned long long*)strtoull(tr, nullptr, 0);
     const bool plain_epilogue = !g.bias && g.act == GGPM_ACT_NONE && !g.zero_row0 && (g.beta == 0.f || g.beta == 1.f);
     bool wide = g.N > 128;
     if (g.tile_n == 128) wide = false;
@@ -1093,12 +1196,20 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
     const int sms = sm_count();
     int ctas = sms;
     p.tiles_full = p.total_tiles;
-    if (plain_epilogue && p.total_tiles % sms != 0 && p.nk >= 2) {
-        p.tiles_full = (p.total_tiles / sms) * sms;
-        const long long tail_units = (long long)(p.total_tiles - p.tiles_full) * p.nk;
-        if (p.tiles_full == 0 && tail_units < sms) ctas = (int)tail_units;
-    } else if (p.total_tiles < sms) {
-        ctas = p.total_tiles;
+    p.split_s = 0;
+    if (p.total_tiles < sms) {
+        // fewer tiles than SMs: cut every tile along K into equal slices so that each CTA runs one segment and one
+        // (reducing) epilogue; slices of a tile are summed by the TMA reduce-add of the epilogue
+        int s_ = plain_epilogue ? sms / p.total_tiles : 1;
+        if (s_ > p.nk) s_ = p.nk;
+        if (const char* cap = getenv("GGPM_F16_SPLIT")) {     // experiment knob
+            const int c = atoi(cap);
+            if (c > 0 && c < s_) s_ = c;
+        }
+        if (s_ >= 2) { p.tiles_full = 0; p.split_s = s_; ctas = p.total_tiles * s_; }
+        else ctas = p.total_tiles;
+    } else if (plain_epilogue && p.total_tiles % sms != 0 && p.nk >= 2) {
+        p.tiles_full = (p.total_tiles / sms) * sms;       // tail tiles after the full waves: stream-K over all CTAs
     }
     if (g.beta != 0.f || g.bias != nullptr || g.act != GGPM_ACT_NONE || g.zero_row0) p.epi_mode = EPI_GENERIC;
     else p.epi_mode = EPI_STORE;
@@ -1108,28 +1219,29 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
                                     sizeof(float) * (size_t)g.N, (size_t)(g.M - m_first), st));
     }
     ProfScope prof(mode == F16_TN_TMA ? PROF_GEMM_WGRAD : PROF_GEMM_TC, st, 2.0 * g.M * g.N * (double)g.K);
-    CUtensorMap tm_hi, tm_lo, ta_hi, ta_lo;
+    CUtensorMap tm_hi, tm_lo, ta_hi, ta_lo, tc_out;
     memset(&ta_hi, 0, sizeof(ta_hi));
     memset(&ta_lo, 0, sizeof(ta_lo));
+    GGPM_TRY(make_out_tmap(&tc_out, g.C, g.M, g.N, g.ldc));
     dim3 grid(ctas, 1, 1);
     if (mode == F16_TN_TMA) {
         GGPM_TRY(make_plane_tmap16_tn(&tm_hi, g.Bh_hi, g.K, g.N, g.sbn, bnf / 64));
         GGPM_TRY(make_plane_tmap16_tn(&tm_lo, g.Bh_lo, g.K, g.N, g.sbn, bnf / 64));
         GGPM_TRY(make_plane_tmap16_tn(&ta_hi, g.Ah_hi, g.K, g.M, g.lda_h, BM / 64));
         GGPM_TRY(make_plane_tmap16_tn(&ta_lo, g.Ah_lo, g.K, g.M, g.lda_h, BM / 64));
-        if (wide) return launch_f16_variant<256, F16_TN_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
-        return launch_f16_variant<128, F16_TN_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
+        if (wide) return launch_f16_variant<256, F16_TN_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, tc_out, st);
+        return launch_f16_variant<128, F16_TN_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, tc_out, st);
     }
     GGPM_TRY(make_plane_tmap16(&tm_hi, g.Bh_hi, g.N, g.K, g.sbn, bnf));
     GGPM_TRY(make_plane_tmap16(&tm_lo, g.Bh_lo, g.N, g.K, g.sbn, bnf));
     if (mode == F16_A_TMA) {
         GGPM_TRY(make_plane_tmap16(&ta_hi, g.Ah_hi, g.M, g.K, g.lda_h, BM));
         GGPM_TRY(make_plane_tmap16(&ta_lo, g.Ah_lo, g.M, g.K, g.lda_h, BM));
-        if (wide) return launch_f16_variant<256, F16_A_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
-        return launch_f16_variant<128, F16_A_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
+        if (wide) return launch_f16_variant<256, F16_A_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, tc_out, st);
+        return launch_f16_variant<128, F16_A_TMA>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, tc_out, st);
     }
-    if (wide) return launch_f16_variant<256, F16_A_REGS>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
-    return launch_f16_variant<128, F16_A_REGS>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, st);
+    if (wide) return launch_f16_variant<256, F16_A_REGS>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, tc_out, st);
+    return launch_f16_variant<128, F16_A_REGS>(fp, grid, tm_hi, tm_lo, ta_hi, ta_lo, tc_out, st);
 }
 
 // ---- helpers of the f16x3 engine: max|w|, scaled fp16 hi / lo planes, max CSR row length ------------------

@@ -1,32 +1,27 @@
 #!/usr/bin/env python
-"""Print headline metrics and the hottest SASS lines (by warp-stall samples) of an .ncu-rep capture."""
+"""Hottest SASS lines (by warp-stall samples) of one kernel of an .ncu-rep capture.
+Usage: python tools/ncu_top.py capture.ncu-rep [ntop] [launch-index]"""
 import csv, subprocess, sys, io
-rep = sys.argv[1]; ntop = int(sys.argv[2]) if len(sys.argv) > 2 else 30
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-rows = list(csv.reader(io.StringIO(raw)))
-hdr, vals = rows[0], rows[2]
-for key in ("gpu__time_duration.sum", "sm__cycles_active.avg", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
-            "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
-            "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
-            "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
-            "launch__registers_per_thread", "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum"):
-    for h, v, u in zip(hdr, vals, rows[1]):
-        if h == key:
-            print("%-75s %s %s" % (h, v, u))
+rep = sys.argv[1]; ntop = int(sys.argv[2]) if len(sys.argv) > 2 else 30; which = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
-hdr, data = rows[1], rows[2:]
-si = hdr.index("# Samples")
-stall_cols = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
-tot = sum(int(r[si]) for r in data)
-print("total samples", tot)
+starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
+starts.append(len(rows))
+blk = rows[starts[which]:starts[which + 1]]
+print(blk[0][1][:120])
+hdr = blk[1]
+data = [r for r in blk[2:] if len(r) == len(hdr) and r[0] != "Address"]
+si, so, ie = hdr.index("# Samples"), hdr.index("Source"), hdr.index("Instructions Executed")
+stall = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
+num = lambda x: int(x) if x else 0
+print("total samples", sum(num(r[si]) for r in data), "SASS lines", len(data))
 agg = {}
 for r in data:
-    for c in stall_cols:
-        agg[hdr[c]] = agg.get(hdr[c], 0) + (int(r[c]) if r[c] else 0)
+    for c in stall:
+        agg[hdr[c]] = agg.get(hdr[c], 0) + num(r[c])
 print("stall reasons:", sorted(agg.items(), key=lambda kv: -kv[1])[:8])
-top = sorted(range(len(data)), key=lambda i: -int(data[i][si]))[:ntop]
+top = sorted(range(len(data)), key=lambda i: -num(data[i][si]))[:ntop]
 for i in sorted(top):
     r = data[i]
-    st = sorted(((int(r[c]) if r[c] else 0, hdr[c]) for c in stall_cols), reverse=True)[:2]
-    print("%5d %6s  %-70s %s" % (i, r[si], r[1].strip()[:70], st))
+    st = sorted(((num(r[c]), hdr[c]) for c in stall), reverse=True)[:2]
+    print("%5d %6s %8s  %-78s %s" % (i, r[si], r[ie], r[so].strip()[:78], st))
