@@ -39,6 +39,8 @@ WORKLOADS = {
                  desc="configs/configs.json encoder, 20 synthetic molecules"),
     "cfg2": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256,
                  desc="encoder of one vae_train.py step, pretrained_w_tie_embedding_configs.json, batch 256"),
+    "cfg3s": dict(hidden=500, depthT=20, depthG=20, dropout=0.0, batch=1024,
+                  desc="double-hidden encoder (hidden 500), batch 1024 synthetic graphs (profiling-sized cfg3)"),
     "cfg3": dict(hidden=500, depthT=20, depthG=20, dropout=0.0, batch=4096,
                  desc="double-hidden encoder (hidden 500), batch 4096 synthetic graphs"),
 }
@@ -56,48 +58,96 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs"""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled every 200 ms while the timed region runs, through NVML in-process
+    (nvidia_ml_py).  Spawning `nvidia-smi -lms 200` instead was measured to stall kernel launches on multi-GPU hosts
+    (3x longer steps while it polled), so it is only the fallback, at a 1 s period."""
 
     def __init__(self, gpu_index):
-        self.rows, self.proc, self.gpu = [], None, gpu_index
+        self.gpu, self.rows, self.stop_flag, self.thread, self.proc = gpu_index, [], False, None, None
+        self.mode = None
+
+    def _nvml_loop(self):
+        import pynvml as nv
+        R = [("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown")
+              else nv.nvmlClocksThrottleReasonHwSlowdown),
+             ("hw_thermal_slowdown", getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", None)
+              or nv.nvmlClocksThrottleReasonHwThermalSlowdown),
+             ("sw_thermal_slowdown", getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", None)
+              or nv.nvmlClocksThrottleReasonSwThermalSlowdown),
+             ("sw_power_cap", getattr(nv, "nvmlClocksEventReasonSwPowerCap", None) or nv.nvmlClocksThrottleReasonSwPowerCap)]
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.rows.append((float(sm), float(self.max_sm), [n for n, bit in R if mask & bit]))
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def _smi_loop(self):
+        for line in self.proc.stdout:
+            r = [c.strip() for c in line.split(",")]
+            try:
+                names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+                self.rows.append((float(r[0]), float(r[1]), [n for n, v in zip(names, r[2:6]) if v.lower().startswith("active")]))
+            except Exception:
+                continue
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = self.gpu
+            if vis:
+                ids = [v for v in vis.split(",") if v.strip() != ""]
+                if self.gpu < len(ids) and ids[self.gpu].strip().isdigit():
+                    phys = int(ids[self.gpu])
+            self.h = None
+            try:                                     # exact device even when CUDA_VISIBLE_DEVICES holds UUIDs
+                uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+                self.h = nv.nvmlDeviceGetHandleByUUID(uuid if uuid.startswith("GPU-") else "GPU-" + uuid)
+            except Exception:
+                self.h = None
+            if self.h is None:
+                self.h = nv.nvmlDeviceGetHandleByIndex(phys)
+            self.max_sm = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            self.mode = "nvml"
+            self.thread = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            pass
+        try:
+            q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "1000"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.mode = "nvidia-smi"
+            self.thread = threading.Thread(target=self._smi_loop, daemon=True)
             self.thread.start()
         except Exception:
             self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
-
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        if self.mode is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no NVML / nvidia-smi"]}
         time.sleep(0.25)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        self.stop_flag = True
+        if self.proc is not None:
+            self.proc.terminate()
             try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
+                self.proc.wait(timeout=2)
             except Exception:
-                continue
-            for n, v in zip(names, r[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
+                self.proc.kill()
+        if self.thread is not None:
+            self.thread.join(timeout=2)
+        sm = [r[0] for r in self.rows]
+        mx = [r[1] for r in self.rows]
+        reasons = sorted({n for r in self.rows for n in r[2]})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": self.mode}
 
 
 def make_batches(workload, n_batches, seed):

@@ -970,8 +970,36 @@ int make_plane_tmap(CUtensorMap* tm, const float* base, int rows, int cols, long
     return 0;
 }
 
+// cuTensorMapEncodeTiled costs about a microsecond and the same maps recur in every round of a layer call (weight
+// planes, Z planes, gradient outputs): a small per-thread cache keyed by everything that goes into the encoding
+struct TmapKey {
+    const void* base; long long a, b, c, ld; int kind;
+    bool operator==(const TmapKey& o) const {
+        return base == o.base && a == o.a && b == o.b && c == o.c && ld == o.ld && kind == o.kind;
+    }
+};
+constexpr int kTmapCache = 32;
+struct TmapCache {
+    TmapKey key[kTmapCache];
+    CUtensorMap map[kTmapCache];
+    int n = 0, next = 0;
+    const CUtensorMap* find(const TmapKey& k) const {
+        for (int i = 0; i < n; ++i)
+            if (key[i] == k) return &map[i];
+        return nullptr;
+    }
+    void put(const TmapKey& k, const CUtensorMap& m) {
+        const int i = n < kTmapCache ? n++ : (next = (next + 1) % kTmapCache);
+        key[i] = k;
+        map[i] = m;
+    }
+};
+static thread_local TmapCache g_tmaps;
+
 // fp16 [rows, cols] row-major plane (leading stride ld halves), box = 64 columns (one 128-byte swizzle row) x box_rows
 int make_plane_tmap16(CUtensorMap* tm, const void* base, int rows, int cols, long long ld, int box_rows) {
+    const TmapKey key{base, rows, cols, box_rows, ld, 1};
+    if (const CUtensorMap* hit = g_tmaps.find(key)) { *tm = *hit; return 0; }
     TmapEncodeFn enc = tmap_encoder();
     GGPM_REQUIRE(enc != nullptr, "gemm_f16: cuTensorMapEncodeTiled is not available from the driver");
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -982,12 +1010,15 @@ int make_plane_tmap16(CUtensorMap* tm, const void* base, int rows, int cols, lon
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     GGPM_REQUIRE(r == CUDA_SUCCESS, "gemm_f16: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    g_tmaps.put(key, *tm);
     return 0;
 }
 
 // 3-D view of a k-row-major fp16 plane [k_rows, mn] (row stride ld halves) for MN-major operand tiles:
 // dims (64 mn, k rows, mn / 64), box (64, 64, mn_blocks): one box = mn_blocks swizzle-atom columns of 64 k rows each
 int make_plane_tmap16_tn(CUtensorMap* tm, const void* base, int k_rows, int mn, long long ld, int mn_blocks) {
+    const TmapKey key{base, k_rows, mn, mn_blocks, ld, 2};
+    if (const CUtensorMap* hit = g_tmaps.find(key)) { *tm = *hit; return 0; }
     TmapEncodeFn enc = tmap_encoder();
     GGPM_REQUIRE(enc != nullptr, "gemm_f16: cuTensorMapEncodeTiled is not available from the driver");
     cuuint64_t dims[3] = {64, (cuuint64_t)k_rows, (cuuint64_t)(mn / 64)};
@@ -998,11 +1029,14 @@ int make_plane_tmap16_tn(CUtensorMap* tm, const void* base, int k_rows, int mn, 
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     GGPM_REQUIRE(r == CUDA_SUCCESS, "gemm_f16: cuTensorMapEncodeTiled (3-D) failed (%d)", (int)r);
+    g_tmaps.put(key, *tm);
     return 0;
 }
 
 // fp32 C [M, N] (row stride ldc floats) for the epilogue's bulk stores: boxes of 32 columns (128 B, swizzled) x 32 rows
 int make_out_tmap(CUtensorMap* tm, const float* base, int M, int N, long long ldc) {
+    const TmapKey key{base, M, N, 0, ldc, 3};
+    if (const CUtensorMap* hit = g_tmaps.find(key)) { *tm = *hit; return 0; }
     TmapEncodeFn enc = tmap_encoder();
     GGPM_REQUIRE(enc != nullptr, "gemm_f16: cuTensorMapEncodeTiled is not available from the driver");
     cuuint64_t dims[2] = {(cuuint64_t)N, (cuuint64_t)M};
@@ -1013,6 +1047,7 @@ int make_out_tmap(CUtensorMap* tm, const float* base, int M, int N, long long ld
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     GGPM_REQUIRE(r == CUDA_SUCCESS, "gemm_f16: cuTensorMapEncodeTiled (output) failed (%d)", (int)r);
+    g_tmaps.put(key, *tm);
     return 0;
 }
 

@@ -61,10 +61,16 @@ class GradBucket:
         """sum of (weight * grad) over ranks divided by the sum of weights; weight = molecules in the
         local batch makes uneven shards exact."""
         flat = self.pack()
-        if weight != 1.0:
-            flat.mul_(weight)
+        multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+        if weight == 1.0:
+            # equal shards: the divisor is the world size, no second collective and no host read-back
+            if multi:
+                dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+            self.unpack(1.0 / (dist.get_world_size(group) if multi else 1))
+            return
+        flat.mul_(weight)
         total = torch.tensor([weight], dtype=torch.float64, device=flat.device)
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        if multi:
             dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
             dist.all_reduce(total, op=dist.ReduceOp.SUM, group=group)
         self.unpack(1.0 / float(total.item()))

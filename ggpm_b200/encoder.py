@@ -15,7 +15,7 @@ import torch.nn as nn
 
 from . import functional as Fn
 from ._lib import ACT_RELU, ACT_TANH
-from .nnutils import to_cuda
+from .nnutils import ints_to_device, to_cuda
 from .rnn import GRU, LSTM
 
 N_BOND_TYPES = 4     # len(MolGraph.BOND_LIST), ggpm/mol_graph.py:14
@@ -94,7 +94,7 @@ class _TreeBatch:
         self.a = Fn.csr_from_padded(agraph, self.n_mess)
         b = Fn.csr_from_padded(bgraph, self.n_mess)
         self.mg = Fn.MessageGraph(b, _i32(fmess[:, 0]), _i32(fmess[:, 2]), None, self.n_nodes, MAX_POS)
-        self.roots = torch.tensor([st for st, le in scope], dtype=torch.long, device=fnode.device)
+        self.roots = ints_to_device([st for st, le in scope], fnode.device)
 
 
 def _root_vectors(W_root, feat, incoming, roots, H):

@@ -30,6 +30,47 @@ def to_cuda(tensor):
     return tensor.to(default_device())
 
 
+class _PinnedRing:
+    """Small ring of pinned int64 staging buffers for host lists that must reach the device every step (the root ids
+    derived from `scope`).  A pageable torch.tensor(list, device=...) copy makes the host wait for the stream, which
+    serialises host and device once per forward; a pinned non_blocking copy does not.  Each slot carries an event so
+    that it is only rewritten after its previous copy has executed."""
+
+    def __init__(self, slots: int = 8):
+        self.slots, self.buf, self.ev, self.i = slots, [None] * slots, [None] * slots, 0
+
+    def to_device(self, values, device) -> torch.Tensor:
+        n = len(values)
+        k = self.i
+        self.i = (self.i + 1) % self.slots
+        if self.ev[k] is not None:
+            self.ev[k].synchronize()
+        if self.buf[k] is None or self.buf[k].numel() < n:
+            self.buf[k] = torch.empty(max(256, 2 * n), dtype=torch.int64).pin_memory()
+        host = self.buf[k][:n]
+        host.numpy()[:] = np.asarray(values, dtype=np.int64)
+        out = host.to(device, non_blocking=True)
+        if self.ev[k] is None:
+            self.ev[k] = torch.cuda.Event()
+        self.ev[k].record(torch.cuda.current_stream(device))
+        return out
+
+
+_RING = None
+
+
+def ints_to_device(values, device) -> torch.Tensor:
+    """Python list of ints -> int64 tensor on `device` without a host/stream synchronisation (CUDA devices);
+    plain torch.tensor elsewhere (the host-side tests)."""
+    global _RING
+    device = torch.device(device)
+    if device.type != "cuda":
+        return torch.tensor(list(values), dtype=torch.long, device=device)
+    if _RING is None:
+        _RING = _PinnedRing()
+    return _RING.to_device(values, device)
+
+
 def index_select_ND(source: torch.Tensor, dim: int, index: torch.Tensor) -> torch.Tensor:
     """source [R, H], index [M, K] -> [M, K, H]; same semantics as ggpm/nnutils.py:65-70 (padding slots
     read row `index` points at, normally the zero row 0).  Materialises the result — the encoder itself

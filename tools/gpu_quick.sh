@@ -1,2 +1,2 @@
-timeout 300 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k "f16x3" 2>&1 | tail -5
-python tools/f16_trace.py 2>&1 | grep -v Warn
+timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+python tools/host_time.py 2>&1 | grep host
