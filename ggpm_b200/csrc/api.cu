@@ -1,6 +1,7 @@
 // C-ABI entry points that orchestrate whole layers: the depth loops of the graph LSTM / GRU
 // (ggpm/rnn.py:41-50, 96-108) and their back-propagation through time, plus library-wide state.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -43,6 +44,15 @@ int sm_count() {
 }
 
 int gemm_engine() { return g_engine.load(std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("GGPM_PDL");
+        on = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return on != 0;
+}
 
 // ---- per-launch event timing -------------------------------------------------------------------------
 constexpr int kProfMax = 1 << 16;
@@ -391,8 +401,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
         const float* h_prev = h_rotate ? nullptr : hist_h + (size_t)(t - 2) * row;     // only read without the plane path
         const float* c_prev = hist_c + (size_t)(t - 2) * row;
         float* dC_prev = dC + (size_t)(t & 1) * row;
-        GGPM_CUDA(cudaMemsetAsync(dP, 0, sizeof(float) * row, st));
-        GGPM_CUDA(cudaMemsetAsync(dC_prev, 0, sizeof(float) * row, st));
+        GGPM_TRY(launch_zero2(dP, dC_prev, row, st));
         // the cell kernel also records max |gate-gradient term| of this round (16 slots): the scale of the f16x3 GEMM
         float* amax_t = f16 ? fw.scal + 16 + 16 * (size_t)t : nullptr;
         GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_cur, dA, dX, overwrite,

@@ -43,6 +43,8 @@ __global__ void __launch_bounds__(kCellWarps * 32)
 lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
                      const float* __restrict__ gp, const float* __restrict__ c_prev, float* __restrict__ h_out,
                      float* __restrict__ c_out, uint2* __restrict__ h16_hi, uint2* __restrict__ h16_lo) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
     const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (e >= E1) return;
@@ -108,6 +110,8 @@ lstm_zgather_kernel(int E1, int Hp, const int* __restrict__ tp, const int* __res
                     const float* __restrict__ dA, const float* __restrict__ dP, const float* __restrict__ amax16,
                     const int* __restrict__ deg, uint4* __restrict__ z_hi, uint4* __restrict__ z_lo,
                     float* __restrict__ scale_out) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
     const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     float amax = 0.f;
@@ -153,6 +157,8 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
                      const float* __restrict__ dH, const float* __restrict__ dC, float* __restrict__ dA,
                      float* __restrict__ dX, int dx_overwrite, float* __restrict__ dP, float* __restrict__ dC_prev,
                      float* __restrict__ amax16) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
     const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (e >= E1) return;
@@ -162,7 +168,7 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
     float* dXe = dX + (size_t)e * ld4h;
     if (e == 0) {
         for (int c = lane * 4; c < ld4h; c += 128) {
-            st4(dAe + c, f4zero());
+            if (c < 3 * Hp) st4(dAe + c, f4zero());
             if (dx_overwrite) st4(dXe + c, f4zero());
         }
         return;
@@ -203,8 +209,7 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
         tmax = fmaxf(tmax, fmaxf(amax4(dai), fmaxf(amax4(dao), amax4(dau))));
         st4(dAe + c, dai);
         st4(dAe + Hp + c, dao);
-        st4(dAe + 2 * Hp + c, dau);
-        st4(dAe + 3 * Hp + c, dafs);
+        st4(dAe + 2 * Hp + c, dau);      // the forget block of dA has no reader (dP carries it): only dX gets dafs
         if (dx_overwrite) {
             st4(dXe + c, dai);
             st4(dXe + Hp + c, dao);
@@ -417,7 +422,27 @@ table_wgrad_kernel(const float* __restrict__ dX, int ld_dx, int rows, int width,
     }
 }
 
+// Zero the two reduction targets of a backward round in one launch, right before the cell kernel that reduces into
+// them: the lines are then L2-resident when the red.global.add traffic arrives (zeroing them a kernel or two earlier
+// lets them be evicted first, which was measured to slow the cell kernel by 60 %).
+__global__ void __launch_bounds__(256) zero2_kernel(float4* __restrict__ a, float4* __restrict__ b, size_t n4) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        a[i] = z;
+        b[i] = z;
+    }
+}
+
 // ---- launchers ----------------------------------------------------------------------------------
+int launch_zero2(float* a, float* b, size_t n, cudaStream_t st) {     // n % 4 == 0, 16-byte aligned
+    const size_t n4 = n / 4;
+    const int blocks = (int)((n4 + 255) / 256 < (size_t)(8 * sm_count()) ? (n4 + 255) / 256 : (size_t)(8 * sm_count()));
+    launch_pdl(zero2_kernel, dim3(blocks > 0 ? blocks : 1), dim3(256), 0, st, (float4*)a, (float4*)b, n4);
+    return check_launch("zero2");
+}
+
 static inline int cell_blocks(int E1) { return ceil_div(E1, kCellWarps); }
 
 int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
@@ -425,20 +450,16 @@ int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const
                          cudaStream_t st) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_FWD, st, 0.0);
-    if (first)
-        lstm_cell_fwd_kernel<true><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out,
-                                                                                (uint2*)h16_hi, (uint2*)h16_lo);
-    else
-        lstm_cell_fwd_kernel<false><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out,
-                                                                                 (uint2*)h16_hi, (uint2*)h16_lo);
+    launch_pdl(first ? lstm_cell_fwd_kernel<true> : lstm_cell_fwd_kernel<false>, dim3(cell_blocks(E1)), dim3(kCellWarps * 32), 0,
+               st, E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out, (uint2*)h16_hi, (uint2*)h16_lo);
     return check_launch("lstm_cell_fwd");
 }
 
 int launch_lstm_zgather(int E1, int Hp, const int* t_ptr, const int* t_row, const float* dA, const float* dP,
                         const float* amax16, const int* deg, void* z_hi, void* z_lo, float* scale_out, cudaStream_t st) {
     ProfScope prof(PROF_GATHER, st, 0.0);
-    lstm_zgather_kernel<<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, Hp, t_ptr, t_row, dA, dP, amax16, deg, (uint4*)z_hi,
-                                                                      (uint4*)z_lo, scale_out);
+    launch_pdl(lstm_zgather_kernel, dim3(cell_blocks(E1)), dim3(kCellWarps * 32), 0, st, E1, Hp, t_ptr, t_row, dA, dP, amax16,
+               deg, (uint4*)z_hi, (uint4*)z_lo, scale_out);
     return check_launch("lstm_zgather");
 }
 
@@ -448,10 +469,8 @@ int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const
                          cudaStream_t st) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_BWD, st, 0.0);
-    if (first)
-        lstm_cell_bwd_kernel<true><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, dx_overwrite, dP, dC_prev, amax16);
-    else
-        lstm_cell_bwd_kernel<false><<<cell_blocks(E1), kCellWarps * 32, 0, st>>>(E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, dx_overwrite, dP, dC_prev, amax16);
+    launch_pdl(first ? lstm_cell_bwd_kernel<true> : lstm_cell_bwd_kernel<false>, dim3(cell_blocks(E1)), dim3(kCellWarps * 32), 0,
+               st, E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, (int)dx_overwrite, dP, dC_prev, amax16);
     return check_launch("lstm_cell_bwd");
 }
 

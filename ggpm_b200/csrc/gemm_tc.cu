@@ -680,6 +680,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(&tmem_slot);
+    pdl_wait();                       // setup above overlapped the previous grid's tail; its results are visible from here
+    pdl_launch_dependents();
     if (threadIdx.x == 0) F16_STAMP(1);
 
     if (MODE != F16_A_REGS && warp < MMA_WARP) {
@@ -1063,7 +1065,7 @@ int launch_f16_variant(const F16Params& p, dim3 grid, const CUtensorMap& tm_hi, 
         GGPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, f16_smem<BN>()));
         configured = true;
     }
-    kern<<<grid, THREADS, f16_smem<BN>(), st>>>(p, tm_hi, tm_lo, ta_hi, ta_lo, tc_out);
+    launch_pdl(kern, grid, dim3(THREADS), (size_t)f16_smem<BN>(), st, p, tm_hi, tm_lo, ta_hi, ta_lo, tc_out);
     return check_launch("gemm_f16x3");
 }
 

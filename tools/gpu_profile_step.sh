@@ -1,7 +1,7 @@
 set -x
 B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --profile-step"
-$B > gpurun_out/s25_plain.log 2>&1 && ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/s25_launches.csv $B > gpurun_out/s25_ncu1.log 2>&1
-python - <<'PY' > gpurun_out/s25_gaps.txt 2>&1
+$B > gpurun_out/s31_plain.log 2>&1 && ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/s31_launches.csv $B > gpurun_out/s31_ncu1.log 2>&1
+python - <<'PY' > gpurun_out/s31_gaps.txt 2>&1
 import torch, time, sys
 sys.path.insert(0,'.')
 import bench, ggpm_b200
