@@ -5,6 +5,8 @@
 // 86-93) are never built.  The depth-invariant x-projection is read as a sum of table rows:
 //     X_g[e] = Yn[src[e], g] + T[k1[e], g] (+ T[k2[e], g])
 // Math: SURVEY.md Appendix A (restated and checked against autograd in tests/_proto.py).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "tc_ptx.cuh"
@@ -12,6 +14,8 @@
 namespace ggpm {
 
 constexpr int kCellWarps = 8;
+constexpr int kCellGridBlocks = 8;
+constexpr int kCellMinBlocks = 4;       // 64 registers per thread: 32 resident warps per SM for the row kernels
 constexpr float kH16Scale = 8192.f;      // 2^13: fp16 planes of h (|h| <= 1), GGPM_H16_SCALE
 
 struct XTab {
@@ -39,23 +43,24 @@ __device__ __forceinline__ float4 xval(const XRow& r, int off) {
 // LSTM forward cell:  reads gp = [G_i|G_o|G_u|P] of this round (rows e: G, rows n: P), c_prev; writes h, c
 // ------------------------------------------------------------------------------------------------
 template <bool FIRST>
-__global__ void __launch_bounds__(kCellWarps * 32)
+__global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
                      const float* __restrict__ gp, const float* __restrict__ c_prev, float* __restrict__ h_out,
                      float* __restrict__ c_out, uint2* __restrict__ h16_hi, uint2* __restrict__ h16_lo) {
     pdl_wait();
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
-    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (e >= E1) return;
     const int ld4h = 4 * Hp;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
+    // grid-stride over message rows: neighbouring warps take neighbouring rows, no partial last wave
+    for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < E1; e += n_warps) {
     if (e == 0) {   // padding row: forced to zero after every round (ggpm/rnn.py:106-107)
         for (int c = lane * 4; c < Hp; c += 128) {
             st4(h_out + c, f4zero());
             st4(c_out + c, f4zero());
             if (h16_hi) { h16_hi[c >> 2] = make_uint2(0u, 0u); h16_lo[c >> 2] = make_uint2(0u, 0u); }
         }
-        return;
+        continue;
     }
     const XRow xr = xrow(xt, e);
     const int b = FIRST ? 0 : __ldg(rp + e), en = FIRST ? 0 : __ldg(rp + e + 1);
@@ -98,6 +103,7 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
             h16_lo[((size_t)e * Hp + c) >> 2] = lo;
         }
     }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -105,7 +111,7 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
 // consume it: dH^{t-1} = Z [Ug; Uf] and [dUg; dUf] += Z^T h^{t-1} (the neighbour sum moved onto the gradient side
 // by linearity), so neither needs a gather in its operand path and both are fed by TMA alone.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kCellWarps * 32)
+__global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_zgather_kernel(int E1, int Hp, const int* __restrict__ tp, const int* __restrict__ trow,
                     const float* __restrict__ dA, const float* __restrict__ dP, const float* __restrict__ amax16,
                     const int* __restrict__ deg, uint4* __restrict__ z_hi, uint4* __restrict__ z_lo,
@@ -113,14 +119,14 @@ lstm_zgather_kernel(int E1, int Hp, const int* __restrict__ tp, const int* __res
     pdl_wait();
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
-    const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     float amax = 0.f;
 #pragma unroll
     for (int i = 0; i < 16; ++i) amax = fmaxf(amax, __ldg(amax16 + i));
     const float s = tc::pow2_scale(amax * (float)max(1, __ldg(deg)));
     if (blockIdx.x == 0 && threadIdx.x == 0) *scale_out = s;
-    if (n >= E1) return;
     const int ld4h = 4 * Hp;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; n < E1; n += n_warps) {
     const int b = __ldg(tp + n), en = __ldg(tp + n + 1);
     for (int c = lane * 8; c < ld4h; c += 256) {
         float4 a0 = f4zero(), a1 = f4zero();
@@ -145,13 +151,14 @@ lstm_zgather_kernel(int E1, int Hp, const int* __restrict__ tp, const int* __res
         z_hi[((size_t)n * ld4h + c) >> 3] = hi;
         z_lo[((size_t)n * ld4h + c) >> 3] = lo;
     }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
 // LSTM backward cell (one round).  dP / dC_prev are accumulated with vector reductions (zeroed by caller).
 // ------------------------------------------------------------------------------------------------
 template <bool FIRST>
-__global__ void __launch_bounds__(kCellWarps * 32)
+__global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
                      const float* __restrict__ gp, const float* __restrict__ c_prev, const float* __restrict__ c_cur,
                      const float* __restrict__ dH, const float* __restrict__ dC, float* __restrict__ dA,
@@ -160,10 +167,10 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
     pdl_wait();
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
-    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (e >= E1) return;
     const int ld4h = 4 * Hp;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
     float tmax = 0.f;      // max |dai|, |dao|, |dau|, |daf_en| seen by this thread (scale of the f16x3 state-gradient GEMM)
+    for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < E1; e += n_warps) {
     float* dAe = dA + (size_t)e * ld4h;
     float* dXe = dX + (size_t)e * ld4h;
     if (e == 0) {
@@ -171,7 +178,7 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
             if (c < 3 * Hp) st4(dAe + c, f4zero());
             if (dx_overwrite) st4(dXe + c, f4zero());
         }
-        return;
+        continue;
     }
     const XRow xr = xrow(xt, e);
     const int b = FIRST ? 0 : __ldg(rp + e), en = FIRST ? 0 : __ldg(rp + e + 1);
@@ -221,6 +228,7 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
             st4(dXe + 2 * Hp + c, ld4(dXe + 2 * Hp + c) + dau);
             st4(dXe + 3 * Hp + c, ld4(dXe + 3 * Hp + c) + dafs);
         }
+    }
     }
     if (amax16 != nullptr) {
         // non-negative floats order like their bit patterns
@@ -443,14 +451,27 @@ int launch_zero2(float* a, float* b, size_t n, cudaStream_t st) {     // n % 4 =
     return check_launch("zero2");
 }
 
+// grid of the LSTM row kernels: one warp per row up to kCellGridBlocks blocks per SM (two residency rounds), grid-stride
+// beyond that (GGPM_CELL_BPS=n overrides; 0: one block per 8 rows, no striding — A/B timing)
 static inline int cell_blocks(int E1) { return ceil_div(E1, kCellWarps); }
+static inline int cell_blocks_persistent(int E1) {
+    static int bps = -1;
+    if (bps < 0) {
+        const char* e = getenv("GGPM_CELL_BPS");
+        bps = e != nullptr ? atoi(e) : kCellGridBlocks;
+    }
+    const int need = ceil_div(E1, kCellWarps);
+    if (bps <= 0) return need;
+    const int cap = bps * sm_count();
+    return need < cap ? need : cap;
+}
 
 int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          const float* gp, const float* c_prev, float* h_out, float* c_out, void* h16_hi, void* h16_lo,
                          cudaStream_t st) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_FWD, st, 0.0);
-    launch_pdl(first ? lstm_cell_fwd_kernel<true> : lstm_cell_fwd_kernel<false>, dim3(cell_blocks(E1)), dim3(kCellWarps * 32), 0,
+    launch_pdl(first ? lstm_cell_fwd_kernel<true> : lstm_cell_fwd_kernel<false>, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0,
                st, E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out, (uint2*)h16_hi, (uint2*)h16_lo);
     return check_launch("lstm_cell_fwd");
 }
@@ -458,7 +479,7 @@ int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const
 int launch_lstm_zgather(int E1, int Hp, const int* t_ptr, const int* t_row, const float* dA, const float* dP,
                         const float* amax16, const int* deg, void* z_hi, void* z_lo, float* scale_out, cudaStream_t st) {
     ProfScope prof(PROF_GATHER, st, 0.0);
-    launch_pdl(lstm_zgather_kernel, dim3(cell_blocks(E1)), dim3(kCellWarps * 32), 0, st, E1, Hp, t_ptr, t_row, dA, dP, amax16,
+    launch_pdl(lstm_zgather_kernel, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0, st, E1, Hp, t_ptr, t_row, dA, dP, amax16,
                deg, (uint4*)z_hi, (uint4*)z_lo, scale_out);
     return check_launch("lstm_zgather");
 }
@@ -469,7 +490,7 @@ int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const
                          cudaStream_t st) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_BWD, st, 0.0);
-    launch_pdl(first ? lstm_cell_bwd_kernel<true> : lstm_cell_bwd_kernel<false>, dim3(cell_blocks(E1)), dim3(kCellWarps * 32), 0,
+    launch_pdl(first ? lstm_cell_bwd_kernel<true> : lstm_cell_bwd_kernel<false>, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0,
                st, E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, (int)dx_overwrite, dP, dC_prev, amax16);
     return check_launch("lstm_cell_bwd");
 }
