@@ -65,6 +65,7 @@ class ClockSampler:
     def __init__(self, gpu_index):
         self.gpu, self.rows, self.stop_flag, self.thread, self.proc = gpu_index, [], False, None, None
         self.mode = None
+        self.period = float(os.environ.get("GGPM_BENCH_CLOCK_PERIOD", "0.2"))
 
     def _nvml_loop(self):
         import pynvml as nv
@@ -82,7 +83,7 @@ class ClockSampler:
                 self.rows.append((float(sm), float(self.max_sm), [n for n, bit in R if mask & bit]))
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(self.period)
 
     def _smi_loop(self):
         for line in self.proc.stdout:
@@ -113,6 +114,10 @@ class ClockSampler:
                 self.h = nv.nvmlDeviceGetHandleByIndex(phys)
             self.max_sm = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
             self.mode = "nvml"
+            # the first NVML query of a process takes ~30 ms inside the driver (measured) and would land in the
+            # timed region: pay for it here
+            nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+            nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
             self.thread = threading.Thread(target=self._nvml_loop, daemon=True)
             self.thread.start()
             return
@@ -291,6 +296,21 @@ def run_ours(args, workload):
             ms = float(t.item())
         return ms
 
+    # ---- settle the process before anything is timed (not part of W): the first steps of a fresh process on a fresh
+    # box pay for allocator growth, lazy module loading and clock ramp-up (a 2x slower first second was measured);
+    # run untimed steps until two consecutive ones agree within 5 % (at most 40)
+    # (ranks must run the same number of steps — the step holds a collective — so N > 1 runs a fixed 12)
+    prev = None
+    for i in range(40 if world == 1 else 12):
+        t0 = time.perf_counter()
+        step(*dev_batches[i % n_batches])
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if world == 1 and prev is not None and i >= 2 * n_batches and abs(dt - prev) <= 0.05 * prev:
+            break
+        prev = dt
+    barrier()
+
     # ---- device-resident throughput ("value") -------------------------------------------------------
     sampler = ClockSampler(local)
     if rank == 0:
@@ -310,18 +330,32 @@ def run_ours(args, workload):
     value = mols_per_step * args.steps / (ms / 1e3)
 
     # ---- end to end from pinned host buffers ("e2e") ------------------------------------------------
+    # (1) through the ingest API (ggpm_b200.ingest.PackedBatch): the batch was packed once at
+    #     preprocess time into one pinned int32 buffer; the step does ONE H2D copy, the encoder, a loss read-back;
+    # (2) through the reference's own make_cuda flow (ggpm/nnutils.py:210-214): one copy + one widening kernel per
+    #     tensor, index structures built on the device.
+    from ggpm_b200 import ingest
+    packed = [ingest.pack((t, g)) for t, g, _ in batches]
+    h2d = packed[0].nbytes
+
+    def e2e_step(i):
+        tree, graph = packed[i % n_batches].to_device(dev)
+        step(tree, graph, read_loss=True)
+    e2e_ms = timed(e2e_step, min(args.warmup, 3), args.steps)
+    e2e_value = mols_per_step * args.steps / (e2e_ms / 1e3)
+
     def pin(arrs):
         return [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() if not isinstance(a, list) else a for a in arrs]
     host_batches = [(pin(t), pin(g)) for t, g, _ in batches]
-    h2d = sum(a.numel() * a.element_size() for a in host_batches[0][0][:-1] + host_batches[0][1][:-1])
+    h2d_mc = sum(a.numel() * a.element_size() for a in host_batches[0][0][:-1] + host_batches[0][1][:-1])
 
-    def e2e_step(i):
+    def e2e_mc_step(i):
         t, g = host_batches[i % n_batches]
         tree = [a.to(dev, non_blocking=True).long() for a in t[:-1]] + [t[-1]]
         graph = [a.to(dev, non_blocking=True).long() for a in g[:-1]] + [g[-1]]
         step(tree, graph, read_loss=True)
-    e2e_ms = timed(e2e_step, min(args.warmup, 3), args.steps)
-    e2e_value = mols_per_step * args.steps / (e2e_ms / 1e3)
+    e2e_mc_ms = timed(e2e_mc_step, min(args.warmup, 3), args.steps)
+    e2e_mc_value = mols_per_step * args.steps / (e2e_mc_ms / 1e3)
 
     # ---- per-kernel-class timing for the roofline (separate instrumented pass, rank 0) --------------
     roofline, kernels = None, None
@@ -387,7 +421,13 @@ def run_ours(args, workload):
                              "activations (>> 126 MB L2) between forward and backward" % n_batches,
                        "shape_per_batch": stats},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
-                    "ms_per_step": e2e_ms / args.steps},
+                    "ms_per_step": e2e_ms / args.steps,
+                    "api": "ingest.PackedBatch.to_device (one pinned int32 buffer, packed ahead of time) -> "
+                           "HierMPNEncoder.forward -> backward -> loss.item()"},
+            "e2e_make_cuda": {"value": e2e_mc_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_mc),
+                              "d2h_bytes_per_step": 4, "ms_per_step": e2e_mc_ms / args.steps,
+                              "api": "reference flow: per-tensor pinned copy + .long() (make_cuda), index structures "
+                                     "built on the device"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roofline,

@@ -26,6 +26,23 @@ def _i32(t: torch.Tensor) -> torch.Tensor:
     return t.to(torch.int32).contiguous()
 
 
+def _message_graph(fmess, bgraph, n_nodes, n_table_rows, k2_offset=None) -> Fn.MessageGraph:
+    """bgraph CSR + per-message source / one-hot column ids; prepared on the host when the batch came through
+    ingest.PackedBatch, else derived here (fmess columns: src, dst, label, position — ggpm/mol_graph.py:262-270)"""
+    b = Fn.csr_from_padded(bgraph, fmess.shape[0])
+    cols = getattr(fmess, "_ggpm_cols", None)
+    if cols is not None:
+        src, k1, k2 = cols
+        if k2_offset is None:
+            k2 = None
+    else:
+        src, k1 = _i32(fmess[:, 0]), _i32(fmess[:, 2])
+        k2 = None if k2_offset is None else _i32(fmess[:, 3] + k2_offset)
+    mg = Fn.MessageGraph(b, src, k1, k2, n_nodes, n_table_rows)
+    mg._by_src = getattr(fmess, "_ggpm_by_src", None)
+    return mg
+
+
 def _public(t: torch.Tensor, H: int) -> torch.Tensor:
     """padded internal table -> fresh contiguous [rows, H] tensor"""
     return t if t.shape[1] == H else t[:, :H].contiguous()
@@ -92,9 +109,11 @@ class _TreeBatch:
         self.fnode = fnode
         self.cgraph = cgraph
         self.a = Fn.csr_from_padded(agraph, self.n_mess)
-        b = Fn.csr_from_padded(bgraph, self.n_mess)
-        self.mg = Fn.MessageGraph(b, _i32(fmess[:, 0]), _i32(fmess[:, 2]), None, self.n_nodes, MAX_POS)
-        self.roots = ints_to_device([st for st, le in scope], fnode.device)
+        self.mg = _message_graph(fmess, bgraph, self.n_nodes, MAX_POS)
+        roots = getattr(scope, "roots_dev", None)
+        if roots is None or roots.device != fnode.device:
+            roots = ints_to_device([st for st, le in scope], fnode.device)
+        self.roots = roots
 
 
 def _root_vectors(W_root, feat, incoming, roots, H):
@@ -144,8 +163,7 @@ class HierMPNEncoder(nn.Module):
         n_atoms, n_bonds = g_fnode.shape[0], g_fmess.shape[0]
         pad = (-self.atom_size) % 4                       # 16-byte rows: both uses below read it at this width
         atom_feat = nn.functional.pad(self.E_a, (0, pad)).index_select(0, g_fnode)
-        mg = Fn.MessageGraph(Fn.csr_from_padded(g_bgraph, n_bonds), _i32(g_fmess[:, 0]), _i32(g_fmess[:, 2]),
-                             _i32(g_fmess[:, 3] + N_BOND_TYPES), n_atoms, N_BOND_TYPES + MAX_POS)
+        mg = _message_graph(g_fmess, g_bgraph, n_atoms, N_BOND_TYPES + MAX_POS, k2_offset=N_BOND_TYPES)
         hatom, _, _ = self.graph_encoder.encode(atom_feat, atom_feat, mg, Fn.csr_from_padded(g_agraph, n_bonds),
                                                 self.atom_size, N_BOND_TYPES)
 

@@ -53,7 +53,11 @@ class CSR:
 
 
 def csr_from_padded(index: torch.Tensor, n_src: int, check: bool = False) -> CSR:
-    """index: [rows, width] int64 (what make_cuda yields, ggpm/nnutils.py:210-214) or int32, on the GPU."""
+    """index: [rows, width] int64 (what make_cuda yields, ggpm/nnutils.py:210-214) or int32, on the GPU.
+    Tensors that came out of ingest.PackedBatch.to_device() carry their CSR (built on the host, same encoding)."""
+    pre = getattr(index, "_ggpm_csr", None)
+    if pre is not None and pre.n_src == n_src and pre.row_ptr.device == index.device:
+        return pre
     _lib.require_device(index, "index tensor")
     if index.dtype not in (torch.int64, torch.int32):
         raise ValueError("index tensors must be int64 or int32, got %s" % index.dtype)

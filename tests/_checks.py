@@ -44,9 +44,13 @@ def run(model, meta, tree, graph):
     return model(tree, graph) if meta["kind"] == "hier" else model(tree)
 
 
-def check_forward_backward_golden(name, device):
+def check_forward_backward_golden(name, device, packed=False):
     meta, z, tree, graph = load_golden(name)
-    tree, graph = to_dev(tree, device), to_dev(graph, device)
+    if packed:      # through ingest.PackedBatch: one buffer, int32 views, index structures prepared on the host
+        from ggpm_b200 import ingest
+        tree, graph = ingest.PackedBatch.from_tensors(tree, graph if meta["kind"] == "hier" else None).to_device(device)
+    else:
+        tree, graph = to_dev(tree, device), to_dev(graph, device)
     model = build_model(meta, device)
     outs = run(model, meta, tree, graph)
     names = OUT_NAMES[meta["kind"]]

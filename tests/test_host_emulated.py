@@ -35,6 +35,13 @@ def test_forward_backward_matches_reference_golden(emu, name):
     C.check_forward_backward_golden(name, DEV)
 
 
+@pytest.mark.parametrize("name", ["hier_lstm_small", "hier_gru_small", "motif_lstm_small"])
+def test_packed_batch_path_matches_reference_golden(emu, name):
+    C.check_forward_backward_golden(name, DEV, packed=True)
+    # the packed path prepares every index structure on the host: no CSR kernels are launched
+    assert not [c for c in emu.calls if "csr" in c], sorted(set(emu.calls))
+
+
 def test_root_only_loss_leaves_tree_readout_without_grad(emu):
     C.check_root_only_loss(DEV)
 
