@@ -30,32 +30,37 @@ class GradBucket:
         self.numel = sum(p.numel() for p in self.params)
         self.flat = None
 
-    def pack(self) -> torch.Tensor:
+    def _views(self):
         dev = self.params[0].device
         if self.flat is None or self.flat.device != dev:
             self.flat = torch.zeros(self.numel, dtype=torch.float32, device=dev)
-        off = 0
-        for p in self.params:
-            n = p.numel()
-            if p.grad is None:
-                self.flat[off:off + n].zero_()
-            else:
-                self.flat[off:off + n].copy_(p.grad.reshape(-1))
-            off += n
+            self.views, off = [], 0
+            for p in self.params:
+                self.views.append(self.flat[off:off + p.numel()].view_as(p))
+                off += p.numel()
+        return self.views
+
+    def pack(self) -> torch.Tensor:
+        """gradients -> flat bucket: one multi-tensor copy (not one kernel per parameter)"""
+        views = self._views()
+        have = [(v, p.grad) for v, p in zip(views, self.params) if p.grad is not None]
+        none = [v for v, p in zip(views, self.params) if p.grad is None]
+        if have:
+            torch._foreach_copy_([v for v, _ in have], [g for _, g in have])
+        if none:
+            torch._foreach_zero_(none)
         return self.flat
 
     def unpack(self, scale: float = 1.0):
-        off = 0
-        for p in self.params:
-            n = p.numel()
-            g = self.flat[off:off + n].view_as(p)
+        views = self._views()
+        if scale != 1.0:
+            self.flat.mul_(scale)
+        have = [(p.grad, v) for v, p in zip(views, self.params) if p.grad is not None]
+        if have:
+            torch._foreach_copy_([g for g, _ in have], [v for _, v in have])
+        for v, p in zip(views, self.params):
             if p.grad is None:
-                p.grad = (g * scale).clone() if scale != 1.0 else g.clone()
-            else:
-                p.grad.copy_(g)
-                if scale != 1.0:
-                    p.grad.mul_(scale)
-            off += n
+                p.grad = v.clone()
 
     def all_reduce_mean(self, weight: float = 1.0, group=None):
         """sum of (weight * grad) over ranks divided by the sum of weights; weight = molecules in the
