@@ -358,8 +358,16 @@ def run_ours(args, workload):
     e2e_mc_value = mols_per_step * args.steps / (e2e_mc_ms / 1e3)
 
     # ---- per-kernel-class timing for the roofline (separate instrumented pass, rank 0) --------------
-    roofline, kernels = None, None
+    roofline, kernels, rooflines = None, None, None
     peaks = load_peaks()
+    traffic = {}
+    try:      # HBM bytes per launch from the committed ncu --set full capture (atom-layer launch of a cfg2 step)
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            tj = json.load(f)
+        if tj.get("workload") == args.workload:
+            traffic = tj.get("per_launch_bytes", {})
+    except Exception:
+        traffic = {}
     if rank == 0:
         lib = _lib.backend()
         _lib.call("ggpm_prof_enable", 1)
@@ -376,26 +384,33 @@ def run_ours(args, workload):
         kernels = {PROF_CLASSES[c]: {"ms_per_step": ms_c[c] / prof_steps, "launches_per_step": cnt_c[c] // prof_steps,
                                      "share": ms_c[c] / total} for c in range(n) if cnt_c[c]}
         gemm_classes = [c for c in (1, 2, 3) if cnt_c[c]]
+        # HBM-side classes: algorithmic bytes per step from SURVEY 8(d) (nnz-dependent part from the batch)
+        Hp = (H + 31) // 32 * 32
+        by = 0.0
+        for E, nnz, D in ((stats["Ea"], stats["nnz_bA"], workload["depthG"]),
+                          (stats["Et"], stats["nnz_bT"], workload["depthT"]),
+                          (stats["Et"], stats["nnz_bT"], workload["depthT"])):
+            by += D * (3.0 * nnz * Hp * 4 + 2.0 * E * Hp * 4 + 4.0 * nnz + 4.0 * E)
+
+        def class_roofline(c):
+            name = PROF_CLASSES[c]
+            if c in gemm_classes:
+                tf = work_c[c] / (ms_c[c] * 1e-3) / 1e12
+                return {"kernel": name, "bound": "tensor", "achieved": tf, "peak": peaks["bf16"], "unit": "TFLOP/s",
+                        "frac": tf / peaks["bf16"], "traffic": traffic.get(name),
+                        "flops_per_launch": work_c[c] / cnt_c[c], "avg_launch_ms": ms_c[c] / cnt_c[c],
+                        "executed_tensor_frac": 3.0 * tf / peaks["bf16"],
+                        "peak_kind": "dense bf16 cuBLAS, sustained, of " + peaks["src"] +
+                                     "; f16x3 executes 3 tensor FLOPs per algorithmic FLOP"}
+            gbs = by * prof_steps / (ms_c[c] * 1e-3) / 1e9
+            return {"kernel": name, "bound": "hbm", "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s",
+                    "frac": gbs / peaks["hbm"], "traffic": traffic.get(name), "avg_launch_ms": ms_c[c] / cnt_c[c],
+                    "peak_kind": "copy bandwidth, of " + peaks["src"]}
+
         top = max(range(n), key=lambda c: ms_c[c])
-        if top in gemm_classes:
-            tf = work_c[top] / (ms_c[top] * 1e-3) / 1e12
-            per_launch = work_c[top] / cnt_c[top]
-            roofline = {"kernel": PROF_CLASSES[top], "bound": "tensor", "achieved": tf, "peak": peaks["bf16"],
-                        "unit": "TFLOP/s", "frac": tf / peaks["bf16"], "traffic": None,
-                        "flops_per_launch": per_launch, "avg_launch_ms": ms_c[top] / cnt_c[top],
-                        "peak_kind": "dense bf16 cuBLAS, sustained, of " + peaks["src"]}
-        else:
-            # HBM-side classes: algorithmic bytes per step from SURVEY 8(d) (nnz-dependent part from the batch)
-            Hp = (H + 31) // 32 * 32
-            by = 0.0
-            for E, nnz, D in ((stats["Ea"], stats["nnz_bA"], workload["depthG"]),
-                              (stats["Et"], stats["nnz_bT"], workload["depthT"]),
-                              (stats["Et"], stats["nnz_bT"], workload["depthT"])):
-                by += D * (3.0 * nnz * Hp * 4 + 2.0 * E * Hp * 4 + 4.0 * nnz + 4.0 * E)
-            gbs = by * prof_steps / (ms_c[top] * 1e-3) / 1e9
-            roofline = {"kernel": PROF_CLASSES[top], "bound": "hbm", "achieved": gbs, "peak": peaks["hbm"],
-                        "unit": "GB/s", "frac": gbs / peaks["hbm"], "traffic": None,
-                        "avg_launch_ms": ms_c[top] / cnt_c[top], "peak_kind": "copy bandwidth, of " + peaks["src"]}
+        roofline = class_roofline(top)
+        # the other large classes, same definitions (the top class flips between cell_bwd and the gate GEMMs run to run)
+        rooflines = {PROF_CLASSES[c]: class_roofline(c) for c in (1, 3, 4, 5) if cnt_c[c] and c != top}
 
     # ---- CPU baseline on the host cores (rank 0, N = 1 only) ----------------------------------------
     cpu = None
@@ -431,6 +446,7 @@ def run_ours(args, workload):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roofline,
+            "rooflines_other": rooflines,
             "kernels": kernels,
             "algorithmic_tflops": flops * world / (ms / args.steps * 1e-3) / 1e12,
             "cpu_baseline": cpu,

@@ -50,6 +50,9 @@ SIGNATURES = {
     "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 27 + [I, P]),
     "ggpm_gru_fwd": (I, [I, I, I, I] + [P] * 13 + [I, P]),
     "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
+    "ggpm_tensorize_graph": (I, [I, P, P, I, P, P, P]),
+    "ggpm_tensorize_fetch": (I, [P] * 9),
+    "ggpm_tensorize_cgraph": (I, [I, I, P, P, P, P, P, P, P]),
 }
 
 _LIB = None
@@ -91,6 +94,14 @@ def call(name, *args):
         if isinstance(msg, bytes):
             msg = msg.decode(errors="replace")
         raise RuntimeError("%s failed (status %d): %s" % (name, status, msg))
+
+
+def call_host(name, *args):
+    """Invoke a host-only entry point of the real library (the index builder): never routed to a test backend."""
+    lib = _load()
+    status = getattr(lib, name)(*args)
+    if status != 0:
+        raise RuntimeError("%s failed (status %d): %s" % (name, status, lib.ggpm_last_error().decode(errors="replace")))
 
 
 def require_device(t: torch.Tensor, what: str = "tensor"):

@@ -225,6 +225,30 @@ int ggpm_gru_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const i
                  float* dX, float* dUz, float* dUr, float* dbr, float* dUh, float* dA, float* dS, float* dSg,
                  float* dPr, float* dHn, void* stream);
 
+/* ---- host-side index builder (no device work, no stream): SURVEY 8(f) rank 3 ----------------------------------
+ * Replaces MolGraph.tensorize_graph (ggpm/mol_graph.py:238-281: Python dict / list loops per edge over networkx
+ * graphs) and the cgraph assembly of MolGraph.tensorize (ggpm/mol_graph.py:211-222) for callers that hold the batch
+ * as flat int32 arrays.  Output layout is the reference's, bit for bit: 1-based ids, row 0 = padding, fnode[0] =
+ * fnode[1], edges enumerated by source node then insertion order, rows zero padded to (longest + 1) columns
+ * (create_pad_tensor, ggpm/nnutils.py:105-110); cgraph has no extra column.
+ *
+ * ggpm_tensorize_graph: node_off [n_mols+1], node_label [nodes, label_cols], edge_off [n_mols+1],
+ *   edges [n_edges, 4] = (u, v, label, position), u / v local to the molecule, insertion order.  Builds into
+ *   thread-local storage; sizes_out[6] = {N+1, E+1, agraph width, bgraph width, nnz(agraph), nnz(bgraph)}.
+ * ggpm_tensorize_fetch: copies the last result of this thread into caller arrays (any pointer may be NULL):
+ *   fnode [N+1, label_cols], fmess [E+1, 4], agraph [N+1, wa], bgraph [E+1, wb], scope [n_mols, 2] and the CSR of
+ *   both neighbour tables a_ptr [N+2], a_col [nnz_a], b_ptr [E+2], b_col [nnz_b].
+ * ggpm_tensorize_cgraph: cluster_off [n_motifs+1], cluster_atoms (local atom ids), motif_mol [n_motifs] (motifs
+ *   listed molecule by molecule), tree_scope / graph_scope [n_mols, 2]; *width_out = longest cluster; cgraph
+ *   [n_motifs+1, width] or NULL to query the width. */
+int ggpm_tensorize_graph(int n_mols, const int32_t* node_off, const int32_t* node_label, int label_cols,
+                         const int32_t* edge_off, const int32_t* edges, int32_t* sizes_out);
+int ggpm_tensorize_fetch(int32_t* fnode, int32_t* fmess, int32_t* agraph, int32_t* bgraph, int32_t* scope,
+                         int32_t* a_ptr, int32_t* a_col, int32_t* b_ptr, int32_t* b_col);
+int ggpm_tensorize_cgraph(int n_mols, int n_motifs, const int32_t* cluster_off, const int32_t* cluster_atoms,
+                          const int32_t* motif_mol, const int32_t* tree_scope, const int32_t* graph_scope,
+                          int32_t* width_out, int32_t* cgraph);
+
 #ifdef __cplusplus
 }
 #endif
