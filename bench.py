@@ -156,11 +156,11 @@ class ClockSampler:
 
 
 def make_batches(workload, n_batches, seed):
-    from ggpm_b200 import synth
+    from ggpm_b200 import synth, tensorize
     out = []
     for i in range(n_batches):
         mols = synth.random_batch(seed * 1000 + i, workload["batch"])
-        tree, graph = synth.tensorize(mols)
+        tree, graph = tensorize.tensorize(mols)      # C++ index builder (bit-identical to synth.tensorize)
         out.append((tree, graph, synth.batch_stats(tree, graph)))
     return out
 
