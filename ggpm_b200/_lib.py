@@ -50,6 +50,8 @@ SIGNATURES = {
     "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 27 + [I, P]),
     "ggpm_gru_fwd": (I, [I, I, I, I] + [P] * 13 + [I, P]),
     "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
+    "ggpm_rsample_fwd": (I, [P, I, I, P, I, I, I, P, I, P, P, P]),
+    "ggpm_rsample_bwd": (I, [P, I, I, P, I, I, I, P, I, P, P, I, I, P]),
     "ggpm_tensorize_graph": (I, [I, P, P, I, P, P, P]),
     "ggpm_tensorize_fetch": (I, [P] * 9),
     "ggpm_tensorize_cgraph": (I, [I, I, P, P, P, P, P, P, P]),

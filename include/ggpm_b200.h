@@ -225,6 +225,17 @@ int ggpm_gru_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const i
                  float* dX, float* dUz, float* dUr, float* dbr, float* dUh, float* dA, float* dS, float* dSg,
                  float* dPr, float* dHn, void* stream);
 
+/* ---- latent head --------------------------------------------------------------------------
+ * Element-wise part of PropertyVAE.rsample / HierVAE.rsample (ggpm/property_vae.py:26-34) after the fused
+ * [W_mean; W_var] projection.  Y [B, ldy] holds z_mean in columns [0, L) and the variance pre-activation v in columns
+ * [var_off, var_off + L):  z_log_var = -|v|,  kl = -0.5 sum(1 + z_log_var - m^2 - exp(z_log_var)) / B (deterministic
+ * two-stage sum; row_kl [B] is scratch),  z = m + exp(z_log_var / 2) eps, or z = m when eps is NULL.
+ * Backward: dY [B, width] = [dm | .. | dv | 0 ..] from dz [B, L] (may be NULL) and the device scalar dkl (may be NULL). */
+int ggpm_rsample_fwd(const float* Y, int ldy, int var_off, const float* eps, int ld_eps, int B, int L, float* z, int ldz,
+                     float* kl, float* row_kl, void* stream);
+int ggpm_rsample_bwd(const float* Y, int ldy, int var_off, const float* eps, int ld_eps, int B, int L, const float* dz,
+                     int ld_dz, const float* dkl, float* dY, int ld_dy, int width, void* stream);
+
 /* ---- host-side index builder (no device work, no stream): SURVEY 8(f) rank 3 ----------------------------------
  * Replaces MolGraph.tensorize_graph (ggpm/mol_graph.py:238-281: Python dict / list loops per edge over networkx
  * graphs) and the cgraph assembly of MolGraph.tensorize (ggpm/mol_graph.py:211-222) for callers that hold the batch

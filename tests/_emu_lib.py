@@ -208,6 +208,34 @@ class EmuLib:
         _tab(dZ, rows, ld_dz, width).copy_(g.float())
         return 0
 
+    # -- latent head (csrc/latent.cu) ---------------------------------------------------------------
+    def ggpm_rsample_fwd(self, Y, ldy, var_off, eps, ld_eps, B, L, z, ldz, kl, row_kl, stream):
+        self._tick("rsample_fwd")
+        y = _tab(Y, B, ldy, var_off + L).to(DT)
+        m, lv = y[:, :L], -y[:, var_off:var_off + L].abs()
+        rows = (1.0 + lv - m * m - torch.exp(lv)).sum(1)
+        _f(row_kl, B).copy_(rows.float())
+        _f(kl, 1)[0] = float(-0.5 * rows.sum() / B)
+        out = m if not eps else m + torch.exp(lv / 2) * _tab(eps, B, ld_eps, L).to(DT)
+        _tab(z, B, ldz, L).copy_(out.float())
+        return 0
+
+    def ggpm_rsample_bwd(self, Y, ldy, var_off, eps, ld_eps, B, L, dz, ld_dz, dkl, dY, ld_dy, width, stream):
+        self._tick("rsample_bwd")
+        y = _tab(Y, B, ldy, var_off + L).to(DT)
+        m, v = y[:, :L], y[:, var_off:var_off + L]
+        lv = -v.abs()
+        gk = float(_f(dkl, 1)[0]) / B if dkl else 0.0
+        g = _tab(dz, B, ld_dz, L).to(DT) if dz else torch.zeros(B, L, dtype=DT)
+        dlv = -0.5 * gk * (1.0 - torch.exp(lv))
+        if eps and dz:
+            dlv = dlv + g * _tab(eps, B, ld_eps, L).to(DT) * 0.5 * torch.exp(lv / 2)
+        out = torch.zeros(B, width, dtype=DT)
+        out[:, :L] = g + gk * m
+        out[:, var_off:var_off + L] = -torch.sign(v) * dlv
+        _tab(dY, B, ld_dy, width).copy_(out.float())
+        return 0
+
     def ggpm_colsum(self, X, ld_x, rows, width, out, accumulate, stream):
         self._tick("colsum")
         s = _tab(X, rows, ld_x, width).to(DT).sum(0)
