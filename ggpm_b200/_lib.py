@@ -30,6 +30,7 @@ SIGNATURES = {
     "ggpm_csr_from_padded": (I, [P, I, I, I, I, P, P, P, P]),
     "ggpm_csr_transpose": (I, [P, P, I, I, P, P, P, P, P]),
     "ggpm_gather_sum": (I, [P, I, P, P, P, I, I, I, I, P]),
+    "ggpm_embedding_bwd": (I, [P, I, P, I, c_longlong, I, I, I, P, I, P]),
     "ggpm_gemm": (I, [P, c_longlong, c_longlong, P, c_longlong, c_longlong, P, I, I, I, I, c_float, P, I, I, I, P]),
     "ggpm_gemm_fused": (I, [P, c_longlong, c_longlong, P, c_longlong, c_longlong, P, I, I, I, I, c_float, P, I, I, I,
                             P, P, P, P, I, I, P, c_longlong, I, P, P, P]),
@@ -43,6 +44,7 @@ SIGNATURES = {
     "ggpm_split_pad": (I, [P, I, I, I, I, I, P, P, P, P, P, P, P]),
     "ggpm_split_unpad": (I, [P, I, I, I, P, P, P, P, P, P, P]),
     "ggpm_act_bwd": (I, [P, I, P, I, P, I, I, I, I, I, P]),
+    "ggpm_bias_act": (I, [P, I, I, I, P, I, I, P]),
     "ggpm_colsum": (I, [P, I, I, I, P, I, P]),
     "ggpm_table_wgrad": (I, [P, I, I, I, P, P, P, I, I, P]),
     "ggpm_lstm_plan": (I, [I, I]),

@@ -371,6 +371,23 @@ __global__ void act_bwd_kernel(const float* __restrict__ dY, int ld_dy, const fl
     dZ[(size_t)r * ld_dz + c] = g;
 }
 
+// in-place epilogue of a linear layer whose product was accumulated by K-split partial sums:
+// C = act(C + bias), optional zero row 0 (the fused GEMM epilogue can only do this on whole-K tiles)
+__global__ void bias_act_kernel(float* __restrict__ C, int ldc, int rows, int width, const float* __restrict__ bias, int act,
+                                int zero_row0) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int w4 = width >> 2;
+    if (i >= (long long)rows * w4) return;
+    const int r = (int)(i / w4), c = (int)(i % w4) * 4;
+    float4 x = ld4(C + (size_t)r * ldc + c);
+    if (bias != nullptr) x += ldg4(bias + c);
+    if (act == GGPM_ACT_RELU) x = make_float4(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f), fmaxf(x.z, 0.f), fmaxf(x.w, 0.f));
+    else if (act == GGPM_ACT_TANH) x = tanh4(x);
+    else if (act == GGPM_ACT_SIGMOID) x = sigmoid4(x);
+    if (zero_row0 && r == 0) x = f4zero();
+    st4(C + (size_t)r * ldc + c, x);
+}
+
 constexpr int kColsumRows = 256;
 __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X, int ld_x, int rows, int width,
                                                      float* __restrict__ out) {
@@ -540,6 +557,16 @@ extern "C" int ggpm_act_bwd(const float* dY, int ld_dy, const float* Y, int ld_y
     act_bwd_kernel<<<(unsigned)ceil_div_ll(n, 256), 256, 0, (cudaStream_t)stream>>>(dY, ld_dy, Y, ld_y, dZ, ld_dz, rows,
                                                                                  width, act, zero_row0);
     return check_launch("act_bwd");
+}
+
+extern "C" int ggpm_bias_act(float* C, int ldc, int rows, int width, const float* bias, int act, int zero_row0, void* stream) {
+    GGPM_REQUIRE(C, "bias_act: null pointer");
+    GGPM_REQUIRE(width % 4 == 0 && ldc % 4 == 0 && ((uintptr_t)C & 15) == 0 && (bias == nullptr || ((uintptr_t)bias & 15) == 0),
+                 "bias_act: width / ld must be multiples of 4 and the pointers 16-byte aligned");
+    if (rows <= 0 || width <= 0) return 0;
+    const long long n = (long long)rows * (width / 4);
+    bias_act_kernel<<<(unsigned)ceil_div_ll(n, 256), 256, 0, (cudaStream_t)stream>>>(C, ldc, rows, width, bias, act, zero_row0);
+    return check_launch("bias_act");
 }
 
 extern "C" int ggpm_colsum(const float* X, int ld_x, int rows, int width, float* out, int accumulate, void* stream) {

@@ -61,6 +61,23 @@ gather_sum_kernel(const float* __restrict__ table, int ld_t, const int* __restri
     }
 }
 
+// dW[idx[r]] += dOut[r]: gradient of an embedding lookup (nn.Embedding of E_c / E_i, ggpm/encoder.py:62-66,98,111).
+// One warp per looked-up row, fp32 reductions into the (pre-zeroed) table; ids are read in place from a strided
+// int32 / int64 column (fnode[:, 0] or fnode[:, 1]).
+template <typename IdxT>
+__global__ void __launch_bounds__(256)
+embedding_bwd_kernel(const float* __restrict__ dOut, int ld, const IdxT* __restrict__ idx, long long idx_stride, int rows,
+                     int width, int n_table_rows, float* __restrict__ dW, int ldw) {
+    const int lane = threadIdx.x & 31;
+    const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (r >= rows) return;
+    const long long k = (long long)idx[(long long)r * idx_stride];
+    if (k < 0 || k >= n_table_rows) return;
+    const float* g = dOut + (size_t)r * ld;
+    float* w = dW + (size_t)k * ldw;
+    for (int c = lane; c < width; c += 32) atomicAdd(w + c, g[c]);
+}
+
 int launch_gather_sum(const float* table, int ld_t, const int* row_ptr, const int* col, float* out, int ld_o,
                       int rows, int width, bool accumulate, cudaStream_t st) {
     GGPM_REQUIRE(width % 4 == 0 && ld_t % 4 == 0 && ld_o % 4 == 0, "gather_sum: width/ld must be multiples of 4 floats");
@@ -78,6 +95,22 @@ int launch_gather_sum(const float* table, int ld_t, const int* row_ptr, const in
 }
 
 }  // namespace ggpm
+
+extern "C" int ggpm_embedding_bwd(const float* dOut, int ld, const void* idx, int idx_is_64bit, long long idx_stride,
+                                  int rows, int width, int n_table_rows, float* dW, int ldw, void* stream) {
+    GGPM_REQUIRE(dOut && idx && dW && width >= 1 && n_table_rows >= 1, "embedding_bwd: bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    GGPM_CUDA(cudaMemsetAsync(dW, 0, sizeof(float) * ((size_t)(n_table_rows - 1) * ldw + width), st));
+    if (rows <= 0) return 0;
+    ggpm::ProfScope prof(ggpm::PROF_MISC, st, 0.0);
+    if (idx_is_64bit)
+        ggpm::embedding_bwd_kernel<long long><<<ggpm::ceil_div(rows, 8), 256, 0, st>>>(dOut, ld, (const long long*)idx, idx_stride, rows,
+                                                                                   width, n_table_rows, dW, ldw);
+    else
+        ggpm::embedding_bwd_kernel<int><<<ggpm::ceil_div(rows, 8), 256, 0, st>>>(dOut, ld, (const int*)idx, idx_stride, rows, width,
+                                                                             n_table_rows, dW, ldw);
+    return ggpm::check_launch("embedding_bwd");
+}
 
 extern "C" int ggpm_gather_sum(const float* table, int ld_table, const int32_t* row_ptr, const int32_t* col,
                                float* out, int ld_out, int rows, int width, int accumulate, void* stream) {

@@ -43,6 +43,17 @@ def _message_graph(fmess, bgraph, n_nodes, n_table_rows, k2_offset=None) -> Fn.M
     return mg
 
 
+def _embed(seq, ids):
+    """E_c / E_i lookup (ggpm/encoder.py:98,111).  The reference calls the nn.Sequential(Embedding, Dropout) module —
+    possibly the decoder's, after tie_embedding; a plain Embedding + Dropout pair is evaluated as the same lookup and the
+    same dropout module, with the library's embedding backward; anything else is called as a module."""
+    if (isinstance(seq, nn.Sequential) and len(seq) == 2 and type(seq[0]) is nn.Embedding and type(seq[1]) is nn.Dropout
+            and seq[0].padding_idx is None and seq[0].max_norm is None and not seq[0].scale_grad_by_freq
+            and not seq[0].sparse and seq[0].weight.dtype == torch.float32 and ids.dim() == 1):
+        return seq[1](Fn.embedding_rows(seq[0].weight, ids))
+    return seq(ids)
+
+
 def _public(t: torch.Tensor, H: int) -> torch.Tensor:
     """padded internal table -> fresh contiguous [rows, H] tensor"""
     return t if t.shape[1] == H else t[:, :H].contiguous()
@@ -168,7 +179,7 @@ class HierMPNEncoder(nn.Module):
                                                 self.atom_size, N_BOND_TYPES)
 
         # attachment layer (embed_inter, :96-107)
-        attach_emb = self.E_i(tb.fnode[:, 1])
+        attach_emb = _embed(self.E_i, tb.fnode[:, 1])
         atoms_of_motif = Fn.gather_sum(hatom, Fn.csr_from_padded(tb.cgraph, n_atoms))
         wi = self.W_i[0].weight
         E = attach_emb.shape[1]
@@ -178,7 +189,7 @@ class HierMPNEncoder(nn.Module):
         hinter, _, _ = self.inter_encoder.encode(inter_feat, inter_feat, tb.mg, tb.a, H, MAX_POS)
 
         # motif layer (embed_tree, :109-117)
-        motif_emb = self.E_c(tb.fnode[:, 0])
+        motif_emb = _embed(self.E_c, tb.fnode[:, 0])
         wc = self.W_c[0].weight
         E = motif_emb.shape[1]
         tree_feat = Fn.linear_act_split([motif_emb, hinter], wc, [E, wc.shape[1] - E], self.W_c[0].bias,
@@ -214,8 +225,8 @@ class MotifEncoder(nn.Module):
     def forward(self, tree_tensors):
         H = self.hidden_size
         tb = _TreeBatch(tree_tensors)
-        motif_emb = self.E_c(tb.fnode[:, 0])         # node feature of the read-out (embed_tree, :305-317)
-        attach_emb = self.E_i(tb.fnode[:, 1])        # feeds the message inputs
+        motif_emb = _embed(self.E_c, tb.fnode[:, 0])         # node feature of the read-out (embed_tree, :305-317)
+        attach_emb = _embed(self.E_i, tb.fnode[:, 1])        # feeds the message inputs
         node, _, incoming = self.tree_encoder.encode(motif_emb, attach_emb, tb.mg, tb.a, H, MAX_POS)
         root = _root_vectors(self.W_root, motif_emb, incoming, tb.roots, H)
         return root, _public(node, H)

@@ -132,6 +132,34 @@ def gather_sum(table: torch.Tensor, csr: CSR) -> torch.Tensor:
     return GatherSum.apply(table, csr)
 
 
+class EmbeddingRows(torch.autograd.Function):
+    """weight[idx] with the library's scatter-add backward (torch's dense embedding backward takes 150 us for the
+    3 k motif rows of a cfg2 batch; this one 5 us).  idx: 1-D int32 / int64, any stride."""
+
+    @staticmethod
+    def forward(ctx, weight, idx):
+        ctx.save_for_backward(idx)
+        ctx.shape = tuple(weight.shape)
+        return weight.index_select(0, idx if idx.is_contiguous() else idx.contiguous())
+
+    @staticmethod
+    def backward(ctx, dout):
+        (idx,) = ctx.saved_tensors
+        V, E = ctx.shape
+        dout = dout if dout.stride(1) == 1 else dout.contiguous()
+        dW = torch.empty(V, E, dtype=torch.float32, device=dout.device)
+        _lib.require_device(idx, "embedding ids")
+        call("ggpm_embedding_bwd", fptr(dout), _row_stride(dout), idx.data_ptr(), int(idx.dtype == torch.int64),
+             idx.stride(0) if idx.numel() > 1 else 1, idx.numel(), E, V, fptr(dW), E, stream_ptr(dout.device))
+        return dW, None
+
+
+def embedding_rows(weight: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    if idx.dim() != 1 or idx.dtype not in (torch.int32, torch.int64):
+        raise ValueError("embedding ids must be a 1-D int32 / int64 tensor")
+    return EmbeddingRows.apply(weight, idx)
+
+
 # ----------------------------------------------------------------------------------------------
 # dense layers
 # ----------------------------------------------------------------------------------------------
@@ -267,10 +295,19 @@ class LinearAct(torch.autograd.Function):
         n = len(ops) // 2
         As, Ws = ops[:n], ops[n:]
         out = None
+        M, N = As[0].shape[0], Ws[0].shape[0]
+        epilogue = bias is not None or act != ACT_NONE or zero_row0
+        # Fewer output tiles than SMs: a GEMM with the fused epilogue can only hand out whole-K tiles (24 CTAs at
+        # 3 k rows: 62 us measured), a plain one is cut along K over all SMs (20 us); the epilogue then runs as one
+        # element-wise pass (3 us).  Large products keep the fused epilogue.
+        two_step = epilogue and N % 4 == 0 and ((M + 127) // 128) * ((N + 255) // 256) < 148
         for i, (A, W) in enumerate(zip(As, Ws)):
-            last = i == n - 1
+            last = (i == n - 1) and not two_step
             out = gemm_nt(A, W, out=out, beta=0.0 if i == 0 else 1.0, bias=bias if last else None,
                           act=act if last else ACT_NONE, zero_row0=zero_row0 and last, out_width=out_width)
+        if two_step:
+            call("ggpm_bias_act", fptr(out), _row_stride(out), M, N, None if bias is None else fptr(bias), act,
+                 int(zero_row0), stream_ptr(out.device))
         ctx.act, ctx.zero_row0, ctx.n, ctx.N = act, zero_row0, n, Ws[0].shape[0]
         ctx.has_bias = bias is not None
         ctx.save_for_backward(out, *ops)

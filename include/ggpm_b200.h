@@ -73,6 +73,12 @@ int ggpm_csr_transpose(const int32_t* row_ptr, const int32_t* col, int rows, int
 int ggpm_gather_sum(const float* table, int ld_table, const int32_t* row_ptr, const int32_t* col,
                     float* out, int ld_out, int rows, int width, int accumulate, void* stream);
 
+/* dW [n_table_rows, ldw] = 0; dW[idx[r]] += dOut[r, :width] — backward of the embedding lookups E_c / E_i
+ * (nn.Embedding, ggpm/encoder.py:62-66 used at :98,111).  idx: int32 or int64 ids read in place with element stride
+ * idx_stride (a column of fnode); ids outside [0, n_table_rows) are skipped. */
+int ggpm_embedding_bwd(const float* dOut, int ld, const void* idx, int idx_is_64bit, long long idx_stride, int rows,
+                       int width, int n_table_rows, float* dW, int ldw, void* stream);
+
 /* ---- dense layers --------------------------------------------------------------------------------
  * C[M,N] = act( A(M,K) * B(K,N) + beta*C + bias[n] ), row 0 optionally forced to 0.
  * A(m,k) = A[m*sam + k*sak], B(k,n) = B[k*sbk + n*sbn] (one stride of each operand must be 1).
@@ -155,6 +161,10 @@ int ggpm_split_unpad(float* dW, int N, int K, int n_pieces, const int* c0, const
 /* dZ = dY * act'(Y) with row 0 optionally zeroed (backward of the fused epilogue above). */
 int ggpm_act_bwd(const float* dY, int ld_dy, const float* Y, int ld_y, float* dZ, int ld_dz, int rows,
                  int width, int act, int zero_row0, void* stream);
+
+/* C[rows, width] = act(C + bias) in place, optional zero row 0: the epilogue of a linear layer (nn.Linear + ReLU /
+ * Tanh + mask, ggpm/encoder.py:33-38) whose product was accumulated from K-split partial sums. */
+int ggpm_bias_act(float* C, int ldc, int rows, int width, const float* bias, int act, int zero_row0, void* stream);
 
 /* out[c] (+)= sum_r X[r, c]  (bias gradients) */
 int ggpm_colsum(const float* X, int ld_x, int rows, int width, float* out, int accumulate, void* stream);

@@ -236,6 +236,31 @@ class EmuLib:
         _tab(dY, B, ld_dy, width).copy_(out.float())
         return 0
 
+    def ggpm_embedding_bwd(self, dOut, ld, idx, is64, idx_stride, rows, width, n_tab, dW, ldw, stream):
+        self._tick("embedding_bwd")
+        n = (rows - 1) * idx_stride + 1 if rows > 0 else 0
+        a = _arr(idx, n, ctypes.c_int64 if is64 else ctypes.c_int32, np.int64 if is64 else np.int32)
+        ids = torch.from_numpy(a.astype(np.int64))[::idx_stride]
+        w = _tab(dW, n_tab, ldw, width)
+        acc = torch.zeros(n_tab, width, dtype=DT)
+        if rows > 0:
+            acc.index_add_(0, ids, _tab(dOut, rows, ld, width).to(DT))
+        w.copy_(acc.float())
+        return 0
+
+    def ggpm_bias_act(self, C, ldc, rows, width, bias, act, zero_row0, stream):
+        self._tick("bias_act")
+        assert width % 4 == 0 and ldc % 4 == 0 and C % 16 == 0
+        c = _tab(C, rows, ldc, width)
+        x = c.to(DT)
+        if bias:
+            x = x + _f(bias, width).to(DT)
+        x = torch.relu(x) if act == 1 else torch.tanh(x) if act == 2 else torch.sigmoid(x) if act == 3 else x
+        if zero_row0:
+            x[0] = 0
+        c.copy_(x.float())
+        return 0
+
     def ggpm_colsum(self, X, ld_x, rows, width, out, accumulate, stream):
         self._tick("colsum")
         s = _tab(X, rows, ld_x, width).to(DT).sum(0)
