@@ -411,14 +411,15 @@ __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X
 }
 
 constexpr int kTabRows = 32;      // max table rows held in shared memory
-constexpr int kTabChunk = 512;    // message rows per block
+constexpr int kTabChunk = 128;    // message rows per block
 __global__ void __launch_bounds__(256)
 table_wgrad_kernel(const float* __restrict__ dX, int ld_dx, int rows, int width, const int* __restrict__ k1,
                    const int* __restrict__ k2, float* __restrict__ dT, int ld_dt, int ntab) {
-    // block: 128 columns (32 lanes x float4) x 8 warps over a chunk of rows; accumulate per table row in smem
+    // block: 128 columns (32 lanes x float4) x 8 warps over a chunk of rows; accumulate per table row in smem.
+    // Column lane*4 + i of a table row lives at word i*32 + lane, so the 32 lanes of one atomic hit 32 banks.
     __shared__ float acc[kTabRows][128];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < kTabRows * 128; i += blockDim.x) (&acc[0][0])[i] = 0.f;
+    for (int i = threadIdx.x; i < ntab * 128; i += blockDim.x) (&acc[0][0])[i] = 0.f;
     __syncthreads();
     const int c = blockIdx.x * 128 + lane * 4;
     const int r0 = blockIdx.y * kTabChunk, r1 = min(rows, r0 + kTabChunk);
@@ -426,23 +427,24 @@ table_wgrad_kernel(const float* __restrict__ dX, int ld_dx, int rows, int width,
         for (int r = r0 + w; r < r1; r += 8) {
             const float4 v = ld4(dX + (size_t)r * ld_dx + c);
             const int a = __ldg(k1 + r);
-            atomicAdd(&acc[a][lane * 4 + 0], v.x);
-            atomicAdd(&acc[a][lane * 4 + 1], v.y);
-            atomicAdd(&acc[a][lane * 4 + 2], v.z);
-            atomicAdd(&acc[a][lane * 4 + 3], v.w);
+            atomicAdd(&acc[a][lane], v.x);
+            atomicAdd(&acc[a][32 + lane], v.y);
+            atomicAdd(&acc[a][64 + lane], v.z);
+            atomicAdd(&acc[a][96 + lane], v.w);
             if (k2) {
                 const int b = __ldg(k2 + r);
-                atomicAdd(&acc[b][lane * 4 + 0], v.x);
-                atomicAdd(&acc[b][lane * 4 + 1], v.y);
-                atomicAdd(&acc[b][lane * 4 + 2], v.z);
-                atomicAdd(&acc[b][lane * 4 + 3], v.w);
+                atomicAdd(&acc[b][lane], v.x);
+                atomicAdd(&acc[b][32 + lane], v.y);
+                atomicAdd(&acc[b][64 + lane], v.z);
+                atomicAdd(&acc[b][96 + lane], v.w);
             }
         }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < ntab * 128; i += blockDim.x) {
-        int k = i >> 7, cc = blockIdx.x * 128 + (i & 127);
-        float v = acc[k][i & 127];
+        const int k = i >> 7, word = i & 127;
+        const int cc = blockIdx.x * 128 + (word & 31) * 4 + (word >> 5);
+        const float v = acc[k][word];
         if (cc < width && v != 0.f) atomicAdd(dT + (size_t)k * ld_dt + cc, v);
     }
 }

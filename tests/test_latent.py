@@ -133,7 +133,7 @@ def test_cuda_repeatable_and_noise_comes_from_the_device_generator():
         outs.append(latent.rsample(z, Wm, Wv, True))
     # same seed -> same noise; the projection is summed from K-split partial sums (fp32 reductions), so repeats agree
     # to rounding, not bit for bit
-    assert all(_rel(o[0], outs[0][0].double().cpu().numpy()) <= 1e-6 and _rel(o[1], outs[0][1].double().cpu().numpy()) <= 1e-6
+    assert all(_rel(o[0], outs[0][0].detach().double().cpu().numpy()) <= 1e-6 and _rel(o[1], outs[0][1].detach().double().cpu().numpy()) <= 1e-6
                for o in outs[1:])
     torch.manual_seed(11)
     eps = torch.randn(256, 24, device="cuda")

@@ -1,7 +1,7 @@
 set -x
 B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --profile-step"
-$B > gpurun_out/s31_plain.log 2>&1 && ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/s31_launches.csv $B > gpurun_out/s31_ncu1.log 2>&1
-python - <<'PY' > gpurun_out/s31_gaps.txt 2>&1
+$B > gpurun_out/s47_plain.log 2>&1 && ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/s47_launches.csv $B > gpurun_out/s47_ncu1.log 2>&1
+python - <<'PY' > gpurun_out/s47_gaps.txt 2>&1
 import torch, time, sys
 sys.path.insert(0,'.')
 import bench, ggpm_b200
@@ -11,7 +11,8 @@ w = bench.WORKLOADS['cfg2']; H=w['hidden']
 torch.manual_seed(0)
 model = ggpm_b200.HierMPNEncoder(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H, 20, 20, 0.1).cuda().train()
 bs = bench.make_batches(w, 2, 1)
-db = [nnutils.make_cuda((t,g)) for t,g,_ in bs]
+from ggpm_b200 import ingest
+db = [ingest.pack((t,g)).to_device("cuda") for t,g,_ in bs]
 def step(i):
     model.zero_grad(set_to_none=True)
     model(*db[i%2])[0].sum().backward()

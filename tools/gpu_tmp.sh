@@ -1,7 +1,9 @@
-T=s46
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/${T}_pytest.log
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
-for r in packed make_cuda packed; do
-timeout 600 python bench.py --no-cpu-baseline --resident $r > gpurun_out/${T}_b_$r.json 2> gpurun_out/${T}_b.err; echo "exit $?"; tail -2 gpurun_out/${T}_b.err
-python tools/bench_summary.py gpurun_out/${T}_b_$r.json | grep mol
+T=s48
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest exit $?"; tail -2 gpurun_out/${T}_pytest.log
+for wl in cfg2 cfg3s; do
+for cfg in "0 0 0" "128 0 0" "0 128 0" "0 0 128" "128 128 128"; do
+set -- $cfg
+GGPM_F16_BN_FWD=$1 GGPM_F16_BN_DGRAD=$2 GGPM_F16_BN_WGRAD=$3 timeout 600 python bench.py --workload $wl --no-cpu-baseline --steps 5 > gpurun_out/${T}_b.json 2> gpurun_out/${T}_b.err
+echo "$wl fwd=$1 dgrad=$2 wgrad=$3: $(python tools/bench_summary.py gpurun_out/${T}_b.json | grep 'mol\|gemm' | tr '\n' ' ')"
+done
 done
