@@ -1,9 +1,6 @@
-T=s48
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest exit $?"; tail -2 gpurun_out/${T}_pytest.log
-for wl in cfg2 cfg3s; do
-for cfg in "0 0 0" "128 0 0" "0 128 0" "0 0 128" "128 128 128"; do
-set -- $cfg
-GGPM_F16_BN_FWD=$1 GGPM_F16_BN_DGRAD=$2 GGPM_F16_BN_WGRAD=$3 timeout 600 python bench.py --workload $wl --no-cpu-baseline --steps 5 > gpurun_out/${T}_b.json 2> gpurun_out/${T}_b.err
-echo "$wl fwd=$1 dgrad=$2 wgrad=$3: $(python tools/bench_summary.py gpurun_out/${T}_b.json | grep 'mol\|gemm' | tr '\n' ' ')"
-done
-done
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/s51_n2.json 2> gpurun_out/s51_n2.err; echo "N=2 exit $?"; tail -2 gpurun_out/s51_n2.err
+python tools/bench_summary.py gpurun_out/s51_n2.json | grep mol
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29534 bench.py --impl reference --gpus 2 --steps 2 --warmup 1 > gpurun_out/s51_ref_n2.json 2> gpurun_out/s51_ref_n2.err; echo "ref N=2 exit $?"
+tail -1 gpurun_out/s51_ref_n2.json | cut -c1-200
+timeout 600 python bench.py > gpurun_out/s51_n1.json 2> gpurun_out/s51_n1.err; echo "N=1 exit $?"
+python tools/bench_summary.py gpurun_out/s51_n1.json | grep mol
