@@ -928,7 +928,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
             tc::fence_before_sync();
             tc::mbar_arrive(acc_empty_bar(b));
         }
-        if (lane == 0) tc::bulk_wait_read<0>();      // the boxes have been read out; the writes complete with the grid
+        // every bulk store / reduce of this warp has been performed before the CTA retires: the next grid may already be
+        // resident (programmatic dependent launch) and reads C right after its griddepcontrol.wait
+        if (lane == 0) tc::bulk_wait_all();
         if (warp == EPI_WARP0 && lane == 0) F16_STAMP(5);
     }
     tc::fence_before_sync();
