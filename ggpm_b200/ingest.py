@@ -257,3 +257,52 @@ def pack(tensors, pin: Optional[bool] = None) -> PackedBatch:
 def make_cuda_packed(tensors, device=None):
     """Drop-in for make_cuda (ggpm/nnutils.py:210-214) on a batch that was not packed ahead of time: pack, one copy."""
     return pack(tensors).to_device(device)
+
+
+class DeviceLoader:
+    """Keeps ``depth`` packed batches in flight: the host-to-device copy of batch i+1 runs on a side stream while batch
+    i is being encoded (what the DataLoader + make_cuda pair of the reference cannot do: its copies are pageable and
+    its index tensors are widened on the compute stream, ggpm/nnutils.py:201-214).  Iterating yields
+    ``(tree_tensors, graph_tensors)`` exactly like ``PackedBatch.to_device()``; the compute stream waits only for the
+    copy of the batch it is about to use."""
+
+    def __init__(self, batches, device=None, depth: int = 2):
+        if device is None:
+            from .nnutils import default_device
+            device = default_device()
+        self.device = torch.device(device)
+        self.depth = max(1, int(depth))
+        self._it = iter(batches)
+        self._queue = []
+        self._copy_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+
+    def _enqueue(self) -> bool:
+        try:
+            pb = next(self._it)
+        except StopIteration:
+            return False
+        if self._copy_stream is None:
+            self._queue.append((pb, pb.host.to(self.device), None))
+            return True
+        with torch.cuda.stream(self._copy_stream):
+            buf = pb.host.to(self.device, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+        self._queue.append((pb, buf, ev))
+        return True
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        while len(self._queue) < self.depth and self._enqueue():
+            pass
+        if not self._queue:
+            raise StopIteration
+        pb, buf, ev = self._queue.pop(0)
+        if ev is not None:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(ev)
+            buf.record_stream(cur)          # the buffer was allocated on the copy stream and is consumed on this one
+        self._enqueue()                     # keep the pipeline full before the caller launches its step
+        return pb.views(buf)

@@ -68,3 +68,17 @@ def test_packed_path_launches_no_index_kernels_and_matches_plain_path():
         assert C.rel(a, b) <= 1e-6                               # same kernels on identical index arrays (fp32 atomics aside)
     for k, g in outs["plain"][2].items():
         assert C.rel(outs["packed"][2][k], g) <= 1e-5, k
+
+
+def test_device_loader_overlapped_copies_deliver_the_same_tensors():
+    pbs = [ingest.pack(synth.tensorize(synth.random_batch(60 + i, 8 + 5 * i))) for i in range(5)]
+    x = torch.randn(4096, 4096, device="cuda")
+    for depth in (1, 2, 3):
+        for pb, (tree, graph) in zip(pbs, ingest.DeviceLoader(iter(pbs), "cuda", depth=depth)):
+            y = x @ x                                   # keep the compute stream busy while the next copy runs
+            ref_tree, ref_graph = pb.to_device("cuda")
+            for a, b in zip(tree[:5] + graph[:4], ref_tree[:5] + ref_graph[:4]):
+                assert torch.equal(a, b)
+            assert torch.equal(tree[3]._ggpm_csr.T.col, ref_tree[3]._ggpm_csr.T.col)
+            assert torch.equal(tree[5].roots_dev, ref_tree[5].roots_dev)
+    torch.cuda.synchronize()

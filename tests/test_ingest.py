@@ -112,3 +112,15 @@ def test_tree_only_batch_and_wire_format_roundtrip():
         ingest.PackedBatch.load(io.BytesIO(b"not a batch at all"), pin=False)
     t_only, none = ingest.PackedBatch.from_tensors(tree, None, pin=False).to_device("cpu")
     assert none is None and not hasattr(t_only[4], "_ggpm_csr") and hasattr(t_only[3], "_ggpm_csr")
+
+
+def test_device_loader_yields_every_batch_in_order():
+    pbs = [ingest.pack(synth.tensorize(synth.random_batch(40 + i, 3 + i)), pin=False) for i in range(4)]
+    got = list(ingest.DeviceLoader(iter(pbs), "cpu", depth=2))
+    assert len(got) == 4
+    for pb, (tree, graph) in zip(pbs, got):
+        ref_tree, ref_graph = pb.to_device("cpu")
+        for a, b in zip(tree[:5] + graph[:4], ref_tree[:5] + ref_graph[:4]):
+            assert torch.equal(a, b)
+        assert hasattr(tree[3], "_ggpm_csr") and list(tree[5]) == list(ref_tree[5])
+    assert list(ingest.DeviceLoader(iter([]), "cpu")) == []
