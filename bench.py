@@ -47,6 +47,9 @@ WORKLOADS = {
                   desc="double-hidden encoder (hidden 500), batch 1024 synthetic graphs (profiling-sized cfg3)"),
     "cfg3": dict(hidden=500, depthT=20, depthG=20, dropout=0.0, batch=4096,
                  desc="double-hidden encoder (hidden 500), batch 4096 synthetic graphs"),
+    "cfg5": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256, encoder="motif", latent=24,
+                 desc="PropertyVAE encoder side of one pre-training step: MotifEncoder + R_mean/R_var rsample/KL "
+                      "(ggpm/property_vae.py:79-99), batch 256 per GPU, decoder excluded"),
 }
 METRIC = "HierMPN encoder molecules/sec (fwd+bwd)"
 UNIT = "molecules/s"
@@ -188,10 +191,12 @@ def make_batches(workload, n_batches, seed):
     return out
 
 
-def algorithmic_flops(stats, H, depthT, depthG, B):
+def algorithmic_flops(stats, H, depthT, depthG, B, motif_only=False):
     """minimal-formulation FLOPs of one HierMPNEncoder forward (LSTM); fwd+bwd = 3x"""
     def layer(E, N, IN, F, D):
         return 2.0 * E * IN * 4 * H + D * 8.0 * E * H * H + 2.0 * N * (F + H) * H
+    if motif_only:      # MotifEncoder: one tree layer + W_root (+ the two latent projections, negligible)
+        return layer(stats["Et"], stats["Nt"], H + 20, H, depthT) + 2.0 * B * 2 * H * H
     f = layer(stats["Ea"], stats["Na"], 62, 38, depthG) + 2 * layer(stats["Et"], stats["Nt"], H + 20, H, depthT)
     f += 2 * (2.0 * stats["Nt"] * 2 * H * H) + 2.0 * B * 2 * H * H
     return f
@@ -209,12 +214,24 @@ def cpu_oracle_rate(workload, sample_mols, warmup, steps):
     tree, graph = synth.tensorize(mols)
     as_long = lambda ts: [torch.from_numpy(np.asarray(t)).long() if not isinstance(t, list) else t for t in ts]
     tree, graph = as_long(tree), as_long(graph)
-    sd = {k: v.requires_grad_(True) for k, v in eo.random_state("hier", "LSTM", H, H, 0, bias_std=0.0).items()}
+    motif = workload.get("encoder") == "motif"
+    sd = {k: v.requires_grad_(True)
+          for k, v in eo.random_state("motif" if motif else "hier", "LSTM", H, H, 0, bias_std=0.0).items()}
+    if motif:
+        from oracle import latent_oracle as lo
+        L = workload["latent"]
+        lat = [torch.randn(L, H) / H ** 0.5, torch.zeros(L), torch.randn(L, H) / H ** 0.5, torch.zeros(L)]
+        lat = [t.requires_grad_(True) for t in lat]
 
     def step():
         for v in sd.values():
             v.grad = None
-        eo.hier_encoder(sd, "LSTM", workload["depthT"], workload["depthG"], tree, graph)[0].sum().backward()
+        if motif:
+            root = eo.motif_encoder(sd, "LSTM", workload["depthT"], tree)[0]
+            z, kl = lo.rsample(root, *lat, torch.randn(root.shape[0], workload["latent"]), True)
+            (z.sum() + kl).backward()
+        else:
+            eo.hier_encoder(sd, "LSTM", workload["depthT"], workload["depthG"], tree, graph)[0].sum().backward()
 
     for _ in range(warmup):
         step()
@@ -273,8 +290,13 @@ def run_ours(args, workload):
 
     H = workload["hidden"]
     torch.manual_seed(0)
-    model = ggpm_b200.HierMPNEncoder(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H,
-                                     workload["depthT"], workload["depthG"], workload["dropout"])
+    motif = workload.get("encoder") == "motif"
+    enc_cls = ggpm_b200.MotifEncoder if motif else ggpm_b200.HierMPNEncoder
+    model = enc_cls(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H,
+                    workload["depthT"], workload["depthG"], workload["dropout"])
+    if motif:                             # PropertyVAE keeps the latent head next to the encoder (property_vae.py:86-87)
+        model.R_mean = torch.nn.Linear(H, workload["latent"])
+        model.R_var = torch.nn.Linear(H, workload["latent"])
     for p in model.parameters():          # vae_train.py:49-53
         if p.dim() == 1:
             torch.nn.init.constant_(p, 0)
@@ -291,17 +313,24 @@ def run_ours(args, workload):
     # host prepared), already in HBM; --resident make_cuda keeps the reference's int64 tensors instead (index structures
     # are then rebuilt on the device every step)
     from ggpm_b200 import ingest
-    packed = [ingest.pack((t, g)) for t, g, _ in batches]
+    packed = [ingest.pack((t, None if motif else g)) for t, g, _ in batches]
     if args.resident == "packed":
         dev_batches = [pb.to_device(dev) for pb in packed]
     else:
         dev_batches = [nnutils.make_cuda((t, g)) for t, g, _ in batches]
     stats = batches[0][2]
 
+    from ggpm_b200 import latent as latent_head
+
+    def forward_loss(tree, graph):
+        if motif:        # MotifEncoder -> rsample -> (z, KL): the encoder side of PropertyVAE.forward (property_vae.py:95-99)
+            z, kl = latent_head.rsample(model(tree)[0], model.R_mean, model.R_var, True)
+            return z.sum() + kl
+        return model(tree, graph)[0].sum()
+
     def step(tree, graph, read_loss=False):
         model.zero_grad(set_to_none=True)
-        hroot = model(tree, graph)[0]
-        loss = hroot.sum()
+        loss = forward_loss(tree, graph)
         loss.backward()
         if world > 1:
             bucket.all_reduce_mean()
@@ -399,7 +428,7 @@ def run_ours(args, workload):
     def e2e_step(i):
         tree, graph = next(loader)
         model.zero_grad(set_to_none=True)
-        loss = model(tree, graph)[0].sum()
+        loss = forward_loss(tree, graph)
         loss.backward()
         if world > 1:
             bucket.all_reduce_mean()
@@ -451,7 +480,7 @@ def run_ours(args, workload):
         prof_steps = 2
         for i in range(prof_steps):
             model.zero_grad(set_to_none=True)
-            model(*dev_batches[i % n_batches])[0].sum().backward()
+            forward_loss(*dev_batches[i % n_batches]).backward()
         n = len(PROF_CLASSES)
         ms_c, cnt_c, work_c = (ctypes.c_double * n)(), (ctypes.c_longlong * n)(), (ctypes.c_double * n)()
         _lib.call("ggpm_prof_collect", ctypes.cast(ms_c, ctypes.c_void_p), ctypes.cast(cnt_c, ctypes.c_void_p),
@@ -464,9 +493,9 @@ def run_ours(args, workload):
         # HBM-side classes: algorithmic bytes per step from SURVEY 8(d) (nnz-dependent part from the batch)
         Hp = (H + 31) // 32 * 32
         by = 0.0
-        for E, nnz, D in ((stats["Ea"], stats["nnz_bA"], workload["depthG"]),
-                          (stats["Et"], stats["nnz_bT"], workload["depthT"]),
-                          (stats["Et"], stats["nnz_bT"], workload["depthT"])):
+        layers = ((stats["Ea"], stats["nnz_bA"], workload["depthG"]), (stats["Et"], stats["nnz_bT"], workload["depthT"]),
+                  (stats["Et"], stats["nnz_bT"], workload["depthT"]))
+        for E, nnz, D in (layers[1:2] if motif else layers):
             by += D * (3.0 * nnz * Hp * 4 + 2.0 * E * Hp * 4 + 4.0 * nnz + 4.0 * E)
 
         def class_roofline(c):
@@ -500,7 +529,7 @@ def run_ours(args, workload):
                          "PyTorch formulation, fp32, %d threads)" % (sample, dt, cores)}
 
     if rank == 0:
-        flops = 3.0 * algorithmic_flops(stats, H, workload["depthT"], workload["depthG"], workload["batch"])
+        flops = 3.0 * algorithmic_flops(stats, H, workload["depthT"], workload["depthG"], workload["batch"], motif)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
