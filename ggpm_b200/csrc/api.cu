@@ -138,6 +138,15 @@ static F16Work f16_work(float* w_split, int Hp) {
     return w;
 }
 static bool f16_scalars_fit(int Hp, int depth) { return (size_t)16 + 16 * (size_t)(depth + 1) <= (size_t)4 * Hp * Hp; }
+// layers with at least this many message rows form S with a gather kernel and run the forward gate GEMM from planes
+static int sgather_min_rows() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("GGPM_SGATHER_MIN_ROWS");
+        v = e != nullptr ? atoi(e) : 32768;
+    }
+    return v;
+}
 static bool f16_engine_on() {
     const int e = gemm_engine();
     return e == GGPM_ENGINE_AUTO || e == GGPM_ENGINE_TCGEN05_F16X3;
@@ -301,6 +310,8 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
         GGPM_TRY(launch_absmax(Ug, (long long)wn, fw.scal + 0, st));
         GGPM_TRY(launch_f16_split(Ug, (long long)wn, fw.scal + 0, fw.hi, fw.lo, fw.scal + 1, st));
         GGPM_TRY(launch_max_degree(b_ptr, E1, reinterpret_cast<int*>(fw.scal + 2), st));
+        static const float kH16 = 8192.f;              // GGPM_H16_SCALE of the forward cell kernel, as a device scalar
+        GGPM_CUDA(cudaMemcpyAsync(fw.scal + 6, &kH16, sizeof(float), cudaMemcpyHostToDevice, st));
     } else if (w_tma) {
         GGPM_TRY(launch_tf32_split(Ug, (long long)wn, w_split, w_split + wn, st));
     }
@@ -329,7 +340,27 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
             g.M = E1; g.K = Hp; g.a_row_ptr = b_ptr; g.a_col = b_col;
             if (fused_w) {   // one launch: columns >= 3Hp (the forget projection) read h_prev un-gathered
                 g.N = 4 * Hp; g.split_dim = 1; g.split_at = 3 * Hp;
-                if (f16) {   // |h| <= 1, so every gathered row is bounded by the largest neighbour count
+                if (f16 && h16 && t >= 2 && E1 >= sgather_min_rows() && Hp % 64 == 0 && ((uintptr_t)s_scratch & 15) == 0) {
+                    // large layer: S as fp16 planes from one gather kernel (s_scratch holds both planes), then two GEMMs
+                    // whose operands all arrive by TMA: [G_i|G_o|G_u] = S Ug^T and P = h^{t-1} Uf^T from the saved h planes
+                    char* s_hi = (char*)s_scratch;
+                    char* s_lo = s_hi + 2 * row;
+                    float* s_scale = fw.scal + 5;
+                    GGPM_TRY(launch_lstm_sgather(E1, Hp, b_ptr, b_col, h_prev, reinterpret_cast<const int*>(fw.scal + 2), s_hi,
+                                                 s_lo, s_scale, st));
+                    GemmArgs a;
+                    a.Ah_hi = s_hi; a.Ah_lo = s_lo; a.lda_h = Hp; a.a_scale = s_scale;
+                    a.Bh_hi = fw.hi; a.Bh_lo = fw.lo; a.sbn = Hp; a.b_scale = fw.scal + 1;
+                    a.C = gp; a.ldc = 4 * Hp; a.M = E1; a.N = 3 * Hp; a.K = Hp;
+                    GGPM_TRY(launch_gemm_f16(a, st));
+                    GemmArgs q;
+                    const char* hp_hi = (const char*)hist_h16 + (size_t)prev * 4 * row;
+                    q.Ah_hi = hp_hi; q.Ah_lo = hp_hi + 2 * row; q.lda_h = Hp; q.a_scale = fw.scal + 6;      // = 2^13
+                    q.Bh_hi = (const char*)fw.hi + (size_t)3 * Hp * Hp * 2; q.Bh_lo = (const char*)fw.lo + (size_t)3 * Hp * Hp * 2;
+                    q.sbn = Hp; q.b_scale = fw.scal + 1;
+                    q.C = gp + 3 * Hp; q.ldc = 4 * Hp; q.M = E1; q.N = Hp; q.K = Hp;
+                    GGPM_TRY(launch_gemm_f16(q, st));
+                } else if (f16) {   // |h| <= 1, so every gathered row is bounded by the largest neighbour count
                     g.Bh_hi = fw.hi; g.Bh_lo = fw.lo; g.b_scale = fw.scal + 1;
                     g.a_amax_const = 1.f; g.a_deg = reinterpret_cast<const int*>(fw.scal + 2);
                     GGPM_TRY(launch_gemm_f16(g, st));

@@ -1,5 +1,6 @@
-timeout 600 python bench.py --workload cfg5 > gpurun_out/s63_cfg5.json 2> gpurun_out/s63_cfg5.err; echo "cfg5 exit $?"; tail -3 gpurun_out/s63_cfg5.err
-python tools/bench_summary.py gpurun_out/s63_cfg5.json
-timeout 600 python bench.py --workload cfg5 --impl reference --steps 2 --warmup 1 | cut -c1-300
-timeout 600 python bench.py > gpurun_out/s63_cfg2.json 2> gpurun_out/s63_cfg2.err; echo "cfg2 exit $?"; tail -3 gpurun_out/s63_cfg2.err
-python tools/bench_summary.py gpurun_out/s63_cfg2.json | head -3
+B3="python bench.py --workload cfg3s --steps 2 --warmup 3 --no-cpu-baseline --profile-step"
+N="ncu --profile-from-start off --set full --clock-control none --import-source on"
+$B3 > gpurun_out/s65_plain3.log 2>&1 || exit 1
+python tools/bench_summary.py gpurun_out/s65_plain3.log | head -2
+timeout 900 $N -k regex:"gemm_f16_kernel|lstm_sgather_kernel" -c 3 -o gpurun_out/s65_cfg3s_fwd_sgather $B3 > gpurun_out/s65_n1.log 2>&1
+ls -la gpurun_out | grep s65
