@@ -75,3 +75,15 @@ def test_launches_are_counted():
     before = _lib.launch_count()
     C.check_no_grad_eval(DEV)
     assert _lib.launch_count() > before
+
+
+def test_plane_fed_forward_of_large_layers_matches_golden():
+    """Layers of >= 32 768 rows form S with the sgather kernel and run the forward gate GEMMs from fp16 planes; the
+    threshold is read once per process, so the golden checks are repeated in a child process with the threshold at 0."""
+    import subprocess
+    env = dict(os.environ, GGPM_SGATHER_MIN_ROWS="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider",
+                        "-k", "cfg1_matches or (forward_backward_matches and auto)"], env=env, capture_output=True, text=True,
+                       timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
+    assert " passed" in r.stdout
