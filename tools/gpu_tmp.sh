@@ -1,6 +1,6 @@
-B3="python bench.py --workload cfg3s --steps 2 --warmup 3 --no-cpu-baseline --profile-step"
-N="ncu --profile-from-start off --set full --clock-control none --import-source on"
-$B3 > gpurun_out/s65_plain3.log 2>&1 || exit 1
-python tools/bench_summary.py gpurun_out/s65_plain3.log | head -2
-timeout 900 $N -k regex:"gemm_f16_kernel|lstm_sgather_kernel" -c 3 -o gpurun_out/s65_cfg3s_fwd_sgather $B3 > gpurun_out/s65_n1.log 2>&1
-ls -la gpurun_out | grep s65
+for wl in cfg3s; do
+for bn in 0 128 0 128; do
+GGPM_F16_BN_FWDP=$bn timeout 600 python bench.py --workload $wl --no-cpu-baseline --steps 10 > gpurun_out/s70_b.json 2> gpurun_out/s70_b.err; tail -1 gpurun_out/s70_b.err
+echo "$wl fwdp=$bn: $(python tools/bench_summary.py gpurun_out/s70_b.json | grep 'mol\|gemm_tcgen05 ' | tr '\n' ' ' | cut -c1-300)"
+done
+done
