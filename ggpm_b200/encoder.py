@@ -1,5 +1,6 @@
 """Hierarchical message-passing encoder — drop-in for ggpm/encoder.py MPNEncoder (:8-38),
-HierMPNEncoder (:41-157) and MotifEncoder (:252-341).
+HierMPNEncoder (:41-157), MotifEncoder (:252-341) and the incremental encoders the decoder drives: IncMPNEncoder
+(:160-179), IncHierMPNEncoder (:182-249), IncEncoder (:344-394).
 
 Same constructor arguments (the configs/*.json keys rnn_type, embed_size, hidden_size, depthT, depthG,
 dropout), same forward inputs/outputs, same parameter names / shapes / registration order (state_dicts
@@ -230,3 +231,134 @@ class MotifEncoder(nn.Module):
         node, _, incoming = self.tree_encoder.encode(motif_emb, attach_emb, tb.mg, tb.a, H, MAX_POS)
         root = _root_vectors(self.W_root, motif_emb, incoming, tb.roots, H)
         return root, _public(node, H)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# incremental encoders driven by the decoder: ggpm/encoder.py:160-249, 344-394
+# ----------------------------------------------------------------------------------------------------------------
+def _linear_seq(seq, parts, widths):
+    """nn.Sequential(Linear, ReLU, Dropout) applied to the concatenation of `parts` without building it"""
+    w, c, Ws = seq[0].weight, 0, []
+    for k in widths:
+        Ws.append(w[:, c:c + k])
+        c += k
+    out = Fn.linear_act(parts, Ws, seq[0].bias, act=ACT_RELU)
+    return seq[2](out)
+
+
+class IncMPNEncoder(MPNEncoder):
+    """ggpm/encoder.py:160-179: recompute the sub-messages `submess` of the state table h, then the read-out of the
+    nodes `subnode`; returns (node table [num_nodes, H] that is zero outside subnode, new state table(s))."""
+
+    def __init__(self, rnn_type, input_size, node_fdim, hidden_size, depth, dropout):
+        super(IncMPNEncoder, self).__init__(rnn_type, input_size, node_fdim, hidden_size, depth, dropout)
+
+    def forward(self, tensors, h, num_nodes, subset):
+        fnode, fmess, agraph, bgraph = tensors
+        subnode, submess = subset
+        if len(submess) > 0:
+            h = self.rnn.sparse_forward(h, fmess, submess, bgraph)
+        nei_message = Fn.slot_gather_sum(self.rnn.get_hidden_state(h), agraph)
+        F = self.W_o[0].in_features - self.hidden_size
+        node_hiddens = _linear_seq(self.W_o, [fnode, nei_message], [F, self.hidden_size])
+        node_buf = torch.zeros(num_nodes, self.hidden_size, device=node_hiddens.device)
+        node_hiddens = Fn.index_scatter(node_hiddens, node_buf, subnode)
+        return node_hiddens, h
+
+
+def _sub_tensors(tensors, subset):
+    """rows of (fnode, fmess, agraph, bgraph[, cgraph]) selected by (subnode, submess) — ggpm/encoder.py:197-208"""
+    subnode, submess = subset
+    fnode, fmess, agraph, bgraph = tensors[:4]
+    fnode, fmess = fnode.index_select(0, subnode), fmess.index_select(0, submess)
+    agraph, bgraph = agraph.index_select(0, subnode), bgraph.index_select(0, submess)
+    if len(tensors) == 6:
+        return fnode, fmess, agraph, bgraph, tensors[4].index_select(0, subnode), tensors[-1]
+    return fnode, fmess, agraph, bgraph, tensors[-1]
+
+
+def _sub_message_inputs(hnode, fmess, subnode, num_nodes, E_pos):
+    """x of the sub-messages: [features of the source node | one-hot position] (ggpm/encoder.py:224-229); only nodes in
+    `subnode` carry features — any other source reads a zero row, as the reference's scattered node_buf does"""
+    node_buf = Fn.index_scatter(hnode, torch.zeros(num_nodes, hnode.shape[1], device=hnode.device), subnode)
+    hmess = Fn.slot_gather_sum(node_buf, fmess[:, 0])
+    return torch.cat([hmess, E_pos.index_select(0, fmess[:, 2])], dim=-1)
+
+
+class IncHierMPNEncoder(HierMPNEncoder):
+
+    def __init__(self, vocab, avocab, rnn_type, embed_size, hidden_size, depthT, depthG, dropout):
+        super(IncHierMPNEncoder, self).__init__(vocab, avocab, rnn_type, embed_size, hidden_size, depthT, depthG, dropout)
+        self.tree_encoder = IncMPNEncoder(rnn_type, hidden_size + MAX_POS, hidden_size, hidden_size, depthT, dropout)
+        self.inter_encoder = IncMPNEncoder(rnn_type, hidden_size + MAX_POS, hidden_size, hidden_size, depthT, dropout)
+        self.graph_encoder = IncMPNEncoder(rnn_type, self.atom_size + self.bond_size, self.atom_size, hidden_size, depthG,
+                                           dropout)
+        del self.W_root
+
+    def embed_graph(self, graph_tensors):
+        """ggpm/encoder.py:119-126 (one-hot rows; the decoder embeds the atom graph once per batch, decoder.py:193)"""
+        fnode, fmess, agraph, bgraph, _ = graph_tensors
+        hnode = self.E_a.index_select(0, fnode)
+        hmess = torch.cat([hnode.index_select(0, fmess[:, 0]), self.E_b.index_select(0, fmess[:, 2]),
+                           self.E_apos.index_select(0, fmess[:, 3])], dim=-1)
+        return hnode, hmess, agraph, bgraph
+
+    def get_sub_tensor(self, tensors, subset):
+        return _sub_tensors(tensors, subset)
+
+    def embed_sub_tree(self, tree_tensors, hinput, subtree, is_inter_layer):
+        subnode, submess = subtree
+        num_nodes = tree_tensors[0].size(0)
+        fnode, fmess, agraph, bgraph, cgraph, _ = _sub_tensors(tree_tensors, subtree)
+        if is_inter_layer:
+            finput = _embed(self.E_i, fnode[:, 1])
+            E = finput.shape[1]
+            hinput = Fn.slot_gather_sum(hinput, cgraph)
+            hnode = _linear_seq(self.W_i, [finput, hinput], [E, self.W_i[0].in_features - E])
+        else:
+            finput = _embed(self.E_c, fnode[:, 0])
+            E = finput.shape[1]
+            hinput = Fn.slot_gather_sum(hinput, subnode)
+            hnode = _linear_seq(self.W_c, [finput, hinput], [E, self.W_c[0].in_features - E])
+        hmess = fmess if len(submess) == 0 else _sub_message_inputs(hnode, fmess, subnode, num_nodes, self.E_pos)
+        return hnode, hmess, agraph, bgraph
+
+    def forward(self, tree_tensors, inter_tensors, graph_tensors, htree, hinter, hgraph, subtree, subgraph):
+        num_tree_nodes = tree_tensors[0].size(0)
+        num_graph_nodes = graph_tensors[0].size(0)
+        if len(subgraph[0]) + len(subgraph[1]) > 0:
+            sub_graph_tensors = _sub_tensors(graph_tensors, subgraph)[:-1]     # already embedded by embed_graph
+            hgraph.node, hgraph.mess = self.graph_encoder(sub_graph_tensors, hgraph.mess, num_graph_nodes, subgraph)
+        if len(subtree[0]) + len(subtree[1]) > 0:
+            sub_inter_tensors = self.embed_sub_tree(inter_tensors, hgraph.node, subtree, is_inter_layer=True)
+            hinter.node, hinter.mess = self.inter_encoder(sub_inter_tensors, hinter.mess, num_tree_nodes, subtree)
+            sub_tree_tensors = self.embed_sub_tree(tree_tensors, hinter.node, subtree, is_inter_layer=False)
+            htree.node, htree.mess = self.tree_encoder(sub_tree_tensors, htree.mess, num_tree_nodes, subtree)
+        return htree, hinter, hgraph
+
+
+class IncEncoder(MotifEncoder):
+
+    def __init__(self, vocab, avocab, rnn_type, embed_size, hidden_size, depthT, depthG, dropout):
+        super(IncEncoder, self).__init__(vocab, avocab, rnn_type, embed_size, hidden_size, depthT, depthG, dropout)
+        self.tree_encoder = IncMPNEncoder(rnn_type, embed_size + MAX_POS, hidden_size, hidden_size, depthT, dropout)
+        del self.W_root
+
+    def get_sub_tensor(self, tensors, subset):
+        return _sub_tensors(tensors, subset)
+
+    def embed_sub_tree(self, tree_tensors, subtree):
+        """ggpm/encoder.py:366-386: node features AND message inputs are the motif embedding E_c here"""
+        subnode, submess = subtree
+        num_nodes = tree_tensors[0].size(0)
+        fnode, fmess, agraph, bgraph, cgraph, _ = _sub_tensors(tree_tensors, subtree)
+        hnode = _embed(self.E_c, fnode[:, 0])
+        hmess = fmess if len(submess) == 0 else _sub_message_inputs(hnode, fmess, subnode, num_nodes, self.E_pos)
+        return hnode, hmess, agraph, bgraph
+
+    def forward(self, tree_tensors, htree, subtree):
+        num_tree_nodes = tree_tensors[0].size(0)
+        if len(subtree[0]) + len(subtree[1]) > 0:
+            sub_tree_tensors = self.embed_sub_tree(tree_tensors, subtree)
+            htree.node, htree.mess = self.tree_encoder(sub_tree_tensors, htree.mess, num_tree_nodes, subtree)
+        return htree

@@ -578,3 +578,252 @@ class GRUMessages(torch.autograd.Function):
              fptr(dSg), fptr(dPr), fptr(dHn), stream_ptr(dev))
         dphi, dWx, dT = _xproj_backward(ctx, dX, phi_x, Wx, T, mg)
         return dphi, dWx, dT, dUz, dUr, dbr, dUh, None, None, None
+
+
+# ----------------------------------------------------------------------------------------------
+# incremental ("sparse") message passing of the decoder's encoder — SURVEY 8(f) rank 1
+# ----------------------------------------------------------------------------------------------
+def _rows(t: torch.Tensor) -> torch.Tensor:
+    """fp32 2-D with unit column stride (row stride free)"""
+    if t.dim() != 2 or t.dtype != torch.float32:
+        raise ValueError("expected a 2-D float32 tensor, got %s %s" % (tuple(t.shape), t.dtype))
+    return t if (t.stride(1) == 1 or t.shape[1] == 1) else t.contiguous()
+
+
+def row_ids(index: torch.Tensor, n_rows: int, check: bool = False) -> torch.Tensor:
+    """int64 / int32 row ids -> contiguous int32 (any shape, flattened by the callers)"""
+    _lib.require_device(index, "index tensor")
+    if index.dtype not in (torch.int64, torch.int32):
+        raise ValueError("index tensors must be int64 or int32, got %s" % index.dtype)
+    if check and index.numel() and (int(index.min()) < 0 or int(index.max()) >= n_rows):
+        raise IndexError("row index out of range [0, %d)" % n_rows)
+    return index.to(torch.int32).contiguous()
+
+
+def rows_gather(table, idx, M, K, pairs=True, total=True):
+    """pairs [M*K, W] = table[idx], total [M, W] = sum over each row's K slots (one kernel)"""
+    table = _rows(table)
+    W = table.shape[1]
+    dev = table.device
+    P_ = torch.empty(M * K, W, dtype=torch.float32, device=dev) if pairs else None
+    S_ = torch.empty(M, W, dtype=torch.float32, device=dev) if total else None
+    call("ggpm_rows_gather", fptr(table), _row_stride(table), iptr(idx), M, K, W, None if P_ is None else fptr(P_), W,
+         None if S_ is None else fptr(S_), W, stream_ptr(dev))
+    return P_, S_
+
+
+def rows_scatter_(table, idx, src=None):
+    """table[idx[m]] = src[m] (zero rows when src is None), in place"""
+    M = idx.numel()
+    if M == 0:
+        return table
+    if src is not None:
+        src = _rows(src)
+    call("ggpm_rows_scatter", fptr(table), _row_stride(table), iptr(idx), M, table.shape[1],
+         None if src is None else fptr(src), 0 if src is None else _row_stride(src), stream_ptr(table.device))
+    return table
+
+
+def rows_scatter_add_(table, idx, M, K, src=None, bcast=None):
+    """table[idx[p]] += src[p] + bcast[p // K], in place"""
+    call("ggpm_rows_scatter_add", fptr(table), _row_stride(table), iptr(idx), M, K, table.shape[1],
+         None if src is None else fptr(src), 0 if src is None else _row_stride(src),
+         None if bcast is None else fptr(bcast), 0 if bcast is None else _row_stride(bcast), stream_ptr(table.device))
+    return table
+
+
+class IndexScatter(torch.autograd.Function):
+    """index_scatter(sub_data, all_data, index) of ggpm/nnutils.py:124-128: a copy of all_data whose rows `index` are
+    replaced by sub_data — one table copy + one row scatter instead of six full-table passes."""
+
+    @staticmethod
+    def forward(ctx, sub, table, idx):
+        out = table.contiguous().clone()
+        rows_scatter_(out, idx, sub)
+        ctx.idx = idx
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        idx = ctx.idx
+        dout = _rows(dout)
+        d_sub = d_tab = None
+        if ctx.needs_input_grad[0]:
+            d_sub, _ = rows_gather(dout, idx, idx.numel(), 1, pairs=True, total=False)
+        if ctx.needs_input_grad[1]:
+            d_tab = rows_scatter_(dout.contiguous().clone(), idx, None)
+        return d_sub, d_tab, None
+
+
+def index_scatter(sub_data, all_data, index):
+    if sub_data.shape[0] != index.numel() or sub_data.shape[1] != all_data.shape[1]:
+        raise ValueError("index_scatter: sub_data %s does not match index %d / table %s"
+                         % (tuple(sub_data.shape), index.numel(), tuple(all_data.shape)))
+    if index.numel() == 0:
+        return all_data * 1.0
+    return IndexScatter.apply(_rows(sub_data), all_data, row_ids(index.reshape(-1), all_data.shape[0]))
+
+
+class SparseLSTM(torch.autograd.Function):
+    """LSTM.sparse_forward (ggpm/rnn.py:110-121) as one autograd node: rows `sub` of (h, c) are zeroed and recomputed for
+    `depth` rounds from the K padded neighbour slots `nbr` [M*K] read out of the whole table; all other rows pass
+    through.  x [M, IN] are the (embedded) inputs of the sub-messages; Wx [4H, IN], b [4H] in gate order (i, o, u, f);
+    U3 [3H, H] = (U_i; U_o; U_u), Uf [H, H].  Per call: one table copy each way; per round: M*K gathered rows, three
+    small GEMMs, one cell kernel, M scattered rows."""
+
+    @staticmethod
+    def forward(ctx, h, c, x, Wx, b, U3, Uf, sub, nbr, K, depth):
+        M, H = sub.numel(), h.shape[1]
+        dev = h.device
+        Xg = gemm_nt(_rows(x), Wx, bias=b)
+        hw = rows_scatter_(h.contiguous().clone(), sub, None)
+        cw = rows_scatter_(c.contiguous().clone(), sub, None)
+        saved = []
+        for _ in range(depth):
+            Hn, S = rows_gather(hw, nbr, M, K)
+            Cn, _ = rows_gather(cw, nbr, M, K, total=False)
+            A = Xg.clone()
+            gemm_nt(S, U3, out=A, beta=1.0)                       # columns [0, 3H) += S U3^T
+            Pf = gemm_nt(Hn, Uf)
+            h_sub = torch.empty(M, H, dtype=torch.float32, device=dev)
+            c_sub = torch.empty_like(h_sub)
+            gates = torch.empty(M, 4 * H, dtype=torch.float32, device=dev)
+            call("ggpm_sparse_lstm_cell_fwd", M, K, H, fptr(A), 4 * H, fptr(Pf), fptr(Cn), fptr(h_sub), fptr(c_sub),
+                 fptr(gates), fptr(Pf), stream_ptr(dev))          # f overwrites Pf element for element
+            rows_scatter_(hw, sub, h_sub)
+            rows_scatter_(cw, sub, c_sub)
+            saved += [S, Hn, Cn, gates, Pf]
+        ctx.dims = (M, K, H, depth)
+        ctx.sub, ctx.nbr = sub, nbr
+        ctx.save_for_backward(x, Wx, U3, Uf, *saved)
+        return hw, cw
+
+    @staticmethod
+    def backward(ctx, dh, dc):
+        M, K, H, depth = ctx.dims
+        sub, nbr = ctx.sub, ctx.nbr
+        x, Wx, U3, Uf, *saved = ctx.saved_tensors
+        dev = x.device
+        dHw = _rows(dh).contiguous().clone()
+        dCw = _rows(dc).contiguous().clone()
+        dXg = torch.zeros(M, 4 * H, dtype=torch.float32, device=dev)
+        dU3 = torch.zeros_like(U3)
+        dUf = torch.zeros_like(Uf)
+        dA = torch.empty(M, 4 * H, dtype=torch.float32, device=dev)
+        dPf = torch.empty(M * K, H, dtype=torch.float32, device=dev)
+        dCn = torch.empty_like(dPf)
+        for t in reversed(range(depth)):
+            S, Hn, Cn, gates, fs = saved[5 * t: 5 * t + 5]
+            dh_sub, _ = rows_gather(dHw, sub, M, 1, total=False)
+            dc_sub, _ = rows_gather(dCw, sub, M, 1, total=False)
+            rows_scatter_(dHw, sub, None)
+            rows_scatter_(dCw, sub, None)
+            call("ggpm_sparse_lstm_cell_bwd", M, K, H, fptr(dh_sub), fptr(dc_sub), fptr(gates), fptr(fs), fptr(Cn),
+                 fptr(dA), fptr(dPf), fptr(dCn), fptr(dXg), stream_ptr(dev))
+            dA3 = dA[:, :3 * H]
+            dS = gemm_nn(dA3, U3)
+            dHn = gemm_nn(dPf, Uf)
+            gemm_tn(dA3, S, out=dU3, beta=1.0)
+            gemm_tn(dPf, Hn, out=dUf, beta=1.0)
+            rows_scatter_add_(dHw, nbr, M, K, src=dHn, bcast=dS)
+            rows_scatter_add_(dCw, nbr, M, K, src=dCn)
+        rows_scatter_(dHw, sub, None)      # the incoming sub rows were discarded by the forward pass
+        rows_scatter_(dCw, sub, None)
+        dx = gemm_nn(dXg, Wx) if ctx.needs_input_grad[2] else None
+        dWx = gemm_tn(dXg, _rows(x))
+        db = torch.empty(4 * H, dtype=torch.float32, device=dev)
+        call("ggpm_colsum", fptr(dXg), 4 * H, M, 4 * H, fptr(db), 0, stream_ptr(dev))
+        return dHw, dCw, dx, dWx, db, dU3, dUf, None, None, None, None
+
+
+class SparseGRU(torch.autograd.Function):
+    """GRU.sparse_forward (ggpm/rnn.py:52-59).  Wx [3H, IN], b [3H] in order (z, h~, r) — b_r is U_r's bias, W_r has
+    none; Uz, Uh, Ur [H, H]."""
+
+    @staticmethod
+    def forward(ctx, h, x, Wx, b, Uz, Uh, Ur, sub, nbr, K, depth):
+        M, H = sub.numel(), h.shape[1]
+        dev = h.device
+        Xg = gemm_nt(_rows(x), Wx, bias=b)
+        hw = rows_scatter_(h.contiguous().clone(), sub, None)
+        saved = []
+        for _ in range(depth):
+            Hn, S = rows_gather(hw, nbr, M, K)
+            Pr = gemm_nt(Hn, Ur)
+            Sg = torch.empty(M, H, dtype=torch.float32, device=dev)
+            call("ggpm_sparse_gru_gate_fwd", M, K, H, fptr(Xg[:, 2 * H:]), 3 * H, fptr(Pr), fptr(Hn), fptr(Pr), fptr(Sg),
+                 stream_ptr(dev))                                 # r overwrites Pr element for element
+            A = Xg[:, :2 * H].clone(memory_format=torch.contiguous_format)     # never a view of Xg (M = 1!)
+            gemm_nt(S, Uz, out=A[:, :H], beta=1.0)
+            gemm_nt(Sg, Uh, out=A[:, H:], beta=1.0)
+            h_sub = torch.empty(M, H, dtype=torch.float32, device=dev)
+            zh = torch.empty(M, 2 * H, dtype=torch.float32, device=dev)
+            call("ggpm_sparse_gru_out_fwd", M, H, fptr(A), 2 * H, fptr(S), fptr(h_sub), fptr(zh), stream_ptr(dev))
+            rows_scatter_(hw, sub, h_sub)
+            saved += [S, Hn, Pr, Sg, zh]
+        ctx.dims = (M, K, H, depth)
+        ctx.sub, ctx.nbr = sub, nbr
+        ctx.save_for_backward(x, Wx, Uz, Uh, Ur, *saved)
+        return hw
+
+    @staticmethod
+    def backward(ctx, dh):
+        M, K, H, depth = ctx.dims
+        sub, nbr = ctx.sub, ctx.nbr
+        x, Wx, Uz, Uh, Ur, *saved = ctx.saved_tensors
+        dev = x.device
+        dHw = _rows(dh).contiguous().clone()
+        dXg = torch.zeros(M, 3 * H, dtype=torch.float32, device=dev)
+        dUz, dUh, dUr = torch.zeros_like(Uz), torch.zeros_like(Uh), torch.zeros_like(Ur)
+        dA = torch.empty(M, 2 * H, dtype=torch.float32, device=dev)
+        dS = torch.empty(M, H, dtype=torch.float32, device=dev)
+        dPr = torch.empty(M * K, H, dtype=torch.float32, device=dev)
+        dHn = torch.empty_like(dPr)
+        for t in reversed(range(depth)):
+            S, Hn, rs, Sg, zh = saved[5 * t: 5 * t + 5]
+            dh_sub, _ = rows_gather(dHw, sub, M, 1, total=False)
+            rows_scatter_(dHw, sub, None)
+            call("ggpm_sparse_gru_out_bwd", M, H, fptr(dh_sub), fptr(zh), fptr(S), fptr(dA), fptr(dS), fptr(dXg), 3 * H,
+                 stream_ptr(dev))
+            daz, dah = dA[:, :H], dA[:, H:]
+            gemm_nn(daz, Uz, out=dS, beta=1.0)
+            dSg = gemm_nn(dah, Uh)
+            gemm_tn(daz, S, out=dUz, beta=1.0)
+            gemm_tn(dah, Sg, out=dUh, beta=1.0)
+            call("ggpm_sparse_gru_gate_bwd", M, K, H, fptr(dSg), fptr(rs), fptr(Hn), fptr(dPr), fptr(dHn),
+                 fptr(dXg[:, 2 * H:]), 3 * H, stream_ptr(dev))
+            gemm_nn(dPr, Ur, out=dHn, beta=1.0)
+            gemm_tn(dPr, Hn, out=dUr, beta=1.0)
+            rows_scatter_add_(dHw, nbr, M, K, src=dHn, bcast=dS)
+        rows_scatter_(dHw, sub, None)
+        dx = gemm_nn(dXg, Wx) if ctx.needs_input_grad[1] else None
+        dWx = gemm_tn(dXg, _rows(x))
+        db = torch.empty(3 * H, dtype=torch.float32, device=dev)
+        call("ggpm_colsum", fptr(dXg), 3 * H, M, 3 * H, fptr(db), 0, stream_ptr(dev))
+        return dHw, dx, dWx, db, dUz, dUh, dUr, None, None, None, None
+
+
+class SlotGatherSum(torch.autograd.Function):
+    """out[m] = sum_k table[idx[m*K + k]] over ALL K slots (slot value 0 reads row 0): index_select_ND(table, 0,
+    index).sum(1) (ggpm/encoder.py:171-172, 217) and, with K = 1, table.index_select(0, index) (:220, 229)."""
+
+    @staticmethod
+    def forward(ctx, table, idx, M, K):
+        ctx.idx, ctx.dims = idx, (M, K, table.shape[0])
+        return rows_gather(table, idx, M, K, pairs=False)[1]
+
+    @staticmethod
+    def backward(ctx, dout):
+        M, K, R = ctx.dims
+        dt = torch.zeros(R, dout.shape[1], dtype=torch.float32, device=dout.device)
+        rows_scatter_add_(dt, ctx.idx, M, K, bcast=_rows(dout))
+        return dt, None, None, None
+
+
+def slot_gather_sum(table: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
+    """index [M, K] (or [M]) of row ids into table [R, W] -> [M, W]"""
+    M = index.shape[0]
+    K = 1 if index.dim() == 1 else index.shape[1]
+    if M == 0 or K == 0:
+        return table.new_zeros(M, table.shape[1])
+    return SlotGatherSum.apply(_rows(table), row_ids(index.reshape(-1), table.shape[0]), M, K)

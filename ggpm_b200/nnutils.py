@@ -1,6 +1,6 @@
 """Tensor utilities of the encoder path — host-side mirror of ggpm/nnutils.py for the functions the
-encoder uses: index_select_ND (:65-70), create_pad_tensor (:105-110), make_tensor / make_cuda
-(:201-214).  Device work goes through libggpm_b200.so; there is no CPU implementation."""
+encoder uses: index_select_ND (:65-70), create_pad_tensor (:105-110), index_scatter (:124-128),
+make_tensor / make_cuda (:201-214).  Device work goes through libggpm_b200.so; there is no CPU implementation."""
 from __future__ import annotations
 
 import numpy as np
@@ -87,6 +87,11 @@ def index_select_ND(source: torch.Tensor, dim: int, index: torch.Tensor) -> torc
 def index_select_sum(source: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
     """index_select_ND(source, 0, index).sum(dim=1) as one CSR gather-sum kernel."""
     return Fn.gather_sum(source, Fn.csr_from_padded(index, source.shape[0]))
+
+
+def index_scatter(sub_data, all_data, index):
+    """all_data with rows `index` replaced by sub_data (ggpm/nnutils.py:124-128), differentiable in both"""
+    return Fn.index_scatter(sub_data, all_data, index)
 
 
 def create_pad_tensor(alist):

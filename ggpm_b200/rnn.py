@@ -31,6 +31,17 @@ class _GraphRNN(nn.Module):
     def padded_hidden(self):
         return Fn.padded_width(self.hidden_size)
 
+    def _sparse_args(self, h, fmess, submess, bgraph):
+        """validated (sub [M] int32, nbr [M*K] int32, K) of a sparse_forward call"""
+        if fmess.dim() != 2 or fmess.shape[1] != self.input_size or fmess.dtype != torch.float32:
+            raise ValueError("fmess must be float32 [M, %d], got %s %s" % (self.input_size, tuple(fmess.shape), fmess.dtype))
+        if bgraph.dim() != 2 or bgraph.shape[0] != fmess.shape[0] or submess.numel() != fmess.shape[0]:
+            raise ValueError("sparse_forward: fmess, submess and bgraph must describe the same sub-messages")
+        if h.dim() != 2 or h.shape[1] != self.hidden_size or h.dtype != torch.float32:
+            raise ValueError("state table must be float32 [R, %d]" % self.hidden_size)
+        R = h.shape[0]
+        return Fn.row_ids(submess.reshape(-1), R), Fn.row_ids(bgraph.reshape(-1), R), bgraph.shape[1]
+
     def _check(self, fmess, bgraph):
         if fmess.dim() != 2 or fmess.shape[1] != self.input_size:
             raise ValueError("fmess must be [E, %d], got %s" % (self.input_size, tuple(fmess.shape)))
@@ -67,6 +78,18 @@ class GRU(_GraphRNN):
         h = self.messages(fmess, _identity_graph(fmess, bgraph), self.input_size, 1)
         return h[:, :self.hidden_size].contiguous()
 
+    def sparse_forward(self, h, fmess, submess, bgraph):
+        """ggpm/rnn.py:52-59: rows `submess` of the table h [R, H] are reset and recomputed for `depth` rounds; fmess
+        [M, IN] / bgraph [M, K] are the inputs / neighbour slots of those rows (slot values index the whole table)."""
+        if submess.numel() == 0 or self.depth == 0:
+            return h * 1.0 if submess.numel() == 0 else Fn.index_scatter(h.new_zeros(submess.numel(), h.shape[1]), h, submess)
+        sub, nbr, K = self._sparse_args(h, fmess, submess, bgraph)
+        IN, H = self.input_size, self.hidden_size
+        Wx = torch.cat([self.W_z.weight[:, :IN], self.W_h.weight[:, :IN], self.W_r.weight], dim=0)
+        b = torch.cat([self.W_z.bias, self.W_h.bias, self.U_r.bias], dim=0)
+        return Fn.SparseGRU.apply(h, fmess, Wx, b, self.W_z.weight[:, IN:], self.W_h.weight[:, IN:], self.U_r.weight,
+                                  sub, nbr, K, self.depth)
+
 
 class LSTM(_GraphRNN):
 
@@ -99,3 +122,21 @@ class LSTM(_GraphRNN):
         h, c = self.messages(fmess, _identity_graph(fmess, bgraph), self.input_size, 1)
         H = self.hidden_size
         return h[:, :H].contiguous(), c[:, :H].contiguous()
+
+    def sparse_forward(self, h, fmess, submess, bgraph):
+        """ggpm/rnn.py:110-121: as GRU.sparse_forward on the (h, c) pair of tables"""
+        h, c = h
+        if submess.numel() == 0 or self.depth == 0:
+            if submess.numel() == 0:
+                return h * 1.0, c * 1.0
+            z = h.new_zeros(submess.numel(), h.shape[1])
+            return Fn.index_scatter(z, h, submess), Fn.index_scatter(z, c, submess)
+        sub, nbr, K = self._sparse_args(h, fmess, submess, bgraph)
+        if c.shape != h.shape:
+            raise ValueError("h and c tables differ in shape")
+        IN = self.input_size
+        gates = (self.W_i[0], self.W_o[0], self.W[0], self.W_f[0])
+        Wx = torch.cat([g.weight[:, :IN] for g in gates], dim=0)
+        b = torch.cat([g.bias for g in gates], dim=0)
+        U3 = torch.cat([g.weight[:, IN:] for g in gates[:3]], dim=0)
+        return Fn.SparseLSTM.apply(h, c, fmess, Wx, b, U3, self.W_f[0].weight[:, IN:], sub, nbr, K, self.depth)

@@ -246,6 +246,40 @@ int ggpm_rsample_fwd(const float* Y, int ldy, int var_off, const float* eps, int
 int ggpm_rsample_bwd(const float* Y, int ldy, int var_off, const float* eps, int ld_eps, int B, int L, const float* dz,
                      int ld_dz, const float* dkl, float* dY, int ld_dy, int width, void* stream);
 
+/* ---- incremental ("sparse") message passing of the decoder's encoder ---------------------
+ * Replaces GRU.sparse_forward / LSTM.sparse_forward (ggpm/rnn.py:52-59, 110-121) and index_scatter
+ * (ggpm/nnutils.py:124-128): M sub-messages of an R-row state table are recomputed for `depth` rounds, each round
+ * reading the K padded neighbour slots of every sub-message from the whole table (slot 0 reads row 0, as
+ * index_select_ND does; slots are not compacted because the decoder zeroes them mid-row, ggpm/decoder.py:72-83).
+ * Row-major fp32 operands of arbitrary width; idx are int32 row ids of the table.
+ *   rows_gather:      pairs [M*K, ld_p] = table[idx[p]] (may be NULL), sum [M, ld_s] = sum over the K slots (may be NULL)
+ *   rows_scatter:     table[idx[m]] = src[m]   (src NULL: zero the rows); idx must not repeat
+ *   rows_scatter_add: table[idx[p]] += src[p] + bcast[p / K]   (either may be NULL) — backward of rows_gather
+ *   sparse_lstm_cell_fwd: A [M, lda>=4H] pre-activations (i | o | u | f x-part), Pf / Cn [M*K, H] = U_f h_nei / c_nei
+ *       -> h_sub, c_sub [M, H]; saves gates [M, 4H] = (i | o | u | tanh c) and fs [M*K, H]   (ggpm/rnn.py:85-94)
+ *   sparse_lstm_cell_bwd: -> dA [M, 4H], dPf [M*K, H], dCn [M*K, H]; dXacc [M, 4H] += dA (sum over the rounds)
+ *   sparse_gru_gate_fwd:  rs [M*K, H] = sigmoid(Xr[m] + Pr[p]), Sg [M, H] = sum_k rs * Hn        (ggpm/rnn.py:30-35)
+ *   sparse_gru_gate_bwd:  -> dPr, dHn [M*K, H] (dHn = direct term dSg * r), dXr [M, ldx] += sum_k dPr
+ *   sparse_gru_out_fwd:   A [M, lda>=2H] pre-activations (z | h~), S [M, H] -> h_sub = (1-z) S + z h~; saves zh [M, 2H]
+ *   sparse_gru_out_bwd:   -> dA [M, 2H], dS [M, H] = dh (1 - z); dXacc [M, ldx] columns [0, 2H) += dA */
+int ggpm_rows_gather(const float* table, int ld_t, const int32_t* idx, int M, int K, int width, float* pairs, int ld_p,
+                     float* sum, int ld_s, void* stream);
+int ggpm_rows_scatter(float* table, int ld_t, const int32_t* idx, int M, int width, const float* src, int ld_s,
+                      void* stream);
+int ggpm_rows_scatter_add(float* table, int ld_t, const int32_t* idx, int M, int K, int width, const float* src, int ld_s,
+                          const float* bcast, int ld_b, void* stream);
+int ggpm_sparse_lstm_cell_fwd(int M, int K, int H, const float* A, int lda, const float* Pf, const float* Cn, float* h_sub,
+                              float* c_sub, float* gates, float* fs, void* stream);
+int ggpm_sparse_lstm_cell_bwd(int M, int K, int H, const float* dh, const float* dc, const float* gates, const float* fs,
+                              const float* Cn, float* dA, float* dPf, float* dCn, float* dXacc, void* stream);
+int ggpm_sparse_gru_gate_fwd(int M, int K, int H, const float* Xr, int ldx, const float* Pr, const float* Hn, float* rs,
+                             float* Sg, void* stream);
+int ggpm_sparse_gru_gate_bwd(int M, int K, int H, const float* dSg, const float* rs, const float* Hn, float* dPr,
+                             float* dHn, float* dXr, int ldx, void* stream);
+int ggpm_sparse_gru_out_fwd(int M, int H, const float* A, int lda, const float* S, float* h_sub, float* zh, void* stream);
+int ggpm_sparse_gru_out_bwd(int M, int H, const float* dh, const float* zh, const float* S, float* dA, float* dS,
+                            float* dXacc, int ldx, void* stream);
+
 /* ---- host-side index builder (no device work, no stream): SURVEY 8(f) rank 3 ----------------------------------
  * Replaces MolGraph.tensorize_graph (ggpm/mol_graph.py:238-281: Python dict / list loops per edge over networkx
  * graphs) and the cgraph assembly of MolGraph.tensorize (ggpm/mol_graph.py:211-222) for callers that hold the batch

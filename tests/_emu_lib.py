@@ -385,3 +385,108 @@ class EmuLib:
         b = _f(dbr, Hp)
         b.copy_((b.to(DT) + dbr_).float())
         return 0
+
+    # -- incremental message passing (sparse.cu) ---------------------------------------------------
+    def ggpm_rows_gather(self, table, ld_t, idx, M, K, width, pairs, ld_p, total, ld_s, stream):
+        self._tick("rows_gather")
+        ix = _i(idx, M * K).long()
+        t = _tab(table, int(ix.max()) + 1, ld_t, width)
+        picked = t[ix]
+        if pairs:
+            _tab(pairs, M * K, ld_p, width).copy_(picked)
+        if total:
+            _tab(total, M, ld_s, width).copy_(picked.to(DT).reshape(M, K, width).sum(1).float())
+        return 0
+
+    def ggpm_rows_scatter(self, table, ld_t, idx, M, width, src, ld_s, stream):
+        self._tick("rows_scatter")
+        ix = _i(idx, M).long()
+        assert len(set(ix.tolist())) == M, "rows_scatter: repeated row ids"
+        t = _tab(table, int(ix.max()) + 1, ld_t, width)
+        t[ix] = _tab(src, M, ld_s, width) if src else torch.zeros(M, width)
+        return 0
+
+    def ggpm_rows_scatter_add(self, table, ld_t, idx, M, K, width, src, ld_s, bcast, ld_b, stream):
+        self._tick("rows_scatter_add")
+        ix = _i(idx, M * K).long()
+        t = _tab(table, int(ix.max()) + 1, ld_t, width)
+        v = torch.zeros(M * K, width, dtype=DT)
+        if src:
+            v = v + _tab(src, M * K, ld_s, width).to(DT)
+        if bcast:
+            v = v + _tab(bcast, M, ld_b, width).to(DT).repeat_interleave(K, 0)
+        acc = t.to(DT)
+        acc.index_add_(0, ix, v)
+        t.copy_(acc.float())
+        return 0
+
+    def ggpm_sparse_lstm_cell_fwd(self, M, K, H, A, lda, Pf, Cn, h_sub, c_sub, gates, fs, stream):
+        self._tick("sparse_lstm_cell_fwd")
+        a = _tab(A, M, lda, 4 * H).to(DT)
+        i, o, u, xf = torch.sigmoid(a[:, :H]), torch.sigmoid(a[:, H:2 * H]), torch.tanh(a[:, 2 * H:3 * H]), a[:, 3 * H:]
+        f = torch.sigmoid(xf[:, None, :] + _tab(Pf, M * K, H, H).to(DT).reshape(M, K, H))
+        c = i * u + (f * _tab(Cn, M * K, H, H).to(DT).reshape(M, K, H)).sum(1)
+        tc = torch.tanh(c)
+        _tab(h_sub, M, H, H).copy_((o * tc).float())
+        _tab(c_sub, M, H, H).copy_(c.float())
+        _tab(gates, M, 4 * H, 4 * H).copy_(torch.cat([i, o, u, tc], 1).float())
+        _tab(fs, M * K, H, H).copy_(f.reshape(M * K, H).float())
+        return 0
+
+    def ggpm_sparse_lstm_cell_bwd(self, M, K, H, dh, dc, gates, fs, Cn, dA, dPf, dCn, dXacc, stream):
+        self._tick("sparse_lstm_cell_bwd")
+        g = _tab(gates, M, 4 * H, 4 * H).to(DT)
+        i, o, u, tc = g[:, :H], g[:, H:2 * H], g[:, 2 * H:3 * H], g[:, 3 * H:]
+        gh = _tab(dh, M, H, H).to(DT)
+        dct = _tab(dc, M, H, H).to(DT) + gh * o * (1 - tc * tc)
+        f = _tab(fs, M * K, H, H).to(DT).reshape(M, K, H)
+        cn = _tab(Cn, M * K, H, H).to(DT).reshape(M, K, H)
+        daf = dct[:, None, :] * cn * f * (1 - f)
+        d = torch.cat([dct * u * i * (1 - i), gh * tc * o * (1 - o), dct * i * (1 - u * u), daf.sum(1)], 1)
+        _tab(dA, M, 4 * H, 4 * H).copy_(d.float())
+        _tab(dPf, M * K, H, H).copy_(daf.reshape(M * K, H).float())
+        _tab(dCn, M * K, H, H).copy_((dct[:, None, :] * f).reshape(M * K, H).float())
+        x = _tab(dXacc, M, 4 * H, 4 * H)
+        x.copy_((x.to(DT) + d).float())
+        return 0
+
+    def ggpm_sparse_gru_gate_fwd(self, M, K, H, Xr, ldx, Pr, Hn, rs, Sg, stream):
+        self._tick("sparse_gru_gate_fwd")
+        r = torch.sigmoid(_tab(Xr, M, ldx, H).to(DT)[:, None, :] + _tab(Pr, M * K, H, H).to(DT).reshape(M, K, H))
+        sg = (r * _tab(Hn, M * K, H, H).to(DT).reshape(M, K, H)).sum(1)
+        _tab(rs, M * K, H, H).copy_(r.reshape(M * K, H).float())
+        _tab(Sg, M, H, H).copy_(sg.float())
+        return 0
+
+    def ggpm_sparse_gru_gate_bwd(self, M, K, H, dSg, rs, Hn, dPr, dHn, dXr, ldx, stream):
+        self._tick("sparse_gru_gate_bwd")
+        g = _tab(dSg, M, H, H).to(DT)[:, None, :]
+        r = _tab(rs, M * K, H, H).to(DT).reshape(M, K, H)
+        hn = _tab(Hn, M * K, H, H).to(DT).reshape(M, K, H)
+        dar = g * hn * r * (1 - r)
+        _tab(dPr, M * K, H, H).copy_(dar.reshape(M * K, H).float())
+        _tab(dHn, M * K, H, H).copy_((g * r).reshape(M * K, H).float())
+        x = _tab(dXr, M, ldx, H)
+        x.copy_((x.to(DT) + dar.sum(1)).float())
+        return 0
+
+    def ggpm_sparse_gru_out_fwd(self, M, H, A, lda, S, h_sub, zh, stream):
+        self._tick("sparse_gru_out_fwd")
+        a = _tab(A, M, lda, 2 * H).to(DT)
+        z, ht = torch.sigmoid(a[:, :H]), torch.tanh(a[:, H:])
+        s = _tab(S, M, H, H).to(DT)
+        _tab(h_sub, M, H, H).copy_(((1 - z) * s + z * ht).float())
+        _tab(zh, M, 2 * H, 2 * H).copy_(torch.cat([z, ht], 1).float())
+        return 0
+
+    def ggpm_sparse_gru_out_bwd(self, M, H, dh, zh, S, dA, dS, dXacc, ldx, stream):
+        self._tick("sparse_gru_out_bwd")
+        zz = _tab(zh, M, 2 * H, 2 * H).to(DT)
+        z, ht = zz[:, :H], zz[:, H:]
+        g = _tab(dh, M, H, H).to(DT)
+        d = torch.cat([g * (ht - _tab(S, M, H, H).to(DT)) * z * (1 - z), g * z * (1 - ht * ht)], 1)
+        _tab(dA, M, 2 * H, 2 * H).copy_(d.float())
+        _tab(dS, M, H, H).copy_((g * (1 - z)).float())
+        x = _tab(dXacc, M, ldx, 2 * H)
+        x.copy_((x.to(DT) + d).float())
+        return 0
