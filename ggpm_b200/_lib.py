@@ -54,7 +54,7 @@ SIGNATURES = {
     "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
     "ggpm_rsample_fwd": (I, [P, I, I, P, I, I, I, P, I, P, P, P]),
     "ggpm_rsample_bwd": (I, [P, I, I, P, I, I, I, P, I, P, P, I, I, P]),
-    "ggpm_rows_gather": (I, [P, I, P, I, I, I, P, I, P, I, P]),
+    "ggpm_rows_gather": (I, [P, I, P, I, I, I, I, P, I, P, I, P]),
     "ggpm_rows_scatter": (I, [P, I, P, I, I, P, I, P]),
     "ggpm_rows_scatter_add": (I, [P, I, P, I, I, I, P, I, P, I, P]),
     "ggpm_sparse_lstm_cell_fwd": (I, [I, I, I, P, I, P, P, P, P, P, P, P]),
@@ -63,6 +63,10 @@ SIGNATURES = {
     "ggpm_sparse_gru_gate_bwd": (I, [I, I, I, P, P, P, P, P, P, I, P]),
     "ggpm_sparse_gru_out_fwd": (I, [I, I, P, I, P, P, P, P]),
     "ggpm_sparse_gru_out_bwd": (I, [I, I, P, P, P, P, P, P, I, P]),
+    "ggpm_sparse_lstm_fwd": (I, [I, I, I, I, I, P, P, I] + [P] * 13),
+    "ggpm_sparse_lstm_bwd": (I, [I, I, I, I, I, P, P, I] + [P] * 18),
+    "ggpm_sparse_gru_fwd": (I, [I, I, I, I, I, P, I] + [P] * 14),
+    "ggpm_sparse_gru_bwd": (I, [I, I, I, I, I, P, I] + [P] * 21),
     "ggpm_tensorize_graph": (I, [I, P, P, I, P, P, P]),
     "ggpm_tensorize_fetch": (I, [P] * 9),
     "ggpm_tensorize_cgraph": (I, [I, I, P, P, P, P, P, P, P]),

@@ -7,12 +7,14 @@
 // runs the cell on the M rows only and writes them back.  The reference does this with full-table passes
 // (zeros_like + scatter_ + ones + scatter_ + mul + add per state tensor per round); here a round touches
 // M*K gathered rows + M written rows and nothing else:
-//     rows_gather      pairs[p] = table[idx[p]],  sum[m] = sum_k pairs[m*K + k]            (one pass)
+//     rows_gather      pairs[p] = table[idx[p]],  sum[m] = sum_k pairs[m*K + k]   (one pass; outputs zero-filled from the
+//                      table width up to the padded width the GEMM path wants)
 //     cell kernels     element-wise gate math on [M, .] / [M*K, .] operands (the H x H products run on the GEMM path)
 //     rows_scatter     table[idx[m]] = src[m]   (or 0)
 //     rows_scatter_add table[idx[p]] += src[p] + bcast[p / K]    (backward of the gathers; fp32 atomics)
-// Row widths are arbitrary (H = 250 tables come in unpadded from the caller), so accesses are scalar and coalesced
-// along the row.
+// Table row widths are arbitrary (H = 250 tables come in unpadded from the caller), so accesses are scalar and coalesced
+// along the row; everything between gather and scatter lives at the padded width Hp (multiple of 32, zero tail — the
+// cells keep a zero tail zero), which makes every H x H product eligible for the tcgen05 GEMM engine.
 #include "common.cuh"
 
 namespace ggpm {
@@ -28,14 +30,14 @@ static inline unsigned sp_blocks(long long n) {
 
 __global__ void __launch_bounds__(kSpThreads)
 rows_gather_kernel(const float* __restrict__ table, int ld_t, const int32_t* __restrict__ idx, int M, int K, int width,
-                   float* __restrict__ pairs, int ld_p, float* __restrict__ sum, int ld_s) {
-    const long long n = (long long)M * width;
+                   int pad_to, float* __restrict__ pairs, int ld_p, float* __restrict__ sum, int ld_s) {
+    const long long n = (long long)M * pad_to;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const int m = (int)(i / width), j = (int)(i % width);
+        const int m = (int)(i / pad_to), j = (int)(i % pad_to);
         float s = 0.f;
         for (int k = 0; k < K; ++k) {
             const long long p = (long long)m * K + k;
-            const float v = table[(size_t)idx[p] * ld_t + j];
+            const float v = j < width ? table[(size_t)idx[p] * ld_t + j] : 0.f;     // columns [width, pad_to) are zero fill
             if (pairs != nullptr) pairs[(size_t)p * ld_p + j] = v;
             s += v;
         }
@@ -205,15 +207,15 @@ using namespace ggpm;
 
 #define SP_SIZES(what) GGPM_REQUIRE(M >= 1 && K >= 1 && H >= 1, what ": bad sizes")
 
-extern "C" int ggpm_rows_gather(const float* table, int ld_t, const int32_t* idx, int M, int K, int width, float* pairs,
-                                int ld_p, float* sum, int ld_s, void* stream) {
+extern "C" int ggpm_rows_gather(const float* table, int ld_t, const int32_t* idx, int M, int K, int width, int pad_to,
+                                float* pairs, int ld_p, float* sum, int ld_s, void* stream) {
     GGPM_REQUIRE(table && idx && (pairs || sum), "rows_gather: null pointer");
     GGPM_REQUIRE(M >= 1 && K >= 1 && width >= 1 && ld_t >= width, "rows_gather: bad sizes");
-    GGPM_REQUIRE((!pairs || ld_p >= width) && (!sum || ld_s >= width), "rows_gather: bad leading dimension");
+    GGPM_REQUIRE(pad_to >= width && (!pairs || ld_p >= pad_to) && (!sum || ld_s >= pad_to), "rows_gather: bad leading dimension");
     cudaStream_t st = (cudaStream_t)stream;
     ProfScope prof(PROF_GATHER, st, (double)M * (K + 1) * width * 4.0);
-    rows_gather_kernel<<<sp_blocks((long long)M * width), kSpThreads, 0, st>>>(table, ld_t, idx, M, K, width, pairs, ld_p,
-                                                                              sum, ld_s);
+    rows_gather_kernel<<<sp_blocks((long long)M * pad_to), kSpThreads, 0, st>>>(table, ld_t, idx, M, K, width, pad_to, pairs,
+                                                                               ld_p, sum, ld_s);
     return check_launch("rows_gather");
 }
 
@@ -303,4 +305,155 @@ extern "C" int ggpm_sparse_gru_out_bwd(int M, int H, const float* dh, const floa
     ProfScope prof(PROF_CELL_BWD, st, (double)M * H * 4.0 * 7);
     sparse_gru_out_bwd_kernel<<<sp_blocks((long long)M * H), kSpThreads, 0, st>>>(M, H, dh, zh, S, dA, dS, dXacc, ldx);
     return check_launch("sparse_gru_out_bwd");
+}
+
+// ---- whole-call drivers: every round of a sparse_forward (and of its backward) launched from ONE C-ABI call ---------
+// The Python host allocates the stacks of saved tensors and the scratch buffers (caching allocator) and makes one
+// call per direction; the `depth` rounds are sequenced here, so the per-round cost on the host is a handful of kernel
+// launches rather than a handful of interpreter round trips.  Operands live at the padded width Hp (zero tail).
+#include "kernels.h"
+
+namespace {
+
+int gemm_rows(const float* A, long long lda, const float* W, long long ldw, float* C, int ldc, int M, int N, int K,
+              float beta, cudaStream_t st) {          // C[M, N] (+)= A[M, K] @ W[N, K]^T
+    GemmArgs g;
+    g.A = A; g.sam = lda; g.sak = 1; g.B = W; g.sbk = 1; g.sbn = ldw; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K;
+    g.beta = beta;
+    return launch_gemm_nt(g, st);
+}
+
+int gemm_back(const float* dY, long long ldy, const float* W, long long ldw, float* dX, int ldx, int M, int N, int K,
+              float beta, cudaStream_t st) {          // dX[M, N] (+)= dY[M, K] @ W[K, N]
+    GemmArgs g;
+    g.A = dY; g.sam = ldy; g.sak = 1; g.B = W; g.sbk = ldw; g.sbn = 1; g.C = dX; g.ldc = ldx; g.M = M; g.N = N; g.K = K;
+    g.beta = beta;
+    return launch_gemm_nt(g, st);
+}
+
+int gemm_wgrad(const float* dY, long long ldy, const float* X, long long ldx, float* dW, int ldw, int N, int Kw, int rows,
+               cudaStream_t st) {                     // dW[N, Kw] += dY[rows, N]^T @ X[rows, Kw], cut along the rows
+    GemmArgs g;
+    g.A = dY; g.sam = 1; g.sak = ldy; g.B = X; g.sbk = ldx; g.sbn = 1; g.C = dW; g.ldc = ldw; g.M = N; g.N = Kw; g.K = rows;
+    g.beta = 1.f;
+    const int tiles = ceil_div(N, 128) * ceil_div(Kw, 128);
+    int splits = ceil_div(2 * sm_count(), tiles);
+    if (splits > ceil_div(rows, 256)) splits = ceil_div(rows, 256);
+    g.split_k = splits < 1 ? 1 : splits;
+    return launch_gemm_nt(g, st);
+}
+
+}  // namespace
+
+extern "C" int ggpm_sparse_lstm_fwd(int M, int K, int H, int Hp, int depth, float* hw, float* cw, int ld_t,
+                                    const int32_t* sub, const int32_t* nbr, const float* Xg, const float* U4, float* S,
+                                    float* Hn, float* Cn, float* gates, float* fs, float* A, float* h_sub, float* c_sub,
+                                    void* stream) {
+    GGPM_REQUIRE(hw && cw && sub && nbr && Xg && U4 && S && Hn && Cn && gates && fs && A && h_sub && c_sub,
+                 "sparse_lstm_fwd: null pointer");
+    GGPM_REQUIRE(M >= 1 && K >= 1 && H >= 1 && Hp >= H && Hp % 4 == 0 && depth >= 1 && ld_t >= H, "sparse_lstm_fwd: bad sizes");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t row = (size_t)M * Hp, pair = (size_t)M * K * Hp;
+    GGPM_TRY(ggpm_rows_scatter(hw, ld_t, sub, M, H, nullptr, 0, stream));
+    GGPM_TRY(ggpm_rows_scatter(cw, ld_t, sub, M, H, nullptr, 0, stream));
+    for (int t = 0; t < depth; ++t) {
+        float *S_t = S + t * row, *Hn_t = Hn + t * pair, *Cn_t = Cn + t * pair, *fs_t = fs + t * pair;
+        GGPM_TRY(ggpm_rows_gather(hw, ld_t, nbr, M, K, H, Hp, Hn_t, Hp, S_t, Hp, stream));
+        GGPM_TRY(ggpm_rows_gather(cw, ld_t, nbr, M, K, H, Hp, Cn_t, Hp, nullptr, 0, stream));
+        GGPM_CUDA(cudaMemcpyAsync(A, Xg, sizeof(float) * 4 * row, cudaMemcpyDeviceToDevice, st));
+        GGPM_TRY(gemm_rows(S_t, Hp, U4, Hp, A, 4 * Hp, M, 3 * Hp, Hp, 1.f, st));
+        GGPM_TRY(gemm_rows(Hn_t, Hp, U4 + (size_t)3 * Hp * Hp, Hp, fs_t, Hp, M * K, Hp, Hp, 0.f, st));
+        GGPM_TRY(ggpm_sparse_lstm_cell_fwd(M, K, Hp, A, 4 * Hp, fs_t, Cn_t, h_sub, c_sub, gates + t * 4 * row, fs_t, stream));
+        GGPM_TRY(ggpm_rows_scatter(hw, ld_t, sub, M, H, h_sub, Hp, stream));
+        GGPM_TRY(ggpm_rows_scatter(cw, ld_t, sub, M, H, c_sub, Hp, stream));
+    }
+    return 0;
+}
+
+extern "C" int ggpm_sparse_lstm_bwd(int M, int K, int H, int Hp, int depth, float* dHw, float* dCw, int ld_t,
+                                    const int32_t* sub, const int32_t* nbr, const float* U4, const float* S, const float* Hn,
+                                    const float* Cn, const float* gates, const float* fs, float* dXg, float* dU4, float* dA,
+                                    float* dPf, float* dCn, float* dh_sub, float* dc_sub, float* dS, float* dHn,
+                                    void* stream) {
+    GGPM_REQUIRE(dHw && dCw && sub && nbr && U4 && S && Hn && Cn && gates && fs && dXg && dU4 && dA && dPf && dCn && dh_sub &&
+                     dc_sub && dS && dHn, "sparse_lstm_bwd: null pointer");
+    GGPM_REQUIRE(M >= 1 && K >= 1 && H >= 1 && Hp >= H && Hp % 4 == 0 && depth >= 1 && ld_t >= H, "sparse_lstm_bwd: bad sizes");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t row = (size_t)M * Hp, pair = (size_t)M * K * Hp;
+    const float* Uf = U4 + (size_t)3 * Hp * Hp;
+    GGPM_CUDA(cudaMemsetAsync(dXg, 0, sizeof(float) * 4 * row, st));
+    GGPM_CUDA(cudaMemsetAsync(dU4, 0, sizeof(float) * 4 * Hp * Hp, st));
+    for (int t = depth - 1; t >= 0; --t) {
+        const float *S_t = S + t * row, *Hn_t = Hn + t * pair, *Cn_t = Cn + t * pair, *fs_t = fs + t * pair;
+        GGPM_TRY(ggpm_rows_gather(dHw, ld_t, sub, M, 1, H, Hp, dh_sub, Hp, nullptr, 0, stream));
+        GGPM_TRY(ggpm_rows_gather(dCw, ld_t, sub, M, 1, H, Hp, dc_sub, Hp, nullptr, 0, stream));
+        GGPM_TRY(ggpm_rows_scatter(dHw, ld_t, sub, M, H, nullptr, 0, stream));
+        GGPM_TRY(ggpm_rows_scatter(dCw, ld_t, sub, M, H, nullptr, 0, stream));
+        GGPM_TRY(ggpm_sparse_lstm_cell_bwd(M, K, Hp, dh_sub, dc_sub, gates + t * 4 * row, fs_t, Cn_t, dA, dPf, dCn, dXg, stream));
+        GGPM_TRY(gemm_back(dA, 4 * Hp, U4, Hp, dS, Hp, M, Hp, 3 * Hp, 0.f, st));
+        GGPM_TRY(gemm_back(dPf, Hp, Uf, Hp, dHn, Hp, M * K, Hp, Hp, 0.f, st));
+        GGPM_TRY(gemm_wgrad(dA, 4 * Hp, S_t, Hp, dU4, Hp, 3 * Hp, Hp, M, st));
+        GGPM_TRY(gemm_wgrad(dPf, Hp, Hn_t, Hp, dU4 + (size_t)3 * Hp * Hp, Hp, Hp, Hp, M * K, st));
+        GGPM_TRY(ggpm_rows_scatter_add(dHw, ld_t, nbr, M, K, H, dHn, Hp, dS, Hp, stream));
+        GGPM_TRY(ggpm_rows_scatter_add(dCw, ld_t, nbr, M, K, H, dCn, Hp, nullptr, 0, stream));
+    }
+    GGPM_TRY(ggpm_rows_scatter(dHw, ld_t, sub, M, H, nullptr, 0, stream));   // the incoming sub rows were discarded by the
+    GGPM_TRY(ggpm_rows_scatter(dCw, ld_t, sub, M, H, nullptr, 0, stream));   // forward pass
+    return 0;
+}
+
+extern "C" int ggpm_sparse_gru_fwd(int M, int K, int H, int Hp, int depth, float* hw, int ld_t, const int32_t* sub,
+                                   const int32_t* nbr, const float* Xg, const float* Uz, const float* Ur, const float* Uh,
+                                   float* S, float* Hn, float* rs, float* Sg, float* zh, float* A, float* h_sub,
+                                   void* stream) {
+    GGPM_REQUIRE(hw && sub && nbr && Xg && Uz && Ur && Uh && S && Hn && rs && Sg && zh && A && h_sub, "sparse_gru_fwd: null pointer");
+    GGPM_REQUIRE(M >= 1 && K >= 1 && H >= 1 && Hp >= H && Hp % 4 == 0 && depth >= 1 && ld_t >= H, "sparse_gru_fwd: bad sizes");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t row = (size_t)M * Hp, pair = (size_t)M * K * Hp;
+    GGPM_TRY(ggpm_rows_scatter(hw, ld_t, sub, M, H, nullptr, 0, stream));
+    for (int t = 0; t < depth; ++t) {
+        float *S_t = S + t * row, *Hn_t = Hn + t * pair, *rs_t = rs + t * pair, *Sg_t = Sg + t * row;
+        GGPM_TRY(ggpm_rows_gather(hw, ld_t, nbr, M, K, H, Hp, Hn_t, Hp, S_t, Hp, stream));
+        GGPM_TRY(gemm_rows(Hn_t, Hp, Ur, Hp, rs_t, Hp, M * K, Hp, Hp, 0.f, st));
+        GGPM_TRY(ggpm_sparse_gru_gate_fwd(M, K, Hp, Xg + 2 * Hp, 3 * Hp, rs_t, Hn_t, rs_t, Sg_t, stream));
+        GGPM_CUDA(cudaMemcpy2DAsync(A, sizeof(float) * 2 * Hp, Xg, sizeof(float) * 3 * Hp, sizeof(float) * 2 * Hp, M,
+                                    cudaMemcpyDeviceToDevice, st));
+        GGPM_TRY(gemm_rows(S_t, Hp, Uz, Hp, A, 2 * Hp, M, Hp, Hp, 1.f, st));
+        GGPM_TRY(gemm_rows(Sg_t, Hp, Uh, Hp, A + Hp, 2 * Hp, M, Hp, Hp, 1.f, st));
+        GGPM_TRY(ggpm_sparse_gru_out_fwd(M, Hp, A, 2 * Hp, S_t, h_sub, zh + t * 2 * row, stream));
+        GGPM_TRY(ggpm_rows_scatter(hw, ld_t, sub, M, H, h_sub, Hp, stream));
+    }
+    return 0;
+}
+
+extern "C" int ggpm_sparse_gru_bwd(int M, int K, int H, int Hp, int depth, float* dHw, int ld_t, const int32_t* sub,
+                                   const int32_t* nbr, const float* Uz, const float* Ur, const float* Uh, const float* S,
+                                   const float* Hn, const float* rs, const float* Sg, const float* zh, float* dXg, float* dUz,
+                                   float* dUr, float* dUh, float* dA, float* dS, float* dSg, float* dPr, float* dHn,
+                                   float* dh_sub, void* stream) {
+    GGPM_REQUIRE(dHw && sub && nbr && Uz && Ur && Uh && S && Hn && rs && Sg && zh && dXg && dUz && dUr && dUh && dA && dS && dSg &&
+                     dPr && dHn && dh_sub, "sparse_gru_bwd: null pointer");
+    GGPM_REQUIRE(M >= 1 && K >= 1 && H >= 1 && Hp >= H && Hp % 4 == 0 && depth >= 1 && ld_t >= H, "sparse_gru_bwd: bad sizes");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t row = (size_t)M * Hp, pair = (size_t)M * K * Hp, sq = sizeof(float) * (size_t)Hp * Hp;
+    GGPM_CUDA(cudaMemsetAsync(dXg, 0, sizeof(float) * 3 * row, st));
+    GGPM_CUDA(cudaMemsetAsync(dUz, 0, sq, st));
+    GGPM_CUDA(cudaMemsetAsync(dUr, 0, sq, st));
+    GGPM_CUDA(cudaMemsetAsync(dUh, 0, sq, st));
+    for (int t = depth - 1; t >= 0; --t) {
+        const float *S_t = S + t * row, *Hn_t = Hn + t * pair, *rs_t = rs + t * pair, *Sg_t = Sg + t * row;
+        GGPM_TRY(ggpm_rows_gather(dHw, ld_t, sub, M, 1, H, Hp, dh_sub, Hp, nullptr, 0, stream));
+        GGPM_TRY(ggpm_rows_scatter(dHw, ld_t, sub, M, H, nullptr, 0, stream));
+        GGPM_TRY(ggpm_sparse_gru_out_bwd(M, Hp, dh_sub, zh + t * 2 * row, S_t, dA, dS, dXg, 3 * Hp, stream));
+        GGPM_TRY(gemm_back(dA, 2 * Hp, Uz, Hp, dS, Hp, M, Hp, Hp, 1.f, st));
+        GGPM_TRY(gemm_back(dA + Hp, 2 * Hp, Uh, Hp, dSg, Hp, M, Hp, Hp, 0.f, st));
+        GGPM_TRY(gemm_wgrad(dA, 2 * Hp, S_t, Hp, dUz, Hp, Hp, Hp, M, st));
+        GGPM_TRY(gemm_wgrad(dA + Hp, 2 * Hp, Sg_t, Hp, dUh, Hp, Hp, Hp, M, st));
+        GGPM_TRY(ggpm_sparse_gru_gate_bwd(M, K, Hp, dSg, rs_t, Hn_t, dPr, dHn, dXg + 2 * Hp, 3 * Hp, stream));
+        GGPM_TRY(gemm_back(dPr, Hp, Ur, Hp, dHn, Hp, M * K, Hp, Hp, 1.f, st));
+        GGPM_TRY(gemm_wgrad(dPr, Hp, Hn_t, Hp, dUr, Hp, Hp, Hp, M * K, st));
+        GGPM_TRY(ggpm_rows_scatter_add(dHw, ld_t, nbr, M, K, H, dHn, Hp, dS, Hp, stream));
+    }
+    GGPM_TRY(ggpm_rows_scatter(dHw, ld_t, sub, M, H, nullptr, 0, stream));
+    return 0;
 }

@@ -238,12 +238,9 @@ class MotifEncoder(nn.Module):
 # ----------------------------------------------------------------------------------------------------------------
 def _linear_seq(seq, parts, widths):
     """nn.Sequential(Linear, ReLU, Dropout) applied to the concatenation of `parts` without building it"""
-    w, c, Ws = seq[0].weight, 0, []
-    for k in widths:
-        Ws.append(w[:, c:c + k])
-        c += k
-    out = Fn.linear_act(parts, Ws, seq[0].bias, act=ACT_RELU)
-    return seq[2](out)
+    out = Fn.linear_act_split(parts, seq[0].weight, widths, seq[0].bias, act=ACT_RELU)      # [M, Np], tensor-core shapes
+    H = seq[0].out_features
+    return seq[2](out if out.shape[1] == H else out[:, :H])
 
 
 class IncMPNEncoder(MPNEncoder):

@@ -600,20 +600,22 @@ def row_ids(index: torch.Tensor, n_rows: int, check: bool = False) -> torch.Tens
     return index.to(torch.int32).contiguous()
 
 
-def rows_gather(table, idx, M, K, pairs=True, total=True):
-    """pairs [M*K, W] = table[idx], total [M, W] = sum over each row's K slots (one kernel)"""
+def rows_gather(table, idx, M, K, pairs=True, total=True, pad_to=None):
+    """pairs [M*K, Wp] = table[idx], total [M, Wp] = sum over each row's K slots (one kernel); Wp = pad_to (default:
+    the table width), columns beyond the table width are zero"""
     table = _rows(table)
     W = table.shape[1]
+    Wp = W if pad_to is None else pad_to
     dev = table.device
-    P_ = torch.empty(M * K, W, dtype=torch.float32, device=dev) if pairs else None
-    S_ = torch.empty(M, W, dtype=torch.float32, device=dev) if total else None
-    call("ggpm_rows_gather", fptr(table), _row_stride(table), iptr(idx), M, K, W, None if P_ is None else fptr(P_), W,
-         None if S_ is None else fptr(S_), W, stream_ptr(dev))
+    P_ = torch.empty(M * K, Wp, dtype=torch.float32, device=dev) if pairs else None
+    S_ = torch.empty(M, Wp, dtype=torch.float32, device=dev) if total else None
+    call("ggpm_rows_gather", fptr(table), _row_stride(table), iptr(idx), M, K, W, Wp, None if P_ is None else fptr(P_), Wp,
+         None if S_ is None else fptr(S_), Wp, stream_ptr(dev))
     return P_, S_
 
 
 def rows_scatter_(table, idx, src=None):
-    """table[idx[m]] = src[m] (zero rows when src is None), in place"""
+    """table[idx[m]] = src[m, :table width] (zero rows when src is None), in place"""
     M = idx.numel()
     if M == 0:
         return table
@@ -664,143 +666,104 @@ def index_scatter(sub_data, all_data, index):
     return IndexScatter.apply(_rows(sub_data), all_data, row_ids(index.reshape(-1), all_data.shape[0]))
 
 
+def _stack(depth, rows, width, dev):
+    return torch.empty(depth, rows, width, dtype=torch.float32, device=dev)
+
+
 class SparseLSTM(torch.autograd.Function):
-    """LSTM.sparse_forward (ggpm/rnn.py:110-121) as one autograd node: rows `sub` of (h, c) are zeroed and recomputed for
-    `depth` rounds from the K padded neighbour slots `nbr` [M*K] read out of the whole table; all other rows pass
-    through.  x [M, IN] are the (embedded) inputs of the sub-messages; Wx [4H, IN], b [4H] in gate order (i, o, u, f);
-    U3 [3H, H] = (U_i; U_o; U_u), Uf [H, H].  Per call: one table copy each way; per round: M*K gathered rows, three
-    small GEMMs, one cell kernel, M scattered rows."""
+    """LSTM.sparse_forward (ggpm/rnn.py:110-121) as one autograd node and ONE library call per direction
+    (ggpm_sparse_lstm_fwd / _bwd sequence all the rounds): rows `sub` of the tables (h, c) [R, H] are zeroed and
+    recomputed for `depth` rounds from the K padded neighbour slots `nbr` [M*K] read out of the whole table; all other
+    rows pass through.  x [M, Fp] are the (embedded) inputs of the sub-messages; Wx [4Hp, Fp], T [1, 4Hp] (biases) and
+    U4 [4Hp, Hp] = (U_i; U_o; U_u; U_f) come from packing.pack_lstm (gate order i, o, u, f; zero padded).  Between
+    gather and scatter everything lives at the padded width Hp, so the H x H products run on the tensor-core engine.
+    Per call: one table copy each way; per round: M*K gathered rows, two small GEMMs, one cell kernel, M scattered
+    rows."""
 
     @staticmethod
-    def forward(ctx, h, c, x, Wx, b, U3, Uf, sub, nbr, K, depth):
-        M, H = sub.numel(), h.shape[1]
+    def forward(ctx, h, c, x, Wx, T, U4, sub, nbr, K, depth):
+        M, Hp, H = sub.numel(), U4.shape[1], h.shape[1]
         dev = h.device
-        Xg = gemm_nt(_rows(x), Wx, bias=b)
-        hw = rows_scatter_(h.contiguous().clone(), sub, None)
-        cw = rows_scatter_(c.contiguous().clone(), sub, None)
-        saved = []
-        for _ in range(depth):
-            Hn, S = rows_gather(hw, nbr, M, K)
-            Cn, _ = rows_gather(cw, nbr, M, K, total=False)
-            A = Xg.clone()
-            gemm_nt(S, U3, out=A, beta=1.0)                       # columns [0, 3H) += S U3^T
-            Pf = gemm_nt(Hn, Uf)
-            h_sub = torch.empty(M, H, dtype=torch.float32, device=dev)
-            c_sub = torch.empty_like(h_sub)
-            gates = torch.empty(M, 4 * H, dtype=torch.float32, device=dev)
-            call("ggpm_sparse_lstm_cell_fwd", M, K, H, fptr(A), 4 * H, fptr(Pf), fptr(Cn), fptr(h_sub), fptr(c_sub),
-                 fptr(gates), fptr(Pf), stream_ptr(dev))          # f overwrites Pf element for element
-            rows_scatter_(hw, sub, h_sub)
-            rows_scatter_(cw, sub, c_sub)
-            saved += [S, Hn, Cn, gates, Pf]
-        ctx.dims = (M, K, H, depth)
+        Xg = gemm_nt(x, Wx, bias=T)
+        hw, cw = h.contiguous().clone(), c.contiguous().clone()
+        S, gates = _stack(depth, M, Hp, dev), _stack(depth, M, 4 * Hp, dev)
+        Hn, Cn, fs = (_stack(depth, M * K, Hp, dev) for _ in range(3))
+        A = torch.empty(M, 6 * Hp, dtype=torch.float32, device=dev)              # A [M, 4Hp] | h_sub | c_sub
+        call("ggpm_sparse_lstm_fwd", M, K, H, Hp, depth, fptr(hw), fptr(cw), H, iptr(sub), iptr(nbr), fptr(Xg), fptr(U4),
+             fptr(S), fptr(Hn), fptr(Cn), fptr(gates), fptr(fs), A.data_ptr(), A.data_ptr() + 16 * M * Hp,
+             A.data_ptr() + 20 * M * Hp, stream_ptr(dev))
+        ctx.dims = (M, K, H, Hp, depth)
         ctx.sub, ctx.nbr = sub, nbr
-        ctx.save_for_backward(x, Wx, U3, Uf, *saved)
+        ctx.save_for_backward(x, Wx, U4, S, Hn, Cn, gates, fs)
         return hw, cw
 
     @staticmethod
     def backward(ctx, dh, dc):
-        M, K, H, depth = ctx.dims
+        M, K, H, Hp, depth = ctx.dims
         sub, nbr = ctx.sub, ctx.nbr
-        x, Wx, U3, Uf, *saved = ctx.saved_tensors
+        x, Wx, U4, S, Hn, Cn, gates, fs = ctx.saved_tensors
         dev = x.device
-        dHw = _rows(dh).contiguous().clone()
-        dCw = _rows(dc).contiguous().clone()
-        dXg = torch.zeros(M, 4 * H, dtype=torch.float32, device=dev)
-        dU3 = torch.zeros_like(U3)
-        dUf = torch.zeros_like(Uf)
-        dA = torch.empty(M, 4 * H, dtype=torch.float32, device=dev)
-        dPf = torch.empty(M * K, H, dtype=torch.float32, device=dev)
-        dCn = torch.empty_like(dPf)
-        for t in reversed(range(depth)):
-            S, Hn, Cn, gates, fs = saved[5 * t: 5 * t + 5]
-            dh_sub, _ = rows_gather(dHw, sub, M, 1, total=False)
-            dc_sub, _ = rows_gather(dCw, sub, M, 1, total=False)
-            rows_scatter_(dHw, sub, None)
-            rows_scatter_(dCw, sub, None)
-            call("ggpm_sparse_lstm_cell_bwd", M, K, H, fptr(dh_sub), fptr(dc_sub), fptr(gates), fptr(fs), fptr(Cn),
-                 fptr(dA), fptr(dPf), fptr(dCn), fptr(dXg), stream_ptr(dev))
-            dA3 = dA[:, :3 * H]
-            dS = gemm_nn(dA3, U3)
-            dHn = gemm_nn(dPf, Uf)
-            gemm_tn(dA3, S, out=dU3, beta=1.0)
-            gemm_tn(dPf, Hn, out=dUf, beta=1.0)
-            rows_scatter_add_(dHw, nbr, M, K, src=dHn, bcast=dS)
-            rows_scatter_add_(dCw, nbr, M, K, src=dCn)
-        rows_scatter_(dHw, sub, None)      # the incoming sub rows were discarded by the forward pass
-        rows_scatter_(dCw, sub, None)
+        dHw = dh.contiguous().clone()
+        dCw = dc.contiguous().clone()
+        dXg = torch.empty(M, 4 * Hp, dtype=torch.float32, device=dev)
+        dU4 = torch.empty_like(U4)
+        rowbuf = torch.empty(M, 7 * Hp, dtype=torch.float32, device=dev)         # dA [M, 4Hp] | dh_sub | dc_sub | dS
+        pairbuf = torch.empty(3, M * K, Hp, dtype=torch.float32, device=dev)     # dPf | dCn | dHn
+        r, p, f4 = rowbuf.data_ptr(), pairbuf.data_ptr(), 4 * M * Hp
+        call("ggpm_sparse_lstm_bwd", M, K, H, Hp, depth, fptr(dHw), fptr(dCw), H, iptr(sub), iptr(nbr), fptr(U4), fptr(S),
+             fptr(Hn), fptr(Cn), fptr(gates), fptr(fs), fptr(dXg), fptr(dU4), r, p, p + f4 * K, r + 4 * f4, r + 5 * f4,
+             r + 6 * f4, p + 2 * f4 * K, stream_ptr(dev))
         dx = gemm_nn(dXg, Wx) if ctx.needs_input_grad[2] else None
-        dWx = gemm_tn(dXg, _rows(x))
-        db = torch.empty(4 * H, dtype=torch.float32, device=dev)
-        call("ggpm_colsum", fptr(dXg), 4 * H, M, 4 * H, fptr(db), 0, stream_ptr(dev))
-        return dHw, dCw, dx, dWx, db, dU3, dUf, None, None, None, None
+        dWx = gemm_tn(dXg, x)
+        dT = torch.empty(1, 4 * Hp, dtype=torch.float32, device=dev)
+        call("ggpm_colsum", fptr(dXg), 4 * Hp, M, 4 * Hp, fptr(dT), 0, stream_ptr(dev))
+        return dHw, dCw, dx, dWx, dT, dU4, None, None, None, None
 
 
 class SparseGRU(torch.autograd.Function):
-    """GRU.sparse_forward (ggpm/rnn.py:52-59).  Wx [3H, IN], b [3H] in order (z, h~, r) — b_r is U_r's bias, W_r has
-    none; Uz, Uh, Ur [H, H]."""
+    """GRU.sparse_forward (ggpm/rnn.py:52-59), one library call per direction (ggpm_sparse_gru_fwd / _bwd).  Operands
+    from packing.pack_gru: Wx [3Hp, Fp], T [1, 3Hp] in order (z, h~, r) — T carries the W_z / W_h biases, br [Hp] is
+    U_r's (W_r has none); Uz, Ur, Uh [Hp, Hp]."""
 
     @staticmethod
-    def forward(ctx, h, x, Wx, b, Uz, Uh, Ur, sub, nbr, K, depth):
-        M, H = sub.numel(), h.shape[1]
+    def forward(ctx, h, x, Wx, T, Uz, Ur, br, Uh, sub, nbr, K, depth):
+        M, Hp, H = sub.numel(), Uz.shape[1], h.shape[1]
         dev = h.device
-        Xg = gemm_nt(_rows(x), Wx, bias=b)
-        hw = rows_scatter_(h.contiguous().clone(), sub, None)
-        saved = []
-        for _ in range(depth):
-            Hn, S = rows_gather(hw, nbr, M, K)
-            Pr = gemm_nt(Hn, Ur)
-            Sg = torch.empty(M, H, dtype=torch.float32, device=dev)
-            call("ggpm_sparse_gru_gate_fwd", M, K, H, fptr(Xg[:, 2 * H:]), 3 * H, fptr(Pr), fptr(Hn), fptr(Pr), fptr(Sg),
-                 stream_ptr(dev))                                 # r overwrites Pr element for element
-            A = Xg[:, :2 * H].clone(memory_format=torch.contiguous_format)     # never a view of Xg (M = 1!)
-            gemm_nt(S, Uz, out=A[:, :H], beta=1.0)
-            gemm_nt(Sg, Uh, out=A[:, H:], beta=1.0)
-            h_sub = torch.empty(M, H, dtype=torch.float32, device=dev)
-            zh = torch.empty(M, 2 * H, dtype=torch.float32, device=dev)
-            call("ggpm_sparse_gru_out_fwd", M, H, fptr(A), 2 * H, fptr(S), fptr(h_sub), fptr(zh), stream_ptr(dev))
-            rows_scatter_(hw, sub, h_sub)
-            saved += [S, Hn, Pr, Sg, zh]
-        ctx.dims = (M, K, H, depth)
+        Xg = gemm_nt(x, Wx, bias=torch.cat([T[0, :2 * Hp], br]))    # the r pre-activation carries U_r's bias
+        hw = h.contiguous().clone()
+        Uz, Ur, Uh = Uz.contiguous(), Ur.contiguous(), Uh.contiguous()
+        S, Sg, zh = _stack(depth, M, Hp, dev), _stack(depth, M, Hp, dev), _stack(depth, M, 2 * Hp, dev)
+        Hn, rs = _stack(depth, M * K, Hp, dev), _stack(depth, M * K, Hp, dev)
+        A = torch.empty(M, 3 * Hp, dtype=torch.float32, device=dev)              # A [M, 2Hp] | h_sub
+        call("ggpm_sparse_gru_fwd", M, K, H, Hp, depth, fptr(hw), H, iptr(sub), iptr(nbr), fptr(Xg), fptr(Uz), fptr(Ur),
+             fptr(Uh), fptr(S), fptr(Hn), fptr(rs), fptr(Sg), fptr(zh), A.data_ptr(), A.data_ptr() + 8 * M * Hp,
+             stream_ptr(dev))
+        ctx.dims = (M, K, H, Hp, depth)
         ctx.sub, ctx.nbr = sub, nbr
-        ctx.save_for_backward(x, Wx, Uz, Uh, Ur, *saved)
+        ctx.save_for_backward(x, Wx, Uz, Ur, Uh, S, Hn, rs, Sg, zh)
         return hw
 
     @staticmethod
     def backward(ctx, dh):
-        M, K, H, depth = ctx.dims
+        M, K, H, Hp, depth = ctx.dims
         sub, nbr = ctx.sub, ctx.nbr
-        x, Wx, Uz, Uh, Ur, *saved = ctx.saved_tensors
+        x, Wx, Uz, Ur, Uh, S, Hn, rs, Sg, zh = ctx.saved_tensors
         dev = x.device
-        dHw = _rows(dh).contiguous().clone()
-        dXg = torch.zeros(M, 3 * H, dtype=torch.float32, device=dev)
-        dUz, dUh, dUr = torch.zeros_like(Uz), torch.zeros_like(Uh), torch.zeros_like(Ur)
-        dA = torch.empty(M, 2 * H, dtype=torch.float32, device=dev)
-        dS = torch.empty(M, H, dtype=torch.float32, device=dev)
-        dPr = torch.empty(M * K, H, dtype=torch.float32, device=dev)
-        dHn = torch.empty_like(dPr)
-        for t in reversed(range(depth)):
-            S, Hn, rs, Sg, zh = saved[5 * t: 5 * t + 5]
-            dh_sub, _ = rows_gather(dHw, sub, M, 1, total=False)
-            rows_scatter_(dHw, sub, None)
-            call("ggpm_sparse_gru_out_bwd", M, H, fptr(dh_sub), fptr(zh), fptr(S), fptr(dA), fptr(dS), fptr(dXg), 3 * H,
-                 stream_ptr(dev))
-            daz, dah = dA[:, :H], dA[:, H:]
-            gemm_nn(daz, Uz, out=dS, beta=1.0)
-            dSg = gemm_nn(dah, Uh)
-            gemm_tn(daz, S, out=dUz, beta=1.0)
-            gemm_tn(dah, Sg, out=dUh, beta=1.0)
-            call("ggpm_sparse_gru_gate_bwd", M, K, H, fptr(dSg), fptr(rs), fptr(Hn), fptr(dPr), fptr(dHn),
-                 fptr(dXg[:, 2 * H:]), 3 * H, stream_ptr(dev))
-            gemm_nn(dPr, Ur, out=dHn, beta=1.0)
-            gemm_tn(dPr, Hn, out=dUr, beta=1.0)
-            rows_scatter_add_(dHw, nbr, M, K, src=dHn, bcast=dS)
-        rows_scatter_(dHw, sub, None)
+        dHw = dh.contiguous().clone()
+        dXg = torch.empty(M, 3 * Hp, dtype=torch.float32, device=dev)
+        dUz, dUr, dUh = torch.empty_like(Uz), torch.empty_like(Ur), torch.empty_like(Uh)
+        rowbuf = torch.empty(M, 5 * Hp, dtype=torch.float32, device=dev)         # dA [M, 2Hp] | dS | dSg | dh_sub
+        pairbuf = torch.empty(2, M * K, Hp, dtype=torch.float32, device=dev)     # dPr | dHn
+        r, p, f4 = rowbuf.data_ptr(), pairbuf.data_ptr(), 4 * M * Hp
+        call("ggpm_sparse_gru_bwd", M, K, H, Hp, depth, fptr(dHw), H, iptr(sub), iptr(nbr), fptr(Uz), fptr(Ur), fptr(Uh),
+             fptr(S), fptr(Hn), fptr(rs), fptr(Sg), fptr(zh), fptr(dXg), fptr(dUz), fptr(dUr), fptr(dUh), r, r + 2 * f4,
+             r + 3 * f4, p, p + f4 * K, r + 4 * f4, stream_ptr(dev))
         dx = gemm_nn(dXg, Wx) if ctx.needs_input_grad[1] else None
-        dWx = gemm_tn(dXg, _rows(x))
-        db = torch.empty(3 * H, dtype=torch.float32, device=dev)
-        call("ggpm_colsum", fptr(dXg), 3 * H, M, 3 * H, fptr(db), 0, stream_ptr(dev))
-        return dHw, dx, dWx, db, dUz, dUh, dUr, None, None, None, None
+        dWx = gemm_tn(dXg, x)
+        dT = torch.empty(1, 3 * Hp, dtype=torch.float32, device=dev)
+        call("ggpm_colsum", fptr(dXg), 3 * Hp, M, 3 * Hp, fptr(dT), 0, stream_ptr(dev))
+        dbr = dT[0, 2 * Hp:].clone()
+        return dHw, dx, dWx, dT, dUz, dUr, dbr, dUh, None, None, None, None
 
 
 class SlotGatherSum(torch.autograd.Function):

@@ -84,12 +84,9 @@ class GRU(_GraphRNN):
         if submess.numel() == 0 or self.depth == 0:
             return h * 1.0 if submess.numel() == 0 else Fn.index_scatter(h.new_zeros(submess.numel(), h.shape[1]), h, submess)
         sub, nbr, K = self._sparse_args(h, fmess, submess, bgraph)
-        IN, H = self.input_size, self.hidden_size
-        Wx = torch.cat([self.W_z.weight[:, :IN], self.W_h.weight[:, :IN], self.W_r.weight], dim=0)
-        b = torch.cat([self.W_z.bias, self.W_h.bias, self.U_r.bias], dim=0)
-        return Fn.SparseGRU.apply(h, fmess, Wx, b, self.W_z.weight[:, IN:], self.W_h.weight[:, IN:], self.U_r.weight,
-                                  sub, nbr, K, self.depth)
-
+        Wx, T, Uz, Ur, br, Uh = packing.pack_gru(self, self.input_size, self.padded_hidden, 1)
+        return Fn.SparseGRU.apply(h, packing.feature_columns(fmess, self.input_size), Wx, T, Uz, Ur, br, Uh, sub, nbr, K,
+                                  self.depth)
 
 class LSTM(_GraphRNN):
 
@@ -134,9 +131,5 @@ class LSTM(_GraphRNN):
         sub, nbr, K = self._sparse_args(h, fmess, submess, bgraph)
         if c.shape != h.shape:
             raise ValueError("h and c tables differ in shape")
-        IN = self.input_size
-        gates = (self.W_i[0], self.W_o[0], self.W[0], self.W_f[0])
-        Wx = torch.cat([g.weight[:, :IN] for g in gates], dim=0)
-        b = torch.cat([g.bias for g in gates], dim=0)
-        U3 = torch.cat([g.weight[:, IN:] for g in gates[:3]], dim=0)
-        return Fn.SparseLSTM.apply(h, c, fmess, Wx, b, U3, self.W_f[0].weight[:, IN:], sub, nbr, K, self.depth)
+        Wx, T, U4 = packing.pack_lstm(self, self.input_size, self.padded_hidden, 1)
+        return Fn.SparseLSTM.apply(h, c, packing.feature_columns(fmess, self.input_size), Wx, T, U4, sub, nbr, K, self.depth)

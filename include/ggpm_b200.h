@@ -251,8 +251,11 @@ int ggpm_rsample_bwd(const float* Y, int ldy, int var_off, const float* eps, int
  * (ggpm/nnutils.py:124-128): M sub-messages of an R-row state table are recomputed for `depth` rounds, each round
  * reading the K padded neighbour slots of every sub-message from the whole table (slot 0 reads row 0, as
  * index_select_ND does; slots are not compacted because the decoder zeroes them mid-row, ggpm/decoder.py:72-83).
- * Row-major fp32 operands of arbitrary width; idx are int32 row ids of the table.
- *   rows_gather:      pairs [M*K, ld_p] = table[idx[p]] (may be NULL), sum [M, ld_s] = sum over the K slots (may be NULL)
+ * Row-major fp32 operands; tables of arbitrary width, idx are int32 row ids of the table.  The cell kernels take one
+ * width H for all their operands: callers run them at the padded width (multiple of 4 floats, zero tail) so that the
+ * H x H products around them run on the tensor-core GEMM engine; a zero tail stays zero through both cells.
+ *   rows_gather:      pairs [M*K, ld_p] = table[idx[p]] (may be NULL), sum [M, ld_s] = sum over the K slots (may be NULL);
+ *                     output columns [width, pad_to) are zero-filled (pad_to = width: none)
  *   rows_scatter:     table[idx[m]] = src[m]   (src NULL: zero the rows); idx must not repeat
  *   rows_scatter_add: table[idx[p]] += src[p] + bcast[p / K]   (either may be NULL) — backward of rows_gather
  *   sparse_lstm_cell_fwd: A [M, lda>=4H] pre-activations (i | o | u | f x-part), Pf / Cn [M*K, H] = U_f h_nei / c_nei
@@ -262,8 +265,8 @@ int ggpm_rsample_bwd(const float* Y, int ldy, int var_off, const float* eps, int
  *   sparse_gru_gate_bwd:  -> dPr, dHn [M*K, H] (dHn = direct term dSg * r), dXr [M, ldx] += sum_k dPr
  *   sparse_gru_out_fwd:   A [M, lda>=2H] pre-activations (z | h~), S [M, H] -> h_sub = (1-z) S + z h~; saves zh [M, 2H]
  *   sparse_gru_out_bwd:   -> dA [M, 2H], dS [M, H] = dh (1 - z); dXacc [M, ldx] columns [0, 2H) += dA */
-int ggpm_rows_gather(const float* table, int ld_t, const int32_t* idx, int M, int K, int width, float* pairs, int ld_p,
-                     float* sum, int ld_s, void* stream);
+int ggpm_rows_gather(const float* table, int ld_t, const int32_t* idx, int M, int K, int width, int pad_to, float* pairs,
+                     int ld_p, float* sum, int ld_s, void* stream);
 int ggpm_rows_scatter(float* table, int ld_t, const int32_t* idx, int M, int width, const float* src, int ld_s,
                       void* stream);
 int ggpm_rows_scatter_add(float* table, int ld_t, const int32_t* idx, int M, int K, int width, const float* src, int ld_s,
@@ -279,6 +282,30 @@ int ggpm_sparse_gru_gate_bwd(int M, int K, int H, const float* dSg, const float*
 int ggpm_sparse_gru_out_fwd(int M, int H, const float* A, int lda, const float* S, float* h_sub, float* zh, void* stream);
 int ggpm_sparse_gru_out_bwd(int M, int H, const float* dh, const float* zh, const float* S, float* dA, float* dS,
                             float* dXacc, int ldx, void* stream);
+
+/* Whole-call drivers of the incremental cells: all `depth` rounds of one sparse_forward (or of its backward) sequenced
+ * inside ONE call — per round: rows_gather, two (GRU: three) GEMMs, the cell kernel(s), rows_scatter.  Operands at the
+ * padded width Hp (multiple of 4, zero tail); tables hw / cw [R, ld_t] are the caller's copies of h / c (width H) and
+ * are updated in place; the backward pass updates the caller's copies of dh / dc in place into the input gradients.
+ * Xg [M, 4Hp] (LSTM: i | o | u | f) or [M, 3Hp] (GRU: z | h~ | r) = x-projection + biases; U4 [4Hp, Hp] = (U_i; U_o;
+ * U_u; U_f).  Stacks saved for the backward pass, one slice per round: S, Sg [depth, M, Hp]; Hn, Cn, fs, rs
+ * [depth, M*K, Hp]; gates [depth, M, 4Hp]; zh [depth, M, 2Hp].  Everything after the stacks is scratch of the sizes
+ * the per-kernel entries above take.  Backward outputs: dXg (zeroed here, then summed over the rounds) and the weight
+ * gradients dU4 / dUz / dUr / dUh (zeroed here). */
+int ggpm_sparse_lstm_fwd(int M, int K, int H, int Hp, int depth, float* hw, float* cw, int ld_t, const int32_t* sub,
+                         const int32_t* nbr, const float* Xg, const float* U4, float* S, float* Hn, float* Cn, float* gates,
+                         float* fs, float* A, float* h_sub, float* c_sub, void* stream);
+int ggpm_sparse_lstm_bwd(int M, int K, int H, int Hp, int depth, float* dHw, float* dCw, int ld_t, const int32_t* sub,
+                         const int32_t* nbr, const float* U4, const float* S, const float* Hn, const float* Cn,
+                         const float* gates, const float* fs, float* dXg, float* dU4, float* dA, float* dPf, float* dCn,
+                         float* dh_sub, float* dc_sub, float* dS, float* dHn, void* stream);
+int ggpm_sparse_gru_fwd(int M, int K, int H, int Hp, int depth, float* hw, int ld_t, const int32_t* sub, const int32_t* nbr,
+                        const float* Xg, const float* Uz, const float* Ur, const float* Uh, float* S, float* Hn, float* rs,
+                        float* Sg, float* zh, float* A, float* h_sub, void* stream);
+int ggpm_sparse_gru_bwd(int M, int K, int H, int Hp, int depth, float* dHw, int ld_t, const int32_t* sub, const int32_t* nbr,
+                        const float* Uz, const float* Ur, const float* Uh, const float* S, const float* Hn, const float* rs,
+                        const float* Sg, const float* zh, float* dXg, float* dUz, float* dUr, float* dUh, float* dA,
+                        float* dS, float* dSg, float* dPr, float* dHn, float* dh_sub, void* stream);
 
 /* ---- host-side index builder (no device work, no stream): SURVEY 8(f) rank 3 ----------------------------------
  * Replaces MolGraph.tensorize_graph (ggpm/mol_graph.py:238-281: Python dict / list loops per edge over networkx

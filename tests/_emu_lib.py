@@ -387,15 +387,16 @@ class EmuLib:
         return 0
 
     # -- incremental message passing (sparse.cu) ---------------------------------------------------
-    def ggpm_rows_gather(self, table, ld_t, idx, M, K, width, pairs, ld_p, total, ld_s, stream):
+    def ggpm_rows_gather(self, table, ld_t, idx, M, K, width, pad_to, pairs, ld_p, total, ld_s, stream):
         self._tick("rows_gather")
+        assert pad_to >= width and (not pairs or ld_p >= pad_to) and (not total or ld_s >= pad_to)
         ix = _i(idx, M * K).long()
         t = _tab(table, int(ix.max()) + 1, ld_t, width)
-        picked = t[ix]
+        picked = torch.nn.functional.pad(t[ix], (0, pad_to - width))
         if pairs:
-            _tab(pairs, M * K, ld_p, width).copy_(picked)
+            _tab(pairs, M * K, ld_p, pad_to).copy_(picked)
         if total:
-            _tab(total, M, ld_s, width).copy_(picked.to(DT).reshape(M, K, width).sum(1).float())
+            _tab(total, M, ld_s, pad_to).copy_(picked.to(DT).reshape(M, K, pad_to).sum(1).float())
         return 0
 
     def ggpm_rows_scatter(self, table, ld_t, idx, M, width, src, ld_s, stream):
@@ -489,4 +490,91 @@ class EmuLib:
         _tab(dS, M, H, H).copy_((g * (1 - z)).float())
         x = _tab(dXacc, M, ldx, 2 * H)
         x.copy_((x.to(DT) + d).float())
+        return 0
+
+    # -- whole-call drivers (mirror the sequencing of sparse.cu on host addresses) ------------------
+    def _g(self, A, lda, W, ldw, C, ldc, M, N, K, beta):          # C (+)= A @ W^T
+        return self.ggpm_gemm(A, lda, 1, W, 1, ldw, C, ldc, M, N, K, beta, None, 0, 0, 1, None)
+
+    def _gb(self, dY, ldy, W, ldw, dX, ldx, M, N, K, beta):       # dX (+)= dY @ W
+        return self.ggpm_gemm(dY, ldy, 1, W, ldw, 1, dX, ldx, M, N, K, beta, None, 0, 0, 1, None)
+
+    def _gw(self, dY, ldy, X, ldx, dW, ldw, N, Kw, rows):         # dW += dY^T @ X
+        return self.ggpm_gemm(dY, 1, ldy, X, ldx, 1, dW, ldw, N, Kw, rows, 1.0, None, 0, 0, 1, None)
+
+    def ggpm_sparse_lstm_fwd(self, M, K, H, Hp, depth, hw, cw, ld_t, sub, nbr, Xg, U4, S, Hn, Cn, gates, fs, A, h_sub,
+                             c_sub, stream):
+        row, pair = 4 * M * Hp, 4 * M * K * Hp          # bytes
+        self.ggpm_rows_scatter(hw, ld_t, sub, M, H, None, 0, None)
+        self.ggpm_rows_scatter(cw, ld_t, sub, M, H, None, 0, None)
+        for t in range(depth):
+            S_t, Hn_t, Cn_t, fs_t = S + t * row, Hn + t * pair, Cn + t * pair, fs + t * pair
+            self.ggpm_rows_gather(hw, ld_t, nbr, M, K, H, Hp, Hn_t, Hp, S_t, Hp, None)
+            self.ggpm_rows_gather(cw, ld_t, nbr, M, K, H, Hp, Cn_t, Hp, None, 0, None)
+            _f(A, 4 * M * Hp).copy_(_f(Xg, 4 * M * Hp))
+            self._g(S_t, Hp, U4, Hp, A, 4 * Hp, M, 3 * Hp, Hp, 1.0)
+            self._g(Hn_t, Hp, U4 + 4 * 3 * Hp * Hp, Hp, fs_t, Hp, M * K, Hp, Hp, 0.0)
+            self.ggpm_sparse_lstm_cell_fwd(M, K, Hp, A, 4 * Hp, fs_t, Cn_t, h_sub, c_sub, gates + t * 4 * row, fs_t, None)
+            self.ggpm_rows_scatter(hw, ld_t, sub, M, H, h_sub, Hp, None)
+            self.ggpm_rows_scatter(cw, ld_t, sub, M, H, c_sub, Hp, None)
+        return 0
+
+    def ggpm_sparse_lstm_bwd(self, M, K, H, Hp, depth, dHw, dCw, ld_t, sub, nbr, U4, S, Hn, Cn, gates, fs, dXg, dU4, dA,
+                             dPf, dCn, dh_sub, dc_sub, dS, dHn, stream):
+        row, pair = 4 * M * Hp, 4 * M * K * Hp
+        Uf, dUf = U4 + 4 * 3 * Hp * Hp, dU4 + 4 * 3 * Hp * Hp
+        _f(dXg, 4 * M * Hp).zero_()
+        _f(dU4, 4 * Hp * Hp).zero_()
+        for t in reversed(range(depth)):
+            S_t, Hn_t, Cn_t, fs_t = S + t * row, Hn + t * pair, Cn + t * pair, fs + t * pair
+            self.ggpm_rows_gather(dHw, ld_t, sub, M, 1, H, Hp, dh_sub, Hp, None, 0, None)
+            self.ggpm_rows_gather(dCw, ld_t, sub, M, 1, H, Hp, dc_sub, Hp, None, 0, None)
+            self.ggpm_rows_scatter(dHw, ld_t, sub, M, H, None, 0, None)
+            self.ggpm_rows_scatter(dCw, ld_t, sub, M, H, None, 0, None)
+            self.ggpm_sparse_lstm_cell_bwd(M, K, Hp, dh_sub, dc_sub, gates + t * 4 * row, fs_t, Cn_t, dA, dPf, dCn, dXg, None)
+            self._gb(dA, 4 * Hp, U4, Hp, dS, Hp, M, Hp, 3 * Hp, 0.0)
+            self._gb(dPf, Hp, Uf, Hp, dHn, Hp, M * K, Hp, Hp, 0.0)
+            self._gw(dA, 4 * Hp, S_t, Hp, dU4, Hp, 3 * Hp, Hp, M)
+            self._gw(dPf, Hp, Hn_t, Hp, dUf, Hp, Hp, Hp, M * K)
+            self.ggpm_rows_scatter_add(dHw, ld_t, nbr, M, K, H, dHn, Hp, dS, Hp, None)
+            self.ggpm_rows_scatter_add(dCw, ld_t, nbr, M, K, H, dCn, Hp, None, 0, None)
+        self.ggpm_rows_scatter(dHw, ld_t, sub, M, H, None, 0, None)
+        self.ggpm_rows_scatter(dCw, ld_t, sub, M, H, None, 0, None)
+        return 0
+
+    def ggpm_sparse_gru_fwd(self, M, K, H, Hp, depth, hw, ld_t, sub, nbr, Xg, Uz, Ur, Uh, S, Hn, rs, Sg, zh, A, h_sub, stream):
+        row, pair = 4 * M * Hp, 4 * M * K * Hp
+        self.ggpm_rows_scatter(hw, ld_t, sub, M, H, None, 0, None)
+        for t in range(depth):
+            S_t, Hn_t, rs_t, Sg_t = S + t * row, Hn + t * pair, rs + t * pair, Sg + t * row
+            self.ggpm_rows_gather(hw, ld_t, nbr, M, K, H, Hp, Hn_t, Hp, S_t, Hp, None)
+            self._g(Hn_t, Hp, Ur, Hp, rs_t, Hp, M * K, Hp, Hp, 0.0)
+            self.ggpm_sparse_gru_gate_fwd(M, K, Hp, Xg + 4 * 2 * Hp, 3 * Hp, rs_t, Hn_t, rs_t, Sg_t, None)
+            _tab(A, M, 2 * Hp, 2 * Hp).copy_(_tab(Xg, M, 3 * Hp, 2 * Hp))
+            self._g(S_t, Hp, Uz, Hp, A, 2 * Hp, M, Hp, Hp, 1.0)
+            self._g(Sg_t, Hp, Uh, Hp, A + 4 * Hp, 2 * Hp, M, Hp, Hp, 1.0)
+            self.ggpm_sparse_gru_out_fwd(M, Hp, A, 2 * Hp, S_t, h_sub, zh + t * 2 * row, None)
+            self.ggpm_rows_scatter(hw, ld_t, sub, M, H, h_sub, Hp, None)
+        return 0
+
+    def ggpm_sparse_gru_bwd(self, M, K, H, Hp, depth, dHw, ld_t, sub, nbr, Uz, Ur, Uh, S, Hn, rs, Sg, zh, dXg, dUz, dUr, dUh,
+                            dA, dS, dSg, dPr, dHn, dh_sub, stream):
+        row, pair = 4 * M * Hp, 4 * M * K * Hp
+        _f(dXg, 3 * M * Hp).zero_()
+        for d in (dUz, dUr, dUh):
+            _f(d, Hp * Hp).zero_()
+        for t in reversed(range(depth)):
+            S_t, Hn_t, rs_t, Sg_t = S + t * row, Hn + t * pair, rs + t * pair, Sg + t * row
+            self.ggpm_rows_gather(dHw, ld_t, sub, M, 1, H, Hp, dh_sub, Hp, None, 0, None)
+            self.ggpm_rows_scatter(dHw, ld_t, sub, M, H, None, 0, None)
+            self.ggpm_sparse_gru_out_bwd(M, Hp, dh_sub, zh + t * 2 * row, S_t, dA, dS, dXg, 3 * Hp, None)
+            self._gb(dA, 2 * Hp, Uz, Hp, dS, Hp, M, Hp, Hp, 1.0)
+            self._gb(dA + 4 * Hp, 2 * Hp, Uh, Hp, dSg, Hp, M, Hp, Hp, 0.0)
+            self._gw(dA, 2 * Hp, S_t, Hp, dUz, Hp, Hp, Hp, M)
+            self._gw(dA + 4 * Hp, 2 * Hp, Sg_t, Hp, dUh, Hp, Hp, Hp, M)
+            self.ggpm_sparse_gru_gate_bwd(M, K, Hp, dSg, rs_t, Hn_t, dPr, dHn, dXg + 4 * 2 * Hp, 3 * Hp, None)
+            self._gb(dPr, Hp, Ur, Hp, dHn, Hp, M * K, Hp, Hp, 1.0)
+            self._gw(dPr, Hp, Hn_t, Hp, dUr, Hp, Hp, Hp, M * K)
+            self.ggpm_rows_scatter_add(dHw, ld_t, nbr, M, K, H, dHn, Hp, dS, Hp, None)
+        self.ggpm_rows_scatter(dHw, ld_t, sub, M, H, None, 0, None)
         return 0
