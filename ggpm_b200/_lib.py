@@ -143,9 +143,18 @@ def iptr(t: torch.Tensor, what: str = "index"):
     return t.data_ptr()
 
 
+_RAW_STREAM = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr(device=None):
+    """cudaStream_t of torch's current stream on `device` (the library launches on it)"""
     if _TEST_BACKEND is not None:
         return None
+    if _RAW_STREAM is not None:          # same value as current_stream(device).cuda_stream without building a Stream object
+        if isinstance(device, torch.device) and device.index is not None:
+            return _RAW_STREAM(device.index)
+        return _RAW_STREAM(torch.cuda.current_device() if device is None or getattr(device, "index", None) is None
+                           else device.index)
     return torch.cuda.current_stream(device).cuda_stream
 
 

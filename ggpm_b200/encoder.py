@@ -237,9 +237,17 @@ class MotifEncoder(nn.Module):
 # incremental encoders driven by the decoder: ggpm/encoder.py:160-249, 344-394
 # ----------------------------------------------------------------------------------------------------------------
 def _linear_seq(seq, parts, widths):
-    """nn.Sequential(Linear, ReLU, Dropout) applied to the concatenation of `parts` without building it"""
-    out = Fn.linear_act_split(parts, seq[0].weight, widths, seq[0].bias, act=ACT_RELU)      # [M, Np], tensor-core shapes
-    H = seq[0].out_features
+    """nn.Sequential(Linear, ReLU, Dropout) on the concatenation of `parts`.  The incremental steps touch few rows, so
+    the reference's own shape is the cheapest: one small torch.cat and ONE GEMM against the unsplit weight (its row
+    length F + H is a multiple of 4 in every layer of the path, which keeps it on the tensor-core engine); the output
+    is produced at a 4-float row pitch and returned as its [:, :H] view."""
+    lin = seq[0]
+    H = lin.out_features
+    if sum(widths) % 4 == 0:
+        A = torch.cat([p[:, :k] for p, k in zip(parts, widths)], dim=1)
+        out = Fn.linear_act([A], [lin.weight], lin.bias, act=ACT_RELU, out_width=Fn.round_up(H, 4))
+    else:
+        out = Fn.linear_act_split(parts, lin.weight, widths, lin.bias, act=ACT_RELU)
     return seq[2](out if out.shape[1] == H else out[:, :H])
 
 
