@@ -55,16 +55,29 @@ rows_scatter_kernel(float* __restrict__ table, int ld_t, const int32_t* __restri
     }
 }
 
+// Most padded slots hold 0 (mean fill of a neighbour row is 1.4 of 4-7 slots), so a plain scatter-add would send the
+// majority of its atomics to the `width` addresses of table row 0.  Row-0 contributions are therefore summed per block
+// in shared memory first and flushed with one global atomic per column and block.
 __global__ void __launch_bounds__(kSpThreads)
 rows_scatter_add_kernel(float* __restrict__ table, int ld_t, const int32_t* __restrict__ idx, int M, int K, int width,
                         const float* __restrict__ src, int ld_s, const float* __restrict__ bcast, int ld_b) {
+    extern __shared__ float row0[];          // [width]
+    for (int j = threadIdx.x; j < width; j += blockDim.x) row0[j] = 0.f;
+    __syncthreads();
     const long long n = (long long)M * K * width;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         const long long p = i / width;
         const int j = (int)(i % width);
         float v = src != nullptr ? src[(size_t)p * ld_s + j] : 0.f;
         if (bcast != nullptr) v += bcast[(size_t)(p / K) * ld_b + j];
-        atomicAdd(&table[(size_t)idx[p] * ld_t + j], v);
+        const int r = idx[p];
+        if (r == 0) atomicAdd(&row0[j], v);
+        else atomicAdd(&table[(size_t)r * ld_t + j], v);
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < width; j += blockDim.x) {
+        const float v = row0[j];
+        if (v != 0.f) atomicAdd(&table[j], v);
     }
 }
 
@@ -236,8 +249,12 @@ extern "C" int ggpm_rows_scatter_add(float* table, int ld_t, const int32_t* idx,
     GGPM_REQUIRE((!src || ld_s >= width) && (!bcast || ld_b >= width), "rows_scatter_add: bad leading dimension");
     cudaStream_t st = (cudaStream_t)stream;
     ProfScope prof(PROF_GATHER, st, (double)M * K * width * 12.0);
-    rows_scatter_add_kernel<<<sp_blocks((long long)M * K * width), kSpThreads, 0, st>>>(table, ld_t, idx, M, K, width, src,
-                                                                                       ld_s, bcast, ld_b);
+    GGPM_REQUIRE(width <= 12288, "rows_scatter_add: rows wider than 12288 floats are not supported");
+    // few, fat blocks: every block ends with one flush of its row-0 partial sums
+    long long blocks = ceil_div_ll((long long)M * K * width, (long long)kSpThreads * 8);
+    if (blocks > 2LL * sm_count()) blocks = 2LL * sm_count();
+    rows_scatter_add_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), kSpThreads, sizeof(float) * (size_t)width, st>>>(
+        table, ld_t, idx, M, K, width, src, ld_s, bcast, ld_b);
     return check_launch("rows_scatter_add");
 }
 
