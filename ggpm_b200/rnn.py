@@ -31,6 +31,21 @@ class _GraphRNN(nn.Module):
     def padded_hidden(self):
         return Fn.padded_width(self.hidden_size)
 
+    def _packed_for_steps(self, pack):
+        """Packed gate weights for sparse_forward, reused while the parameters are unchanged.  The decoder calls
+        sparse_forward once per step (~37 times per batch) with the same weights; sharing ONE packing node between those
+        calls means one pack launch per batch instead of one per step and, in the backward pass, one summed gradient
+        per packed operand and one unpack.  The key holds every parameter's storage address and version counter
+        (optimizer steps, load_state_dict and in-place initialisers bump it) plus the autograd mode."""
+        params = list(self.parameters())
+        key = (torch.is_grad_enabled(), self.padded_hidden) + tuple((p.data_ptr(), p._version, p.requires_grad, p.device)
+                                                                    for p in params)
+        cached = getattr(self, "_step_pack", None)
+        if cached is None or cached[0] != key:
+            cached = (key, pack(self, self.input_size, self.padded_hidden, 1))
+            object.__setattr__(self, "_step_pack", cached)        # plain attribute: not a parameter / buffer / submodule
+        return cached[1]
+
     def _sparse_args(self, h, fmess, submess, bgraph):
         """validated (sub [M] int32, nbr [M*K] int32, K) of a sparse_forward call"""
         if fmess.dim() != 2 or fmess.shape[1] != self.input_size or fmess.dtype != torch.float32:
@@ -84,7 +99,7 @@ class GRU(_GraphRNN):
         if submess.numel() == 0 or self.depth == 0:
             return h * 1.0 if submess.numel() == 0 else Fn.index_scatter(h.new_zeros(submess.numel(), h.shape[1]), h, submess)
         sub, nbr, K = self._sparse_args(h, fmess, submess, bgraph)
-        Wx, T, Uz, Ur, br, Uh = packing.pack_gru(self, self.input_size, self.padded_hidden, 1)
+        Wx, T, Uz, Ur, br, Uh = self._packed_for_steps(packing.pack_gru)
         return Fn.SparseGRU.apply(h, packing.feature_columns(fmess, self.input_size), Wx, T, Uz, Ur, br, Uh, sub, nbr, K,
                                   self.depth)
 
@@ -131,5 +146,5 @@ class LSTM(_GraphRNN):
         sub, nbr, K = self._sparse_args(h, fmess, submess, bgraph)
         if c.shape != h.shape:
             raise ValueError("h and c tables differ in shape")
-        Wx, T, U4 = packing.pack_lstm(self, self.input_size, self.padded_hidden, 1)
+        Wx, T, U4 = self._packed_for_steps(packing.pack_lstm)
         return Fn.SparseLSTM.apply(h, c, packing.feature_columns(fmess, self.input_size), Wx, T, U4, sub, nbr, K, self.depth)

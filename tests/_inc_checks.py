@@ -157,3 +157,54 @@ def check_sparse_forward_cell(rnn_type, device, H=10, IN=7, depth=3):
     for k, p in cell.named_parameters():
         assert rel(p.grad, sd["rnn." + k].grad) <= TOL_GRAD, (k, rel(p.grad, sd["rnn." + k].grad))
     assert torch.equal(hp.detach().cpu(), h0), "sparse_forward must not modify the incoming table"
+
+
+def check_packed_weight_reuse(device):
+    """sparse_forward shares one packing of the gate weights between calls while the parameters are unchanged: two
+    calls inside one graph, a second forward + backward after the first graph was consumed, and an in-place update of a
+    parameter (as an optimizer step does) must all give the oracle's values and gradients"""
+    gen = torch.Generator().manual_seed(23)
+    H, IN, R = 12, 6, 8
+    cell = ggpm_b200.LSTM(IN, H, 2)
+    for p in cell.parameters():
+        p.data = torch.randn(p.shape, generator=gen) * 0.3
+    cell = cell.to(device)
+    h0, c0 = torch.randn(R, H, generator=gen), torch.randn(R, H, generator=gen)
+    x1, x2 = torch.randn(2, IN, generator=gen), torch.randn(3, IN, generator=gen)
+    s1, b1 = torch.tensor([3, 5]), torch.tensor([[1, 0, 2], [3, 0, 0]])
+    s2, b2 = torch.tensor([1, 2, 6]), torch.tensor([[3, 5, 0], [0, 0, 0], [5, 1, 7]])
+
+    def product():
+        st = (h0.clone().to(device), c0.clone().to(device))
+        st = cell.sparse_forward(st, x1.to(device), s1.to(device), b1.to(device))
+        st = cell.sparse_forward(st, x2.to(device), s2.to(device), b2.to(device))
+        cell.zero_grad(set_to_none=True)
+        (st[0].sum() + 2 * st[1].sum()).backward()
+        return st, {k: p.grad.detach().cpu().clone() for k, p in cell.named_parameters()}
+
+    def oracle():
+        sd = {"rnn." + k: v.detach().cpu().double().requires_grad_(True) for k, v in cell.state_dict().items()}
+        st = (h0.double(), c0.double())
+        st = io.sparse_forward(sd, "rnn.", "LSTM", st, x1.double(), s1, b1, 2)
+        st = io.sparse_forward(sd, "rnn.", "LSTM", st, x2.double(), s2, b2, 2)
+        (st[0].sum() + 2 * st[1].sum()).backward()
+        return st, {k[4:]: v.grad for k, v in sd.items()}
+
+    def same(a, b):
+        (sa, ga), (sb, gb) = a, b
+        assert rel(sa[0], sb[0]) <= TOL_OUT and rel(sa[1], sb[1]) <= TOL_OUT
+        for k in gb:
+            assert rel(ga[k], gb[k]) <= TOL_GRAD, (k, rel(ga[k], gb[k]))
+
+    same(product(), oracle())
+    pack_a = cell._step_pack[1][0]
+    same(product(), oracle())                               # second loop on unchanged weights reuses the packing
+    assert cell._step_pack[1][0] is pack_a
+    with torch.no_grad():
+        cell.W_f[0].weight.add_(0.05)                       # what an optimizer step does
+        cell.W[0].bias.mul_(-1.0)
+    same(product(), oracle())
+    assert cell._step_pack[1][0] is not pack_a
+    with torch.no_grad():                                   # no graph in no_grad mode: separate packing
+        out = cell.sparse_forward((h0.clone().to(device), c0.clone().to(device)), x1.to(device), s1.to(device), b1.to(device))
+    assert not out[0].requires_grad

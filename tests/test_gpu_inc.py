@@ -58,3 +58,7 @@ def test_cpu_tables_are_rejected():
     h = (torch.zeros(6, 8), torch.zeros(6, 8))
     with pytest.raises(RuntimeError, match="CUDA devices only"):
         cell.sparse_forward(h, torch.zeros(2, 5), torch.tensor([1, 2]), torch.zeros(2, 3, dtype=torch.long))
+
+
+def test_packed_weights_are_reused_until_parameters_change():
+    IC.check_packed_weight_reuse(DEV)

@@ -117,3 +117,7 @@ def test_sparse_forward_rejects_mismatched_arguments(emu):
         cell.sparse_forward(h, torch.zeros(2, 4), torch.tensor([1, 2]), torch.zeros(2, 3, dtype=torch.long))
     with pytest.raises(ValueError):
         cell.sparse_forward(h, torch.zeros(2, 5), torch.tensor([1, 2, 3]), torch.zeros(2, 3, dtype=torch.long))
+
+
+def test_packed_weights_are_reused_until_parameters_change(emu):
+    IC.check_packed_weight_reuse("cpu")

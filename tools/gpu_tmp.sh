@@ -1,6 +1,7 @@
-for wl in cfg3s; do
-for bn in 0 128 0 128; do
-GGPM_F16_BN_FWDP=$bn timeout 600 python bench.py --workload $wl --no-cpu-baseline --steps 10 > gpurun_out/s70_b.json 2> gpurun_out/s70_b.err; tail -1 gpurun_out/s70_b.err
-echo "$wl fwdp=$bn: $(python tools/bench_summary.py gpurun_out/s70_b.json | grep 'mol\|gemm_tcgen05 ' | tr '\n' ' ' | cut -c1-300)"
-done
-done
+set -x
+T=${TAG:-tmp}
+python -c "import __graft_entry__ as g; g.build(); g.smoke()" > gpurun_out/${T}_smoke.log 2>&1; echo "smoke exit $?"; tail -1 gpurun_out/${T}_smoke.log
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest exit $?"; tail -2 gpurun_out/${T}_pytest.log
+timeout 300 python tools/inc_time.py > gpurun_out/${T}_inc_time.json 2> gpurun_out/${T}_inc_time.err; cat gpurun_out/${T}_inc_time.json
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo "bench exit $?"; tail -2 gpurun_out/${T}_bench.err
+python tools/bench_summary.py gpurun_out/${T}_bench.json
