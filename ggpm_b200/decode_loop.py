@@ -85,7 +85,22 @@ def run_decode(enc, hier: bool, tree_tensors, graph_tensors, sched, init_vecs, d
     """Drive `enc` through the schedule.  tree_tensors / graph_tensors: torch.long tensors (+ scope list) on `device`.
     Returns a list of float tensors in a fixed order: per step the node rows, message rows and atom rows the decoder
     reads (topology / cluster / attachment predictions, ggpm/decoder.py:226-259), then the final state tables."""
-    lt = lambda lst: torch.tensor(lst, dtype=torch.long, device=device)
+    steps = sched["steps"] if max_steps is None else sched["steps"][:max_steps]
+    # Every index list of the schedule goes to the device in ONE copy before the loop (teacher forcing: the order is
+    # known up front).  A torch.tensor(list, device=...) per step, as ggpm/decoder.py:213-214 does, is a pageable
+    # host-to-device copy that makes the host wait for the stream four times per step.
+    root_out = sched["root_out"]
+    lists = [sched["first_atoms"], sched["first_bonds"], [r for r, _ in tree_tensors[-1]],
+             [m for ms in root_out for m in ms], [i for i, ms in enumerate(root_out) for _ in ms]]
+    for st in steps:
+        lists += [st["nodes"], st["mess"], st["next_atoms"], st["next_bonds"]]
+    flat = torch.tensor([v for lst in lists for v in lst], dtype=torch.long)
+    if torch.device(device).type == "cuda":
+        flat = flat.pin_memory().to(device, non_blocking=True)
+    offs = np.cumsum([0] + [len(lst) for lst in lists])
+    staged = [flat[offs[i]:offs[i + 1]] for i in range(len(lists))]
+    first_atoms, first_bonds, roots, root_mess, root_mess_mol = staged[:5]
+    step_lists = [staged[5 + 4 * i: 9 + 4 * i] for i in range(len(steps))]
     fnode, fmess, agraph, bgraph, cgraph, scope = tree_tensors
     B, num_mess = len(scope), fmess.shape[0]
     rnn = enc.tree_encoder.rnn
@@ -93,10 +108,8 @@ def run_decode(enc, hier: bool, tree_tensors, graph_tensors, sched, init_vecs, d
 
     # init_decoder_state (ggpm/decoder.py:102-120): one extra state row per molecule, wired into the root's rows
     agraph, bgraph = agraph.clone(), bgraph.clone()
-    for i, (root, _) in enumerate(scope):
-        agraph[root, -1] = num_mess + i
-        for m in sched["root_out"][i]:
-            bgraph[m, -1] = num_mess + i
+    agraph[roots, -1] = num_mess + torch.arange(B, dtype=agraph.dtype, device=agraph.device)
+    bgraph[root_mess, -1] = num_mess + root_mess_mol.to(bgraph.dtype)
     tree_tensors = [fnode, fmess, agraph, bgraph, cgraph, scope]
     htree = HTuple(mess=rnn.get_init_state(fmess, init_vecs),
                    emask=torch.cat([bgraph.new_zeros(num_mess), bgraph.new_ones(B)], dim=0))
@@ -105,15 +118,14 @@ def run_decode(enc, hier: bool, tree_tensors, graph_tensors, sched, init_vecs, d
         hinter = HTuple(mess=rnn.get_init_state(fmess), emask=bgraph.new_zeros(num_mess))
         hgraph = HTuple(mess=rnn.get_init_state(graph_tensors[1]), vmask=bgraph.new_zeros(graph_tensors[0].shape[0]),
                         emask=bgraph.new_zeros(graph_tensors[1].shape[0]))
-        atoms, bonds = lt(sched["first_atoms"]), lt(sched["first_bonds"])
+        atoms, bonds = first_atoms, first_bonds
         hgraph.vmask.scatter_(0, atoms, 1)
         hgraph.emask.scatter_(0, bonds, 1)
         subgraph = (atoms, bonds)
         graph_tensors = tuple(enc.embed_graph(graph_tensors)) + (graph_tensors[-1],)
 
-    steps = sched["steps"] if max_steps is None else sched["steps"][:max_steps]
-    for st in steps:
-        subtree = (lt(st["nodes"]), lt(st["mess"]))
+    for nodes, mess, next_atoms, next_bonds in step_lists:
+        subtree = (nodes, mess)
         htree.emask.scatter_(0, subtree[1], 1)
         t_f, t_m, t_a, t_b, t_c, t_s = tree_tensors
         if hier:
@@ -134,7 +146,7 @@ def run_decode(enc, hier: bool, tree_tensors, graph_tensors, sched, init_vecs, d
         if len(subtree[1]) > 0:
             outs.append(rnn.get_hidden_state(htree.mess).index_select(0, subtree[1]))
         if hier:
-            atoms, bonds = lt(st["next_atoms"]), lt(st["next_bonds"])
+            atoms, bonds = next_atoms, next_bonds
             if len(atoms) > 0:
                 hgraph.vmask.scatter_(0, atoms, 1)
             if len(bonds) > 0:

@@ -266,9 +266,7 @@ class IncMPNEncoder(MPNEncoder):
         nei_message = Fn.slot_gather_sum(self.rnn.get_hidden_state(h), agraph)
         F = self.W_o[0].in_features - self.hidden_size
         node_hiddens = _linear_seq(self.W_o, [fnode, nei_message], [F, self.hidden_size])
-        node_buf = torch.zeros(num_nodes, self.hidden_size, device=node_hiddens.device)
-        node_hiddens = Fn.index_scatter(node_hiddens, node_buf, subnode)
-        return node_hiddens, h
+        return Fn.scatter_into_zeros(node_hiddens, subnode, num_nodes), h      # index_scatter into a zero node_buf
 
 
 def _sub_tensors(tensors, subset):
@@ -285,7 +283,7 @@ def _sub_tensors(tensors, subset):
 def _sub_message_inputs(hnode, fmess, subnode, num_nodes, E_pos):
     """x of the sub-messages: [features of the source node | one-hot position] (ggpm/encoder.py:224-229); only nodes in
     `subnode` carry features — any other source reads a zero row, as the reference's scattered node_buf does"""
-    node_buf = Fn.index_scatter(hnode, torch.zeros(num_nodes, hnode.shape[1], device=hnode.device), subnode)
+    node_buf = Fn.scatter_into_zeros(hnode, subnode, num_nodes)
     hmess = Fn.slot_gather_sum(node_buf, fmess[:, 0])
     return torch.cat([hmess, E_pos.index_select(0, fmess[:, 2])], dim=-1)
 

@@ -657,6 +657,30 @@ class IndexScatter(torch.autograd.Function):
         return d_sub, d_tab, None
 
 
+class ScatterIntoZeros(torch.autograd.Function):
+    """index_scatter(sub, zeros(R, W), index) — the node_buf pattern of ggpm/encoder.py:176-178, 224-226 — without the
+    table copies: one memset + one row scatter forward, one row gather backward."""
+
+    @staticmethod
+    def forward(ctx, sub, idx, R):
+        out = torch.zeros(R, sub.shape[1], dtype=torch.float32, device=sub.device)
+        rows_scatter_(out, idx, sub)
+        ctx.idx = idx
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        return rows_gather(_rows(dout), ctx.idx, ctx.idx.numel(), 1, total=False)[0], None, None
+
+
+def scatter_into_zeros(sub_data, index, n_rows):
+    if sub_data.shape[0] != index.numel():
+        raise ValueError("scatter_into_zeros: %d rows for %d indices" % (sub_data.shape[0], index.numel()))
+    if index.numel() == 0:
+        return sub_data.new_zeros(n_rows, sub_data.shape[1])
+    return ScatterIntoZeros.apply(_rows(sub_data), row_ids(index.reshape(-1), n_rows), n_rows)
+
+
 def index_scatter(sub_data, all_data, index):
     if sub_data.shape[0] != index.numel() or sub_data.shape[1] != all_data.shape[1]:
         raise ValueError("index_scatter: sub_data %s does not match index %d / table %s"
