@@ -4,11 +4,16 @@ order (so state_dicts interchange), same forward(fmess, bgraph) contract; the ar
 libggpm_b200.so (hoisted x-projection, CSR neighbour lists, hand-written BPTT)."""
 from __future__ import annotations
 
+import weakref
+
 import torch
 import torch.nn as nn
 
 from . import functional as Fn
 from . import packing
+
+
+_STEP_PACKS = weakref.WeakKeyDictionary()      # module -> (key, packed operands), see _GraphRNN._packed_for_steps
 
 
 def _identity_graph(fmess: torch.Tensor, bgraph: torch.Tensor) -> Fn.MessageGraph:
@@ -40,10 +45,10 @@ class _GraphRNN(nn.Module):
         params = list(self.parameters())
         key = (torch.is_grad_enabled(), self.padded_hidden) + tuple((p.data_ptr(), p._version, p.requires_grad, p.device)
                                                                     for p in params)
-        cached = getattr(self, "_step_pack", None)
+        cached = _STEP_PACKS.get(self)
         if cached is None or cached[0] != key:
             cached = (key, pack(self, self.input_size, self.padded_hidden, 1))
-            object.__setattr__(self, "_step_pack", cached)        # plain attribute: not a parameter / buffer / submodule
+            _STEP_PACKS[self] = cached      # kept beside the module, not on it: deepcopy / pickle / state_dict never see it
         return cached[1]
 
     def _sparse_args(self, h, fmess, submess, bgraph):

@@ -197,14 +197,17 @@ def check_packed_weight_reuse(device):
             assert rel(ga[k], gb[k]) <= TOL_GRAD, (k, rel(ga[k], gb[k]))
 
     same(product(), oracle())
-    pack_a = cell._step_pack[1][0]
+    from ggpm_b200 import rnn as grnn
+    pack_a = grnn._STEP_PACKS[cell][1][0]
     same(product(), oracle())                               # second loop on unchanged weights reuses the packing
-    assert cell._step_pack[1][0] is pack_a
+    assert grnn._STEP_PACKS[cell][1][0] is pack_a
     with torch.no_grad():
         cell.W_f[0].weight.add_(0.05)                       # what an optimizer step does
         cell.W[0].bias.mul_(-1.0)
     same(product(), oracle())
-    assert cell._step_pack[1][0] is not pack_a
+    assert grnn._STEP_PACKS[cell][1][0] is not pack_a
+    import copy
+    copy.deepcopy(cell)                                     # the cache must not ride along with the module
     with torch.no_grad():                                   # no graph in no_grad mode: separate packing
         out = cell.sparse_forward((h0.clone().to(device), c0.clone().to(device)), x1.to(device), s1.to(device), b1.to(device))
     assert not out[0].requires_grad
