@@ -121,3 +121,49 @@ def test_sparse_forward_rejects_mismatched_arguments(emu):
 
 def test_packed_weights_are_reused_until_parameters_change(emu):
     IC.check_packed_weight_reuse("cpu")
+
+
+@pytest.mark.skipif(not reference_available(), reason="reference checkout not present (GPU box)")
+@pytest.mark.parametrize("kind,rnn", [("hier", "LSTM"), ("hier", "GRU"), ("motif", "LSTM")])
+def test_state_dict_interchanges_with_live_reference(emu, kind, rnn):
+    """same keys, shapes and registration order as the reference's Inc classes; strict loads both ways"""
+    from ggpm_b200 import encoder as genc
+    ref = load_reference()
+    args = (FakePairVocab(30, 40), IdAtomVocab(), rnn, 16, 16, 2, 3, 0.0)
+    r = (ref.encoder.IncHierMPNEncoder if kind == "hier" else ref.encoder.IncEncoder)(*args)
+    m = (genc.IncHierMPNEncoder if kind == "hier" else genc.IncEncoder)(*args)
+    rs, ms = r.state_dict(), m.state_dict()
+    assert list(rs.keys()) == list(ms.keys())
+    assert [tuple(v.shape) for v in rs.values()] == [tuple(v.shape) for v in ms.values()]
+    assert [n for n, _ in r.named_parameters()] == [n for n, _ in m.named_parameters()]
+    m.load_state_dict(rs, strict=True)
+    r.load_state_dict(ms, strict=True)
+    assert not hasattr(m, "W_root") and not hasattr(r, "W_root")
+    for name in ("get_sub_tensor", "embed_sub_tree", "forward"):
+        assert hasattr(m, name)
+
+
+def test_tie_embedding_hands_over_the_decoder_side_modules(emu):
+    """encoder.tie_embedding(decoder.hmpn) (ggpm/encoder.py:92-94): the encoder adopts the incremental encoder's E_c /
+    E_i modules and one-hot tables, so both sides train the same embedding"""
+    import ggpm_b200
+    from ggpm_b200 import encoder as genc
+    args = (FakePairVocab(30, 40), IdAtomVocab(), "LSTM", 16, 16, 2, 3, 0.0)
+    hmpn = genc.IncHierMPNEncoder(*args)
+    enc = ggpm_b200.HierMPNEncoder(*args)
+    enc.tie_embedding(hmpn)
+    assert enc.E_c is hmpn.E_c and enc.E_i is hmpn.E_i and enc.E_a is hmpn.E_a and enc.E_b is hmpn.E_b
+
+
+def test_dropout_in_train_mode_reaches_the_incremental_readout(emu):
+    case, _ = IC.load("inc_motif_lstm")
+    from ggpm_b200 import encoder as genc
+    nm, na = case["vocab"]
+    model = genc.IncEncoder(FakePairVocab(nm, na), IdAtomVocab(), "LSTM", case["hidden"], case["hidden"], case["depthT"], 0, 0.5)
+    model.load_state_dict(mg.inc_state(case), strict=True)
+    _, tree_t, graph_t, sched, init = mg.build_inputs(case)
+    torch.manual_seed(0)
+    a = io.run_decode(model.train(), False, tree_t, graph_t, sched, init.float(), max_steps=2)
+    b = io.run_decode(model.eval(), False, tree_t, graph_t, sched, init.float(), max_steps=2)
+    assert not torch.allclose(a[0], b[0])            # node read-out goes through W_o's Dropout (ggpm/encoder.py:12-16)
+    assert float((a[0] == 0).float().mean()) > 0.2
