@@ -11,6 +11,8 @@ modules by tie_embedding and must keep the reference's RNG behaviour).
 """
 from __future__ import annotations
 
+import weakref
+
 import torch
 import torch.nn as nn
 
@@ -236,16 +238,37 @@ class MotifEncoder(nn.Module):
 # ----------------------------------------------------------------------------------------------------------------
 # incremental encoders driven by the decoder: ggpm/encoder.py:160-249, 344-394
 # ----------------------------------------------------------------------------------------------------------------
+_PADDED_LINEARS = weakref.WeakKeyDictionary()     # nn.Linear -> (key, (weight, bias) zero padded to 32-row multiples)
+
+
+def _padded_linear(lin):
+    """(W [Np, K], b [Np]) of an nn.Linear with the output rows zero padded to Np = multiple of 32, shared between the
+    decoder steps while the parameters are unchanged (same key as rnn._GraphRNN._packed_for_steps).  With N = 250 the
+    unpadded layer keeps its two gradient GEMMs on the CUDA-core engine (N % 4 != 0); padded, all three run on tcgen05
+    and the ≈ 37 uses per batch share one padding node, so the parameter receives one summed gradient."""
+    import torch.nn.functional as F_
+    w, b = lin.weight, lin.bias
+    key = (torch.is_grad_enabled(), w.data_ptr(), w._version, w.requires_grad, w.device,
+           None if b is None else (b.data_ptr(), b._version, b.requires_grad))
+    cached = _PADDED_LINEARS.get(lin)
+    if cached is None or cached[0] != key:
+        pad = Fn.round_up(w.shape[0], 32) - w.shape[0]
+        cached = (key, (F_.pad(w, (0, 0, 0, pad)), None if b is None else F_.pad(b, (0, pad))))
+        _PADDED_LINEARS[lin] = cached
+    return cached[1]
+
+
 def _linear_seq(seq, parts, widths):
     """nn.Sequential(Linear, ReLU, Dropout) on the concatenation of `parts`.  The incremental steps touch few rows, so
     the reference's own shape is the cheapest: one small torch.cat and ONE GEMM against the unsplit weight (its row
     length F + H is a multiple of 4 in every layer of the path, which keeps it on the tensor-core engine); the output
-    is produced at a 4-float row pitch and returned as its [:, :H] view."""
+    rows are padded to a multiple of 32 columns (zero weights) and returned as the [:, :H] view."""
     lin = seq[0]
     H = lin.out_features
     if sum(widths) % 4 == 0:
         A = torch.cat([p[:, :k] for p, k in zip(parts, widths)], dim=1)
-        out = Fn.linear_act([A], [lin.weight], lin.bias, act=ACT_RELU, out_width=Fn.round_up(H, 4))
+        W, b = _padded_linear(lin)
+        out = Fn.linear_act([A], [W], b, act=ACT_RELU)
     else:
         out = Fn.linear_act_split(parts, lin.weight, widths, lin.bias, act=ACT_RELU)
     return seq[2](out if out.shape[1] == H else out[:, :H])

@@ -211,3 +211,23 @@ def check_packed_weight_reuse(device):
     with torch.no_grad():                                   # no graph in no_grad mode: separate packing
         out = cell.sparse_forward((h0.clone().to(device), c0.clone().to(device)), x1.to(device), s1.to(device), b1.to(device))
     assert not out[0].requires_grad
+
+
+def check_readout_linear_cache_invalidation(device):
+    """the padded read-out weights are shared between steps; an in-place parameter update must be picked up"""
+    case, _ = load("inc_motif_lstm")
+    _, tree_t, graph_t, sched, init = mg.build_inputs(case, device)
+    model = build_model(case, device)
+    init_d = init.float().to(device)
+    with torch.no_grad():
+        first = io.run_decode(model, False, tree_t, graph_t, sched, init_d, device=device, max_steps=3)
+        model.tree_encoder.W_o[0].weight.mul_(1.5)
+        model.tree_encoder.W_o[0].bias.add_(0.25)
+        second = io.run_decode(model, False, tree_t, graph_t, sched, init_d, device=device, max_steps=3)
+    _, tree_c, graph_c, _, _ = mg.build_inputs(case)
+    sd = {k: v.detach().cpu().double() for k, v in model.state_dict().items()}
+    want = io.run_decode(io.IncMotifOracle(sd, case["rnn"], case["depthT"]), False, tree_c, graph_c, sched, init, max_steps=3)
+    assert rel(first[0], want[0]) > 1e-3
+    for a, b in zip(second, want):
+        if b.numel():
+            assert rel(a, b) <= TOL_OUT, rel(a, b)

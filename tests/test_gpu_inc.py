@@ -96,3 +96,7 @@ def test_row_kernels_against_torch(M, K, width, pad_to):
     want[sub.long()] = rows[:, :width]
     assert torch.equal(out, want)
     assert float(Fn.rows_scatter_(table.clone(), sub, None)[sub.long()].abs().sum()) == 0.0
+
+
+def test_readout_weights_are_repadded_after_a_parameter_update():
+    IC.check_readout_linear_cache_invalidation(DEV)

@@ -167,3 +167,7 @@ def test_dropout_in_train_mode_reaches_the_incremental_readout(emu):
     b = io.run_decode(model.eval(), False, tree_t, graph_t, sched, init.float(), max_steps=2)
     assert not torch.allclose(a[0], b[0])            # node read-out goes through W_o's Dropout (ggpm/encoder.py:12-16)
     assert float((a[0] == 0).float().mean()) > 0.2
+
+
+def test_readout_weights_are_repadded_after_a_parameter_update(emu):
+    IC.check_readout_linear_cache_invalidation("cpu")
