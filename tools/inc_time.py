@@ -97,6 +97,19 @@ def main():
     names = ["gather", "gemm_tc", "gemm_simt", "gemm_wgrad", "cell_fwd", "cell_bwd", "misc"]
     out["kernel_ms"] = {n: round(ms_c[i], 3) for i, n in enumerate(names) if cnt[i]}
     out["kernel_launches"] = {n: int(cnt[i]) for i, n in enumerate(names) if cnt[i]}
+    # HBM-side class of this path (row gather / scatter / scatter-add): algorithmic bytes as counted by the library
+    # (rows_gather (K + 1) M W 4, rows_scatter 2 M W 4, rows_scatter_add 3 M K W 4) over its summed launch time
+    peak = 6539.9
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        pass
+    if cnt[0]:
+        ach = work[0] / (ms_c[0] * 1e-3) / 1e9
+        out["roofline"] = dict(kernel="rows_gather / rows_scatter / rows_scatter_add", bound="hbm", achieved=round(ach, 1),
+                               peak=peak, unit="GB/s", frac=round(ach / peak, 4), traffic=None,
+                               avg_launch_us=round(ms_c[0] * 1e3 / cnt[0], 2),
+                               note="launches of a few microseconds on tables that fit the L2: latency bound, not HBM bound")
 
     if args.cpu_batch > 0:
         from oracle import inc_oracle as io, make_golden_inc as mg
