@@ -420,34 +420,47 @@ def run_ours(args, workload):
     # encoded, and the loss of step i goes to pinned host memory asynchronously and is read once step i+1 has been
     # enqueued.  Every step still moves its own inputs H2D and its own result D2H inside the timed region.
     n_e2e = min(args.warmup, 3) + args.steps
-    loader = ingest.DeviceLoader((packed[i % n_batches] for i in range(n_e2e)), dev, depth=2)
-    loss_host = torch.empty(n_e2e, dtype=torch.float32).pin_memory()
-    loss_ev = [torch.cuda.Event() for _ in range(n_e2e)]
-    loss_seen = []
 
-    def e2e_step(i):
-        tree, graph = next(loader)
-        model.zero_grad(set_to_none=True)
-        loss = forward_loss(tree, graph)
-        loss.backward()
-        if world > 1:
-            bucket.all_reduce_mean()
-        loss_host[i].copy_(loss.detach(), non_blocking=True)
-        loss_ev[i].record()
-        if i > 0:
-            loss_ev[i - 1].synchronize()
-            loss_seen.append(float(loss_host[i - 1]))
-    e2e_ms = timed(e2e_step, min(args.warmup, 3), args.steps)
-    loss_ev[n_e2e - 1].synchronize()
-    loss_seen.append(float(loss_host[n_e2e - 1]))
-    assert len(loss_seen) == n_e2e and all(np.isfinite(loss_seen))
+    def pipelined_pass():
+        loader = ingest.DeviceLoader((packed[i % n_batches] for i in range(n_e2e)), dev, depth=2)
+        loss_host = torch.empty(n_e2e, dtype=torch.float32).pin_memory()
+        loss_ev = [torch.cuda.Event() for _ in range(n_e2e)]
+        loss_seen = []
+
+        def e2e_step(i):
+            tree, graph = next(loader)
+            model.zero_grad(set_to_none=True)
+            loss = forward_loss(tree, graph)
+            loss.backward()
+            if world > 1:
+                bucket.all_reduce_mean()
+            loss_host[i].copy_(loss.detach(), non_blocking=True)
+            loss_ev[i].record()
+            if i > 0:
+                loss_ev[i - 1].synchronize()
+                loss_seen.append(float(loss_host[i - 1]))
+        ms_ = timed(e2e_step, min(args.warmup, 3), args.steps)
+        loss_ev[n_e2e - 1].synchronize()
+        loss_seen.append(float(loss_host[n_e2e - 1]))
+        assert len(loss_seen) == n_e2e and all(np.isfinite(loss_seen))
+        return ms_
+
+    # Each end-to-end leg is timed twice (W + K steps each) and the faster pass is reported, both are printed: on some
+    # boxes of this pool a single host stall of 50-100 ms (measured: one pass at 21.8 ms/step between passes at
+    # 12.9 ms/step, same build) lands inside a 10-step region.
+    def best_of_two(run):
+        a = run()
+        b = run()
+        return min(a, b), [a / args.steps, b / args.steps]
+
+    e2e_ms, e2e_passes = best_of_two(pipelined_pass)
     e2e_value = mols_per_step * args.steps / (e2e_ms / 1e3)
 
     # the same without any pipelining: copy, encode, loss.item() strictly one after the other
     def e2e_sync_step(i):
         tree, graph = packed[i % n_batches].to_device(dev)
         step(tree, graph, read_loss=True)
-    e2e_sync_ms = timed(e2e_sync_step, min(args.warmup, 3), args.steps)
+    e2e_sync_ms, e2e_sync_passes = best_of_two(lambda: timed(e2e_sync_step, min(args.warmup, 3), args.steps))
     e2e_sync_value = mols_per_step * args.steps / (e2e_sync_ms / 1e3)
 
     def pin(arrs):
@@ -460,7 +473,7 @@ def run_ours(args, workload):
         tree = [a.to(dev, non_blocking=True).long() for a in t[:-1]] + [t[-1]]
         graph = [a.to(dev, non_blocking=True).long() for a in g[:-1]] + [g[-1]]
         step(tree, graph, read_loss=True)
-    e2e_mc_ms = timed(e2e_mc_step, min(args.warmup, 3), args.steps)
+    e2e_mc_ms, e2e_mc_passes = best_of_two(lambda: timed(e2e_mc_step, min(args.warmup, 3), args.steps))
     e2e_mc_value = mols_per_step * args.steps / (e2e_mc_ms / 1e3)
 
     # ---- per-kernel-class timing for the roofline (separate instrumented pass, rank 0) --------------
@@ -542,15 +555,17 @@ def run_ours(args, workload):
                              "activations (>> 126 MB L2) between forward and backward" % n_batches,
                        "shape_per_batch": stats},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
-                    "ms_per_step": e2e_ms / args.steps,
+                    "ms_per_step": e2e_ms / args.steps, "passes_ms_per_step": e2e_passes,
                     "api": "ingest.DeviceLoader (one pinned int32 buffer per batch, packed ahead of time, H2D of batch "
                            "i+1 on a side stream) -> HierMPNEncoder.forward -> backward -> async loss read-back, "
                            "read one step later"},
             "e2e_unpipelined": {"value": e2e_sync_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                                 "d2h_bytes_per_step": 4, "ms_per_step": e2e_sync_ms / args.steps,
+                                "passes_ms_per_step": e2e_sync_passes,
                                 "api": "PackedBatch.to_device -> forward -> backward -> loss.item(), no overlap"},
             "e2e_make_cuda": {"value": e2e_mc_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_mc),
                               "d2h_bytes_per_step": 4, "ms_per_step": e2e_mc_ms / args.steps,
+                              "passes_ms_per_step": e2e_mc_passes,
                               "api": "reference flow: per-tensor pinned copy + .long() (make_cuda), index structures "
                                      "built on the device"},
             "gpu_launches": int(launches),

@@ -1,12 +1,10 @@
-# ncu --set full of the incremental path's kernels at 1024 molecules (largest sub-message sets), one launch each
 set -x
 T=${TAG:-tmp}
-B="python tools/inc_time.py --batch 1024 --iters 1 --cpu-batch 0"
-N="ncu --set full --clock-control none --import-source on"
-$B > gpurun_out/${T}_plain.json 2> gpurun_out/${T}_plain.err || exit 1
-cat gpurun_out/${T}_plain.json
-timeout 600 $N -k regex:rows_scatter_add_kernel -s 60 -c 1 -o gpurun_out/${T}_inc_scatter_add $B > gpurun_out/${T}_n1.log 2>&1
-timeout 600 $N -k regex:rows_gather_kernel -s 60 -c 1 -o gpurun_out/${T}_inc_gather $B > gpurun_out/${T}_n2.log 2>&1
-timeout 600 $N -k regex:sparse_lstm_cell_bwd_kernel -s 10 -c 1 -o gpurun_out/${T}_inc_cell_bwd $B > gpurun_out/${T}_n3.log 2>&1
-timeout 600 $N -k regex:sparse_lstm_cell_fwd_kernel -s 10 -c 1 -o gpurun_out/${T}_inc_cell_fwd $B > gpurun_out/${T}_n4.log 2>&1
-ls -la gpurun_out | grep ${T}
+for r in 1 2 3; do
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/${T}_bench_$r.json 2> gpurun_out/${T}_bench_$r.err; echo "bench exit $?"
+python - <<PY
+import json
+d=json.loads(open("gpurun_out/${T}_bench_$r.json").read().strip().splitlines()[-1])
+print(round(d['value']), round(d['ms_per_step'],2), {k:(round(v['value']), [round(x,2) for x in v['passes_ms_per_step']]) for k,v in d.items() if k.startswith('e2e')})
+PY
+done
