@@ -1227,6 +1227,8 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
     // state gradient of a small layer (N = Hp = 256, fewer than two waves of 128 x 256 tiles): 128-wide tiles double the
     // tile count and leave TMEM room for a second accumulator set (measured -0.2 ms per cfg2 step, neutral at cfg3)
     if (mode == F16_A_TMA && g.tile_n == 0 && g.N == 256 && ceil_div(g.M, BM) < 2 * sm_count()) wide = false;
+    // (weight gradients keep 256-wide tiles: 128-wide ones measured -4 % (cfg2) / -12 % (cfg1) on that class, -0.5 % on the
+    // step, but the doubled number of row-range partial sums moved the K = 19001 kernel test from 1.9e-6 to 2.7e-6)
     if (g.tile_n == 128) wide = false;
     if (g.tile_n == 256) wide = true;
     {   // experiment knob: GGPM_F16_BN_FWD / _DGRAD / _WGRAD = 128 | 256

@@ -1,10 +1,6 @@
-set -x
 T=${TAG:-tmp}
-for r in 1 2 3; do
-timeout 600 python bench.py --no-cpu-baseline > gpurun_out/${T}_bench_$r.json 2> gpurun_out/${T}_bench_$r.err; echo "bench exit $?"
-python - <<PY
-import json
-d=json.loads(open("gpurun_out/${T}_bench_$r.json").read().strip().splitlines()[-1])
-print(round(d['value']), round(d['ms_per_step'],2), {k:(round(v['value']), [round(x,2) for x in v['passes_ms_per_step']]) for k,v in d.items() if k.startswith('e2e')})
-PY
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest exit $?"; tail -2 gpurun_out/${T}_pytest.log
+for W in cfg2 cfg1 cfg3s; do
+  timeout 600 python bench.py --workload $W --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/${T}_${W}.json 2> gpurun_out/${T}_${W}.err
+  python tools/bench_summary.py gpurun_out/${T}_${W}.json | head -2
 done
