@@ -48,12 +48,13 @@ def _edges_in_nx_order(n_nodes: int, edges: Sequence[Tuple[int, int, object]]):
 
 
 def random_molecule(rng: random.Random, n_motif_vocab=721, n_attach_vocab=6215, n_atom_vocab=38,
-                    mean_motifs=12.0, sd_motifs=3.0) -> SynthMol:
+                    mean_motifs=12.0, sd_motifs=3.0, min_motifs=2) -> SynthMol:
     """Degree-bounded random molecule: rings (5/6/6 atoms, aromatic bonds) and 2-atom bonds glued
-    by sharing one atom, exactly one tree edge per glue."""
+    by sharing one atom, exactly one tree edge per glue.  ``min_motifs=1`` admits
+    single-motif molecules, whose motif tree has no edge at all (a lone ring in the real data)."""
     mol = SynthMol()
     degree: List[int] = []
-    n_motifs = max(2, int(round(rng.gauss(mean_motifs, sd_motifs))))
+    n_motifs = max(min_motifs, int(round(rng.gauss(mean_motifs, sd_motifs))))
 
     def new_atom():
         mol.atom_labels.append(rng.randrange(n_atom_vocab))

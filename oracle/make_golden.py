@@ -54,6 +54,16 @@ CASES = [
     # BASELINE config #1 stand-in: configs/configs.json hyper-parameters, 20 synthetic molecules
     dict(name="hier_lstm_cfg1", kind="hier", rnn="LSTM", hidden=250, depthT=20, depthG=20, batch=20,
          data_seed=1, weight_seed=0, vocab=(721, 6215), mean_motifs=12.0, full=False),
+    # edge cases of the motif tree: single-motif molecules (no tree edge) mixed into a batch, and batches
+    # whose tree message table is the padding row alone (Et = 0, bgraph / agraph of width 1)
+    dict(name="hier_lstm_lone_motifs", kind="hier", rnn="LSTM", hidden=32, depthT=4, depthG=5, batch=7,
+         data_seed=17, weight_seed=107, vocab=(40, 60), mean_motifs=1.6, sd_motifs=0.8, min_motifs=1, full=True),
+    dict(name="hier_lstm_no_tree_edges", kind="hier", rnn="LSTM", hidden=32, depthT=4, depthG=5, batch=4,
+         data_seed=18, weight_seed=108, vocab=(40, 60), mean_motifs=1.0, sd_motifs=0.0, min_motifs=1, full=True),
+    dict(name="hier_gru_no_tree_edges", kind="hier", rnn="GRU", hidden=32, depthT=4, depthG=5, batch=4,
+         data_seed=19, weight_seed=109, vocab=(40, 60), mean_motifs=1.0, sd_motifs=0.0, min_motifs=1, full=True),
+    dict(name="motif_lstm_no_tree_edges", kind="motif", rnn="LSTM", hidden=24, depthT=6, depthG=0, batch=3,
+         data_seed=20, weight_seed=110, vocab=(40, 60), mean_motifs=1.0, sd_motifs=0.0, min_motifs=1, full=True),
 ]
 GRAD_STRIDE = 97      # big-case gradients are stored as flat[::GRAD_STRIDE] plus their L2 norm
 
@@ -61,7 +71,9 @@ GRAD_STRIDE = 97      # big-case gradients are stored as flat[::GRAD_STRIDE] plu
 def build_inputs(case):
     nm, na = case["vocab"]
     mols = synth.random_batch(case["data_seed"], case["batch"], n_motif_vocab=nm, n_attach_vocab=na,
-                              mean_motifs=case["mean_motifs"], sd_motifs=case["mean_motifs"] / 4.0)
+                              mean_motifs=case["mean_motifs"],
+                              sd_motifs=case.get("sd_motifs", case["mean_motifs"] / 4.0),
+                              min_motifs=case.get("min_motifs", 2))
     return mols, synth.tensorize(mols)
 
 
@@ -190,8 +202,10 @@ def run_case(ref, case):
 def main():
     ref = load_reference()
     torch.set_num_threads(max(1, os.cpu_count() or 1))
+    only = set(sys.argv[1:])          # optional: names of the cases to (re)generate
     for case in CASES:
-        run_case(ref, case)
+        if not only or case["name"] in only:
+            run_case(ref, case)
 
 
 if __name__ == "__main__":

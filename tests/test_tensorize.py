@@ -12,7 +12,9 @@ from oracle.ref_loader import FakePairVocab, IdAtomVocab, load_reference, refere
 def _regen(meta):
     nm, na = meta["vocab"]
     mols = synth.random_batch(meta["data_seed"], meta["batch"], n_motif_vocab=nm, n_attach_vocab=na,
-                              mean_motifs=meta["mean_motifs"], sd_motifs=meta["mean_motifs"] / 4.0)
+                              mean_motifs=meta["mean_motifs"],
+                              sd_motifs=meta.get("sd_motifs", meta["mean_motifs"] / 4.0),
+                              min_motifs=meta.get("min_motifs", 2))
     return mols, synth.tensorize(mols)
 
 
