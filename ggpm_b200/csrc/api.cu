@@ -54,6 +54,34 @@ bool pdl_enabled() {
     return on != 0;
 }
 
+// ---- side stream of the backward depth loop ------------------------------------------------------------
+// The weight-gradient GEMM of a backward round has no consumer until the loop ends, while everything else of the
+// round sits on the critical path (state-gradient GEMM -> cell kernel of the next round).  It is therefore issued on
+// a second stream, forked and joined with events, so that this tensor-bound GEMM runs under the HBM-bound cell
+// kernel of the next round.  One stream + two events per device, created on first use (GGPM_WGRAD_OVERLAP=0: off).
+struct SideStream { cudaStream_t s; cudaEvent_t fork, join; bool ok; };
+static SideStream* side_stream() {
+    static SideStream side[64];
+    static std::atomic<int> state[64];          // 0 = untouched, 1 = being created, 2 = ready
+    static int enabled = -1;
+    if (enabled < 0) {
+        const char* e = getenv("GGPM_WGRAD_OVERLAP");
+        enabled = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    int dev = 0;
+    if (!enabled || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    int expect = 0;
+    if (state[dev].compare_exchange_strong(expect, 1)) {
+        SideStream& q = side[dev];
+        q.ok = cudaStreamCreateWithFlags(&q.s, cudaStreamNonBlocking) == cudaSuccess &&
+               cudaEventCreateWithFlags(&q.fork, cudaEventDisableTiming) == cudaSuccess &&
+               cudaEventCreateWithFlags(&q.join, cudaEventDisableTiming) == cudaSuccess;
+        state[dev].store(2);
+    }
+    while (state[dev].load() != 2) {}
+    return side[dev].ok ? &side[dev] : nullptr;
+}
+
 // ---- per-launch event timing -------------------------------------------------------------------------
 constexpr int kProfMax = 1 << 16;
 static bool g_prof_on = false;
@@ -420,6 +448,8 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     GGPM_REQUIRE(zmode || !h_rotate, "lstm_bwd: the forward kept only a rotating hist_h, which needs the fp16-plane path");
     char* z_hi = (char*)z_planes;
     char* z_lo = z_hi + (size_t)8 * row;                  // 4 * row halves
+    SideStream* side = zmode ? side_stream() : nullptr;
+    bool side_busy = false;                               // a weight-gradient GEMM may still be reading the Z planes
     for (int t = depth; t >= 1; --t) {
         const float* c_cur = hist_c + (size_t)(t - 1) * row;
         const float* gp = hist_gp + (size_t)(t - 1) * 4 * row;
@@ -441,6 +471,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
             // Z = [gather^T(dA[:, :3Hp]) | dP] as scaled fp16 planes; then dH^{t-1} = Z [Ug; Uf] and
             // [dUg; dUf] += Z^T h^{t-1}: two plain GEMMs whose operands all arrive by TMA
             float* z_scale = fw.scal + 4;
+            if (side_busy) GGPM_CUDA(cudaStreamWaitEvent(st, side->join, 0));     // Z planes / scale are rewritten next
             GGPM_TRY(launch_lstm_zgather(E1, Hp, bt_ptr, bt_row, dA, dP, amax_t, reinterpret_cast<const int*>(fw.scal + 2),
                                          z_hi, z_lo, z_scale, st));
             GemmArgs w;
@@ -448,12 +479,22 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
             w.Bh_hi = (const char*)hist_h16 + (size_t)(t - 2) * 4 * row; w.Bh_lo = (const char*)w.Bh_hi + 2 * row;
             w.sbn = Hp; w.b_scale_const = 8192.f;          // GGPM_H16_SCALE of the forward cell kernel
             w.C = dUg; w.ldc = Hp; w.M = 4 * Hp; w.N = Hp; w.K = E1; w.beta = 1.f;
-            GGPM_TRY(launch_gemm_f16(w, st));
+            if (side == nullptr) GGPM_TRY(launch_gemm_f16(w, st));
             GemmArgs d;
             d.Ah_hi = z_hi; d.Ah_lo = z_lo; d.lda_h = 4 * Hp; d.a_scale = z_scale;
             d.Bh_hi = fw.hi; d.Bh_lo = fw.lo; d.sbn = 4 * Hp; d.b_scale = fw.scal + 1;
             d.C = dH_next; d.ldc = Hp; d.M = E1; d.N = Hp; d.K = 4 * Hp;
-            GGPM_TRY(launch_gemm_f16(d, st));
+            if (side != nullptr) {
+                // critical path first (its CTAs are dispatched ahead of the weight-gradient GEMM's), then the fork
+                GGPM_CUDA(cudaEventRecord(side->fork, st));                        // Z planes of this round complete
+                GGPM_TRY(launch_gemm_f16(d, st));
+                GGPM_CUDA(cudaStreamWaitEvent(side->s, side->fork, 0));
+                GGPM_TRY(launch_gemm_f16(w, side->s));
+                GGPM_CUDA(cudaEventRecord(side->join, side->s));
+                side_busy = true;
+            } else {
+                GGPM_TRY(launch_gemm_f16(d, st));
+            }
         } else if (tc_ok) {
             // weight gradients: dUg += dA[:, :3Hp]^T S^t (S re-gathered inside the B-operand prologue) ;
             // dUf += dP^T h^{t-1}
@@ -504,6 +545,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
         float* tmp = dH; dH = dH_next; dH_next = tmp;
         dC_cur = dC_prev;
     }
+    if (side_busy) GGPM_CUDA(cudaStreamWaitEvent(st, side->join, 0));   // dUg / dUf complete for the caller's stream
     return 0;
 }
 

@@ -1,6 +1,8 @@
 T=${TAG:-tmp}
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest exit $?"; tail -2 gpurun_out/${T}_pytest.log
-for W in cfg2 cfg1 cfg3s; do
-  timeout 600 python bench.py --workload $W --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/${T}_${W}.json 2> gpurun_out/${T}_${W}.err
-  python tools/bench_summary.py gpurun_out/${T}_${W}.json | head -2
+for OV in 0 1; do
+for W in cfg2 cfg3s; do
+  GGPM_WGRAD_OVERLAP=$OV timeout 600 python bench.py --workload $W --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/${T}_${W}_ov${OV}.json 2> gpurun_out/${T}_${W}_ov${OV}.err
+  echo "overlap=$OV"; python tools/bench_summary.py gpurun_out/${T}_${W}_ov${OV}.json | head -2
+done
 done
