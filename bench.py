@@ -2,7 +2,7 @@
 """Benchmark of the hierarchical message-passing encoder hot path (BASELINE.json metric:
 "HierMPN encoder molecules/sec (fwd+bwd)").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg3|cfg1]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg1|cfg2|cfg3s|cfg3|cfg4|cfg5]
 
 One step = HierMPNEncoder forward + backward (loss = hroot.sum(), the only output the VAEs consume,
 ggpm/property_vae.py:50) over one synthetic batch.  Workload at N=1 is BASELINE config #2: the encoder of
@@ -47,6 +47,10 @@ WORKLOADS = {
                   desc="double-hidden encoder (hidden 500), batch 1024 synthetic graphs (profiling-sized cfg3)"),
     "cfg3": dict(hidden=500, depthT=20, depthG=20, dropout=0.0, batch=4096,
                  desc="double-hidden encoder (hidden 500), batch 4096 synthetic graphs"),
+    "cfg4": dict(hidden=250, depthT=20, depthG=20, dropout=0.0, batch=4096, pool=16,
+                 desc="throughput sweep: synthetic molecular graphs (~30 atoms, ~12 motifs, depth 20) streamed in batches "
+                      "of 4096 per GPU from a rotating pool of 16 distinct batches (65 536 molecules per GPU); "
+                      "--steps 245 at 1 GPU (31 at 8) covers 1M molecules"),
     "cfg5": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256, encoder="motif", latent=24,
                  desc="PropertyVAE encoder side of one pre-training step: MotifEncoder + R_mean/R_var rsample/KL "
                       "(ggpm/property_vae.py:79-99), batch 256 per GPU, decoder excluded"),
@@ -308,6 +312,7 @@ def run_ours(args, workload):
     n_batches = min(4, max(1, args.warmup))      # every batch shape is seen once before the timed region (allocator warm)
     if workload["batch"] >= 4096:
         n_batches = min(n_batches, 2)
+    n_batches = workload.get("pool", n_batches)
     batches = make_batches(workload, n_batches, seed=rank + 1)
     # resident inputs of the device-timed arm: the batch in the ingest format (index tensors + the CSR / reverse CSR the
     # host prepared), already in HBM; --resident make_cuda keeps the reference's int64 tensors instead (index structures

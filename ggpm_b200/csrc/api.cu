@@ -58,7 +58,8 @@ bool pdl_enabled() {
 // The weight-gradient GEMM of a backward round has no consumer until the loop ends, while everything else of the
 // round sits on the critical path (state-gradient GEMM -> cell kernel of the next round).  It is therefore issued on
 // a second stream, forked and joined with events, so that this tensor-bound GEMM runs under the HBM-bound cell
-// kernel of the next round.  One stream + two events per device, created on first use (GGPM_WGRAD_OVERLAP=0: off).
+// kernel of the next round.  One stream + two events per device, created on first use.  Opt-in (GGPM_WGRAD_OVERLAP=1):
+// the GEMM CTAs own most of an SM's registers, so the measured gain decides the default.
 struct SideStream { cudaStream_t s; cudaEvent_t fork, join; bool ok; };
 static SideStream* side_stream() {
     static SideStream side[64];
@@ -66,7 +67,7 @@ static SideStream* side_stream() {
     static int enabled = -1;
     if (enabled < 0) {
         const char* e = getenv("GGPM_WGRAD_OVERLAP");
-        enabled = (e != nullptr && e[0] == '0') ? 0 : 1;
+        enabled = (e != nullptr && e[0] == '1') ? 1 : 0;
     }
     int dev = 0;
     if (!enabled || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;

@@ -89,12 +89,12 @@ def test_plane_fed_forward_of_large_layers_matches_golden():
     assert " passed" in r.stdout
 
 
-def test_backward_without_the_side_stream_matches_golden():
-    """The weight-gradient GEMM of every backward LSTM round is issued on a side stream (forked / joined with events)
-    so that it runs under the next round's cell kernel; GGPM_WGRAD_OVERLAP=0 keeps it on the caller's stream.  The
-    switch is read once per process, so the golden checks are repeated in a child process with the overlap off."""
+def test_backward_with_the_side_stream_matches_golden():
+    """GGPM_WGRAD_OVERLAP=1 issues the weight-gradient GEMM of every backward LSTM round on a side stream (forked /
+    joined with events) so that it runs under the next round's cell kernel.  The switch is read once per process, so
+    the golden checks are repeated in a child process with the overlap on."""
     import subprocess
-    env = dict(os.environ, GGPM_WGRAD_OVERLAP="0")
+    env = dict(os.environ, GGPM_WGRAD_OVERLAP="1")
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider",
                         "-k", "cfg1_matches or (forward_backward_matches and auto and lstm)"], env=env, capture_output=True,
                        text=True, timeout=900)
