@@ -6,3 +6,5 @@ for W in cfg2 cfg3s; do
   echo "overlap=$OV"; python tools/bench_summary.py gpurun_out/${T}_${W}_ov${OV}.json | head -2
 done
 done
+timeout 900 python bench.py --workload cfg4 --steps 32 --warmup 4 --no-cpu-baseline > gpurun_out/${T}_cfg4.json 2> gpurun_out/${T}_cfg4.err; echo "cfg4 exit $?"; tail -2 gpurun_out/${T}_cfg4.err
+python tools/bench_summary.py gpurun_out/${T}_cfg4.json | head -2
