@@ -490,6 +490,8 @@ def run_ours(args, workload):
             tj = json.load(f)
         if tj.get("workload") == args.workload:
             traffic = tj.get("per_launch_bytes", {})
+        else:   # captures of other workloads: {"others": {"cfg4": {"per_launch_bytes": {...}, "source": "..."}}}
+            traffic = tj.get("others", {}).get(args.workload, {}).get("per_launch_bytes", {})
     except Exception:
         traffic = {}
     if rank == 0:
