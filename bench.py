@@ -5,16 +5,19 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg1|cfg2|cfg3s|cfg3|cfg4|cfg5]
 
 One step = HierMPNEncoder forward + backward (loss = hroot.sum(), the only output the VAEs consume,
-ggpm/property_vae.py:50) over one synthetic batch.  Workload at N=1 is BASELINE config #2: the encoder of
-one vae_train.py pre-training step with configs/pretrained_w_tie_embedding_configs.json (LSTM, hidden =
-embed = 250, depthT = depthG = 20, dropout 0.1, train mode), batch 256 per GPU.  For N > 1 every rank
-encodes its own batches (weak scaling, no communication on the encoder path) and the encoder-weight
-gradients are all-reduced with NCCL as one flat bucket inside the step.
+ggpm/property_vae.py:50) over one synthetic batch.  The default workload is BASELINE config #4, the one the
+metric is quoted on: the synthetic throughput sweep (molecular graphs of ~30 atoms / ~12 motifs, depth 20/20,
+LSTM, hidden = embed = 250) streamed in batches of 4096 molecules per GPU; `--workload cfg2` is the encoder of
+one vae_train.py pre-training step (pretrained_w_tie_embedding_configs.json, dropout 0.1, batch 256), the other
+names are the remaining BASELINE configs.  For N > 1 every rank encodes its own batches (weak scaling, no
+communication on the encoder path) and the encoder-weight gradients are all-reduced with NCCL inside the step.
 
 Prints ONE JSON line (rank 0).  `value` is timed with inputs resident in HBM; `e2e` goes through the public
 module API from pinned HOST index tensors (H2D copy + loss read-back inside the timed region).
-`--impl reference` times the CPU oracle (oracle/encoder_oracle.py: the reference's padded PyTorch
-formulation; the reference itself is Python and cannot travel to the GPU box) on the host cores.
+`--impl reference` times the reference's OWN HierMPNEncoder / MotifEncoder (unmodified ggpm/encoder.py, staged
+under oracle/_ref/ by oracle/make_ref.py, rdkit stubbed) on the host cores with the same hyper-parameters, dropout
+setting, mode and loss; `cpu_baseline.kind` is "reference" then, "port" only if the staged copy is missing (the
+oracle restatement is timed instead).
 """
 from __future__ import annotations
 
@@ -49,8 +52,9 @@ WORKLOADS = {
                  desc="double-hidden encoder (hidden 500), batch 4096 synthetic graphs"),
     "cfg4": dict(hidden=250, depthT=20, depthG=20, dropout=0.0, batch=4096, pool=16,
                  desc="throughput sweep: synthetic molecular graphs (~30 atoms, ~12 motifs, depth 20) streamed in batches "
-                      "of 4096 per GPU from a rotating pool of 16 distinct batches (65 536 molecules per GPU); "
-                      "--steps 245 at 1 GPU (31 at 8) covers 1M molecules"),
+                      "of 4096 per GPU; the stream REPLAYS a rotating pool of 16 distinct batches per rank (65 536 "
+                      "distinct molecules per GPU, topologies repeat every 16 steps); --steps 245 at 1 GPU (31 at 8) "
+                      "covers 1M molecules"),
     "cfg5": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256, encoder="motif", latent=24,
                  desc="PropertyVAE encoder side of one pre-training step: MotifEncoder + R_mean/R_var rsample/KL "
                       "(ggpm/property_vae.py:79-99), batch 256 per GPU, decoder excluded"),
@@ -207,23 +211,56 @@ def algorithmic_flops(stats, H, depthT, depthG, B, motif_only=False):
 
 
 # --------------------------------------------------------------------------------------------------
-# reference arm / cpu baseline: the oracle (reference's padded torch formulation) on the host cores
+# reference arm / cpu baseline: the reference's own encoder classes on the host cores
 # --------------------------------------------------------------------------------------------------
-def cpu_oracle_rate(workload, sample_mols, warmup, steps):
+def _reference_step_fn(workload, sample_mols):
+    """-> (step(), kind): one forward + backward of the reference's own HierMPNEncoder / MotifEncoder (kind
+    "reference"; unmodified ggpm/encoder.py from oracle/_ref or /root/reference) on a `sample_mols`-molecule batch of
+    the workload's generator, same hyper-parameters / dropout / train mode / loss as our arm; the oracle restatement
+    (kind "port") only when no copy of the reference is reachable."""
     from ggpm_b200 import synth
-    from oracle import encoder_oracle as eo
-    torch.set_num_threads(os.cpu_count() or 1)
+    from oracle import ref_loader
     H = workload["hidden"]
     mols = synth.random_batch(424242, sample_mols)
     tree, graph = synth.tensorize(mols)
     as_long = lambda ts: [torch.from_numpy(np.asarray(t)).long() if not isinstance(t, list) else t for t in ts]
     tree, graph = as_long(tree), as_long(graph)
     motif = workload.get("encoder") == "motif"
+    L = workload.get("latent", 0)
+    if ref_loader.reference_available():
+        ref = ref_loader.load_reference()
+        ref.nnutils.device = torch.device("cpu")          # the reference pins cuda:0 when it sees a GPU (nnutils.py:9-10)
+        torch.manual_seed(0)
+        cls = ref.encoder.MotifEncoder if motif else ref.encoder.HierMPNEncoder
+        model = cls(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H, workload["depthT"],
+                    workload["depthG"], workload["dropout"])
+        if motif:
+            model.R_mean, model.R_var = torch.nn.Linear(H, L), torch.nn.Linear(H, L)
+        for p in model.parameters():                       # vae_train.py:49-53
+            if p.dim() == 1:
+                torch.nn.init.constant_(p, 0)
+            else:
+                torch.nn.init.xavier_normal_(p)
+        model.train()
+
+        def step():
+            model.zero_grad(set_to_none=True)
+            if motif:      # PropertyVAE.forward's encoder side (ggpm/property_vae.py:95-99): encoder + rsample / KL
+                root = model(tree)[0]
+                z_mean = model.R_mean(root)
+                z_log_var = -torch.abs(model.R_var(root))
+                kl = -0.5 * torch.sum(1.0 + z_log_var - z_mean * z_mean - torch.exp(z_log_var)) / root.size(0)
+                z = z_mean + torch.exp(z_log_var / 2) * torch.randn_like(z_mean)
+                (z.sum() + kl).backward()
+            else:
+                model(tree, graph)[0].sum().backward()
+        return step, "reference"
+
+    from oracle import encoder_oracle as eo
     sd = {k: v.requires_grad_(True)
           for k, v in eo.random_state("motif" if motif else "hier", "LSTM", H, H, 0, bias_std=0.0).items()}
     if motif:
         from oracle import latent_oracle as lo
-        L = workload["latent"]
         lat = [torch.randn(L, H) / H ** 0.5, torch.zeros(L), torch.randn(L, H) / H ** 0.5, torch.zeros(L)]
         lat = [t.requires_grad_(True) for t in lat]
 
@@ -232,26 +269,54 @@ def cpu_oracle_rate(workload, sample_mols, warmup, steps):
             v.grad = None
         if motif:
             root = eo.motif_encoder(sd, "LSTM", workload["depthT"], tree)[0]
-            z, kl = lo.rsample(root, *lat, torch.randn(root.shape[0], workload["latent"]), True)
+            z, kl = lo.rsample(root, *lat, torch.randn(root.shape[0], L), True)
             (z.sum() + kl).backward()
         else:
             eo.hier_encoder(sd, "LSTM", workload["depthT"], workload["depthG"], tree, graph)[0].sum().backward()
+    return step, "port"
 
+
+def cpu_reference_rate(workload, warmup, steps, budget_s):
+    """times `steps` reference steps after `warmup`; the per-step sample (molecules) is the largest of
+    32, 64, 128, 256 (capped by the workload's batch) whose (warmup + steps) steps fit `budget_s` on this box,
+    judged from one probe step on 32 molecules.  -> (molecules/s, s/step, sample, kind)"""
+    torch.set_num_threads(os.cpu_count() or 1)
+    probe, kind = _reference_step_fn(workload, min(32, workload["batch"]))
+    probe()                                   # first call pays for thread-pool start-up
+    t0 = time.perf_counter()
+    probe()
+    per_mol = (time.perf_counter() - t0) / min(32, workload["batch"])
+    sample = min(32, workload["batch"])
+    for cand in (64, 128, 256):
+        if cand <= workload["batch"] and per_mol * cand * (warmup + steps) <= budget_s:
+            sample = cand
+    step, kind = _reference_step_fn(workload, sample)
     for _ in range(warmup):
         step()
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
     dt = (time.perf_counter() - t0) / max(steps, 1)
-    return sample_mols / dt, dt
+    return sample / dt, dt, sample, kind
+
+
+def _sample_note(workload, sample, kind, dt, cores):
+    from oracle import ref_loader
+    where = "oracle/_ref staged copy" if ref_loader.reference_is_staged_copy() else ref_loader.REFERENCE_ROOT
+    what = ("the reference's own %s (unmodified ggpm/encoder.py, " + where + ")" if kind == "reference" else
+            "the oracle restatement of %s (reference's padded PyTorch formulation)") % (
+                "MotifEncoder + rsample/KL" if workload.get("encoder") == "motif" else "HierMPNEncoder")
+    scale = "" if sample == workload["batch"] else (
+        "; the workload's batch is %d, CPU time is linear in molecules, so molecules/s carries over" % workload["batch"])
+    return ("%d-molecule batch of the same generator per step, fwd+bwd %.2f s/step, %s, fp32, train mode, dropout %.1f, "
+            "%d torch threads%s" % (sample, dt, what, workload["dropout"], cores, scale))
 
 
 def run_reference(args, workload):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample = min(workload["batch"], 32)
-    rate, dt = cpu_oracle_rate(workload, sample, args.warmup, args.steps)
+    rate, dt, sample, kind = cpu_reference_rate(workload, args.warmup, args.steps, budget_s=150.0)
     cores = os.cpu_count() or 1
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
@@ -259,11 +324,9 @@ def run_reference(args, workload):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload + ": " + workload["desc"], "hidden": workload["hidden"],
                    "depthT": workload["depthT"], "depthG": workload["depthG"], "rnn_type": "LSTM",
-                   "batch_per_gpu": workload["batch"]},
-        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": "%d-molecule synthetic batch of the same generator per step (CPU time scales "
-                                   "linearly in molecules); oracle = reference's padded PyTorch formulation, fp32, "
-                                   "%d torch threads" % (sample, cores)},
+                   "dropout": workload["dropout"], "batch_per_gpu": workload["batch"], "sample_molecules": sample},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": _sample_note(workload, sample, kind, dt, cores)},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -450,22 +513,21 @@ def run_ours(args, workload):
         assert len(loss_seen) == n_e2e and all(np.isfinite(loss_seen))
         return ms_
 
-    # Each end-to-end leg is timed twice (W + K steps each) and the faster pass is reported, both are printed: on some
-    # boxes of this pool a single host stall of 50-100 ms (measured: one pass at 21.8 ms/step between passes at
-    # 12.9 ms/step, same build) lands inside a 10-step region.
-    def best_of_two(run):
-        a = run()
-        b = run()
-        return min(a, b), [a / args.steps, b / args.steps]
+    # Each end-to-end leg is timed three times (W + K steps each) and the MEDIAN pass is reported, all three are
+    # printed: on some boxes of this pool a single host stall of 50-100 ms (measured: one pass at 21.8 ms/step between
+    # passes at 12.9 ms/step, same build) lands inside a 10-step region.
+    def median_of_three(run):
+        passes = [run() for _ in range(3)]
+        return sorted(passes)[1], [p / args.steps for p in passes]
 
-    e2e_ms, e2e_passes = best_of_two(pipelined_pass)
+    e2e_ms, e2e_passes = median_of_three(pipelined_pass)
     e2e_value = mols_per_step * args.steps / (e2e_ms / 1e3)
 
     # the same without any pipelining: copy, encode, loss.item() strictly one after the other
     def e2e_sync_step(i):
         tree, graph = packed[i % n_batches].to_device(dev)
         step(tree, graph, read_loss=True)
-    e2e_sync_ms, e2e_sync_passes = best_of_two(lambda: timed(e2e_sync_step, min(args.warmup, 3), args.steps))
+    e2e_sync_ms, e2e_sync_passes = median_of_three(lambda: timed(e2e_sync_step, min(args.warmup, 3), args.steps))
     e2e_sync_value = mols_per_step * args.steps / (e2e_sync_ms / 1e3)
 
     def pin(arrs):
@@ -478,7 +540,7 @@ def run_ours(args, workload):
         tree = [a.to(dev, non_blocking=True).long() for a in t[:-1]] + [t[-1]]
         graph = [a.to(dev, non_blocking=True).long() for a in g[:-1]] + [g[-1]]
         step(tree, graph, read_loss=True)
-    e2e_mc_ms, e2e_mc_passes = best_of_two(lambda: timed(e2e_mc_step, min(args.warmup, 3), args.steps))
+    e2e_mc_ms, e2e_mc_passes = median_of_three(lambda: timed(e2e_mc_step, min(args.warmup, 3), args.steps))
     e2e_mc_value = mols_per_step * args.steps / (e2e_mc_ms / 1e3)
 
     # ---- per-kernel-class timing for the roofline (separate instrumented pass, rank 0) --------------
@@ -510,43 +572,62 @@ def run_ours(args, workload):
         kernels = {PROF_CLASSES[c]: {"ms_per_step": ms_c[c] / prof_steps, "launches_per_step": cnt_c[c] // prof_steps,
                                      "share": ms_c[c] / total} for c in range(n) if cnt_c[c]}
         gemm_classes = [c for c in (1, 2, 3) if cnt_c[c]]
-        # HBM-side classes: algorithmic bytes per step from SURVEY 8(d) (nnz-dependent part from the batch)
-        Hp = (H + 31) // 32 * 32
-        by = 0.0
-        layers = ((stats["Ea"], stats["nnz_bA"], workload["depthG"]), (stats["Et"], stats["nnz_bT"], workload["depthT"]),
-                  (stats["Et"], stats["nnz_bT"], workload["depthT"]))
-        for E, nnz, D in (layers[1:2] if motif else layers):
-            by += D * (3.0 * nnz * Hp * 4 + 2.0 * E * Hp * 4 + 4.0 * nnz + 4.0 * E)
+        # HBM-side classes: ALGORITHMIC bytes per step, per class, from SURVEY 8(d) on the unpadded width H (fp32).
+        # Per LSTM round and layer with E messages and nnz true neighbour entries, one row = H * 4 bytes:
+        #   gather class   forward: the neighbour gather of h (nnz rows read) + S written (E rows: the large-layer path
+        #                  forms S with a gather kernel); backward mirrors it over the reverse CSR (nnz + E);
+        #                  plus the node / cluster aggregations (nnz_a + N, nnz_c + Nt rows) each way
+        #   cell_fwd       neighbour rows of c and of the forget projection U_f h (2 nnz read), h', c' written (2 E)
+        #   cell_bwd       the same two neighbour tables re-read for the forget gate (2 nnz), the two scatter targets
+        #                  dC_prev / dP (2 nnz), dH, dC and the saved c_t read (3 E)
+        #   + 4 bytes per index entry (nnz + E) per pass.  Everything else a kernel moves (gate pre-activations, the
+        #   x-projection rows, dX, fp16 planes) is implementation traffic and counts against `frac`.
+        rowb = H * 4.0
+        layers = ((stats["Ea"], stats["nnz_bA"], workload["depthG"], stats["Na"], stats["nnz_aA"]),
+                  (stats["Et"], stats["nnz_bT"], workload["depthT"], stats["Nt"], stats["nnz_aT"]),
+                  (stats["Et"], stats["nnz_bT"], workload["depthT"], stats["Nt"], stats["nnz_aT"]))
+        by_cls = {0: 0.0, 4: 0.0, 5: 0.0}
+        for E, nnz, D, N, nnz_a in (layers[1:2] if motif else layers):
+            idx = 4.0 * (nnz + E)
+            # layers below the library's 32 768-row threshold gather h inside the forward GEMM's operand prologue
+            # (no gather-class launch forward): only the backward mirror is a gather kernel there
+            passes = 2 if (E + 1) >= 32768 else 1
+            by_cls[0] += passes * (D - 1) * ((nnz + E) * rowb + idx) + 2 * ((nnz_a + N) * rowb + 4.0 * (nnz_a + N))
+            by_cls[4] += (D - 1) * ((2.0 * nnz + 2.0 * E) * rowb + idx) + 2.0 * E * rowb
+            by_cls[5] += (D - 1) * ((4.0 * nnz + 3.0 * E) * rowb + idx) + 3.0 * E * rowb
+        if not motif:
+            by_cls[0] += 2 * ((stats["nnz_c"] + stats["Nt"]) * rowb + 4.0 * (stats["nnz_c"] + stats["Nt"]))
+        flop_scale = (H / float((H + 31) // 32 * 32)) ** 2     # the library counts 2 M N K on the padded width Hp
 
         def class_roofline(c):
             name = PROF_CLASSES[c]
             if c in gemm_classes:
-                tf = work_c[c] / (ms_c[c] * 1e-3) / 1e12
+                tf = work_c[c] * flop_scale / (ms_c[c] * 1e-3) / 1e12
                 return {"kernel": name, "bound": "tensor", "achieved": tf, "peak": peaks["bf16"], "unit": "TFLOP/s",
                         "frac": tf / peaks["bf16"], "traffic": traffic.get(name),
-                        "flops_per_launch": work_c[c] / cnt_c[c], "avg_launch_ms": ms_c[c] / cnt_c[c],
-                        "executed_tensor_frac": 3.0 * tf / peaks["bf16"],
+                        "flops_per_launch": work_c[c] * flop_scale / cnt_c[c], "avg_launch_ms": ms_c[c] / cnt_c[c],
+                        "executed_tensor_frac": 3.0 * work_c[c] / (ms_c[c] * 1e-3) / 1e12 / peaks["bf16"],
                         "peak_kind": "dense bf16 cuBLAS, sustained, of " + peaks["src"] +
-                                     "; f16x3 executes 3 tensor FLOPs per algorithmic FLOP"}
-            gbs = by * prof_steps / (ms_c[c] * 1e-3) / 1e9
+                                     "; algorithmic FLOPs on the unpadded H; f16x3 executes 3 tensor FLOPs per "
+                                     "algorithmic FLOP on the padded Hp (executed_tensor_frac)"}
+            gbs = by_cls.get(c, 0.0) * prof_steps / (ms_c[c] * 1e-3) / 1e9
             return {"kernel": name, "bound": "hbm", "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s",
                     "frac": gbs / peaks["hbm"], "traffic": traffic.get(name), "avg_launch_ms": ms_c[c] / cnt_c[c],
-                    "peak_kind": "copy bandwidth, of " + peaks["src"]}
+                    "algorithmic_bytes_per_launch": by_cls.get(c, 0.0) / max(cnt_c[c] // prof_steps, 1),
+                    "peak_kind": "copy bandwidth, of " + peaks["src"] + "; per-class algorithmic bytes (bench.py)"}
 
         top = max(range(n), key=lambda c: ms_c[c])
         roofline = class_roofline(top)
         # the other large classes, same definitions (the top class flips between cell_bwd and the gate GEMMs run to run)
-        rooflines = {PROF_CLASSES[c]: class_roofline(c) for c in (1, 3, 4, 5) if cnt_c[c] and c != top}
+        rooflines = {PROF_CLASSES[c]: class_roofline(c) for c in (0, 1, 3, 4, 5) if cnt_c[c] and c != top}
 
     # ---- CPU baseline on the host cores (rank 0, N = 1 only) ----------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sample = min(workload["batch"], 32)
-        rate, dt = cpu_oracle_rate(workload, sample, 1, 3)
+        rate, dt, sample, kind = cpu_reference_rate(workload, 1, 2, budget_s=25.0)
         cores = os.cpu_count() or 1
-        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": "%d-molecule batch x 3 timed fwd+bwd (%.2f s each) of the oracle (reference's padded "
-                         "PyTorch formulation, fp32, %d threads)" % (sample, dt, cores)}
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": "1 warm-up + 2 timed steps: " + _sample_note(workload, sample, kind, dt, cores)}
 
     if rank == 0:
         flops = 3.0 * algorithmic_flops(stats, H, workload["depthT"], workload["depthG"], workload["batch"], motif)
@@ -594,7 +675,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="cfg4", choices=sorted(WORKLOADS))
     ap.add_argument("--engine", type=int, default=None, help="0 auto, 1 fp32 CUDA cores, 2 tcgen05 3xTF32")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--resident", default="packed", choices=["packed", "make_cuda"],
@@ -603,6 +684,9 @@ def main():
                     help="run one extra step between cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     args = ap.parse_args()
     workload = WORKLOADS[args.workload]
+    if os.environ.get("GGPM_ALLOW_TEST_BACKEND"):
+        raise SystemExit("bench.py: GGPM_ALLOW_TEST_BACKEND is set — the C-ABI emulator seam of tests/ must be off "
+                         "for any measurement")
     if args.impl == "reference":
         run_reference(args, workload)
         return

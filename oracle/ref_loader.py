@@ -1,13 +1,15 @@
-"""Import the UNMODIFIED reference modules from /root/reference (this container only).
+"""Import the UNMODIFIED reference modules: from /root/reference in the build container, else from the staged
+byte-identical copy under oracle/_ref/ (oracle/make_ref.py; git-ignored, travels to the GPU box).
 
-TEST INFRASTRUCTURE ONLY — used by oracle/make_golden.py and by the oracle-vs-reference
-pin tests (skipped when /root/reference is absent, as on the GPU box).
+TEST INFRASTRUCTURE ONLY — used by oracle/make_golden*.py, by the oracle-vs-reference pin tests, by the
+wrapper-level drop-in tests and by bench.py's reference arm / cpu_baseline leg (the one place outside tests/ that
+may execute the reference).  The product (ggpm_b200/) never imports this.
 
 The reference imports rdkit at module import time (ggpm/nnutils.py:4-5,
 ggpm/mol_graph.py:2, ggpm/chemutils.py:1-6) but the encoder arithmetic never touches it,
 so rdkit is replaced by MagicMock modules.  ggpm/__init__.py star-imports everything, so a
 synthetic package object with the right __path__ is registered instead of executing it.
-Nothing is copied: the modules are executed from where they lie.
+The modules are executed unmodified from where they lie (the staged copy is byte-identical, see its MANIFEST.json).
 """
 import importlib
 import os
@@ -15,11 +17,26 @@ import sys
 import types
 from unittest.mock import MagicMock
 
-REFERENCE_ROOT = os.environ.get("GGPM_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+STAGED_ROOT = os.path.join(_HERE, "_ref")
+
+
+def _resolve_root():
+    for cand in (os.environ.get("GGPM_REFERENCE_ROOT"), "/root/reference", STAGED_ROOT):
+        if cand and os.path.isfile(os.path.join(cand, "ggpm", "encoder.py")):
+            return cand
+    return os.environ.get("GGPM_REFERENCE_ROOT", "/root/reference")
+
+
+REFERENCE_ROOT = _resolve_root()
 
 
 def reference_available() -> bool:
     return os.path.isfile(os.path.join(REFERENCE_ROOT, "ggpm", "encoder.py"))
+
+
+def reference_is_staged_copy() -> bool:
+    return os.path.abspath(REFERENCE_ROOT) == os.path.abspath(STAGED_ROOT)
 
 
 _cache = {}
@@ -48,6 +65,13 @@ def load_reference():
     ns.encoder = importlib.import_module("ggpm.encoder")
     _cache["ns"] = ns
     return ns
+
+
+def load_reference_module(name: str):
+    """any further module of the reference package by name ('property_vae', 'hpgnn', 'decoder',
+    'property_optimizer', ...), imported unmodified under the same stub"""
+    load_reference()
+    return importlib.import_module("ggpm." + name)
 
 
 class FakePairVocab:
