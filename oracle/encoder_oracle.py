@@ -15,8 +15,11 @@ read row 0, which is kept at zero), the gate inputs are concatenations ``[x | h]
 is one affine map on that concatenation.  This is deliberately the expensive padded form, so that
 timing it is timing the reference's CPU algorithm (bench.py ``cpu_baseline`` / ``--impl reference``).
 
-Dropout layers are identities here (eval mode or p = 0), which is the only regime where parity with
-the reference is defined bit-for-bit.
+Dropout layers are identities by default (eval mode or p = 0), which is the only regime where parity with
+the reference is defined bit-for-bit.  For train-mode parity the encoders take ``drop``: a dict
+``site -> multiplier`` (mask / (1 - p), shaped like the site's activation) applied exactly where the reference's
+``nn.Dropout`` modules sit (E_i / E_c: ggpm/encoder.py:51-55,98,111; W_i / W_c: :60-72; W_o of each MPNEncoder:
+:15-19); tests install the same fixed multipliers in place of the product's dropout modules.
 
 PARITY PIN: the reference ships no tests or golden vectors for this path, so the pin
 is the reference itself executed in the build container: ``oracle/make_golden.py`` runs the
@@ -96,8 +99,12 @@ def gru_messages(sd, prefix: str, x: Tensor, bgraph: Tensor, depth: int) -> Tens
     return h
 
 
+def _drop(drop, site: str, x: Tensor) -> Tensor:
+    return x if not drop or site not in drop else x * drop[site].to(x.dtype)
+
+
 def mpn_layer(sd, prefix: str, rnn_type: str, fnode: Tensor, fmess: Tensor, agraph: Tensor,
-              bgraph: Tensor, depth: int) -> Tuple[Tensor, Tensor]:
+              bgraph: Tensor, depth: int, drop=None) -> Tuple[Tensor, Tensor]:
     """ggpm/encoder.py:28-38: message RNN, messages->nodes sum, W_o + ReLU, row-0 mask."""
     if rnn_type == "LSTM":
         h, _ = lstm_messages(sd, prefix + "rnn.", fmess, bgraph, depth)
@@ -107,6 +114,7 @@ def mpn_layer(sd, prefix: str, rnn_type: str, fnode: Tensor, fmess: Tensor, agra
         raise ValueError("unsupported rnn cell type " + rnn_type)
     incoming = gather_padded(h, agraph).sum(1)
     node = torch.relu(_affine(sd, prefix + "W_o.0", torch.cat([fnode, incoming], dim=-1)))
+    node = _drop(drop, prefix + "W_o", node)
     return node * _row0_mask(node.shape[0], node), h
 
 
@@ -123,7 +131,7 @@ def _root_vectors(sd, node_feat: Tensor, hmess: Tensor, agraph: Tensor, scope) -
 
 
 def hier_encoder(sd: Dict[str, Tensor], rnn_type: str, depthT: int, depthG: int,
-                 tree_tensors: Sequence, graph_tensors: Sequence):
+                 tree_tensors: Sequence, graph_tensors: Sequence, drop=None):
     """HierMPNEncoder.forward, ggpm/encoder.py:140-157.  Index tensors are torch.long (make_cuda,
     ggpm/nnutils.py:210-214).  Returns (hroot, hnode, hinter, hatom)."""
     dtype = sd["W_root.0.weight"].dtype
@@ -136,35 +144,37 @@ def hier_encoder(sd: Dict[str, Tensor], rnn_type: str, depthT: int, depthG: int,
     bond_in = torch.cat([atom_feat.index_select(0, g_fmess[:, 0]),
                          _onehot(g_fmess[:, 2], N_BOND_TYPES, dtype),
                          _onehot(g_fmess[:, 3], MAX_POS, dtype)], dim=-1)
-    hatom, _ = mpn_layer(sd, "graph_encoder.", rnn_type, atom_feat, bond_in, g_agraph, g_bgraph, depthG)
+    hatom, _ = mpn_layer(sd, "graph_encoder.", rnn_type, atom_feat, bond_in, g_agraph, g_bgraph, depthG, drop)
 
     # attachment layer (embed_inter, ggpm/encoder.py:96-107)
-    attach_emb = sd["E_i.0.weight"].index_select(0, t_fnode[:, 1])
+    attach_emb = _drop(drop, "E_i", sd["E_i.0.weight"].index_select(0, t_fnode[:, 1]))
     atoms_of_motif = gather_padded(hatom, t_cgraph).sum(1)
     inter_feat = torch.relu(_affine(sd, "W_i.0", torch.cat([attach_emb, atoms_of_motif], dim=-1)))
+    inter_feat = _drop(drop, "W_i", inter_feat)
     pos = _onehot(t_fmess[:, 2], MAX_POS, dtype)
     inter_in = torch.cat([inter_feat.index_select(0, t_fmess[:, 0]), pos], dim=-1)
-    hinter, _ = mpn_layer(sd, "inter_encoder.", rnn_type, inter_feat, inter_in, t_agraph, t_bgraph, depthT)
+    hinter, _ = mpn_layer(sd, "inter_encoder.", rnn_type, inter_feat, inter_in, t_agraph, t_bgraph, depthT, drop)
 
     # motif layer (embed_tree, ggpm/encoder.py:109-117)
-    motif_emb = sd["E_c.0.weight"].index_select(0, t_fnode[:, 0])
+    motif_emb = _drop(drop, "E_c", sd["E_c.0.weight"].index_select(0, t_fnode[:, 0]))
     tree_feat = torch.relu(_affine(sd, "W_c.0", torch.cat([motif_emb, hinter], dim=-1)))
+    tree_feat = _drop(drop, "W_c", tree_feat)
     tree_in = torch.cat([tree_feat.index_select(0, t_fmess[:, 0]), pos], dim=-1)
-    hnode, hmess = mpn_layer(sd, "tree_encoder.", rnn_type, tree_feat, tree_in, t_agraph, t_bgraph, depthT)
+    hnode, hmess = mpn_layer(sd, "tree_encoder.", rnn_type, tree_feat, tree_in, t_agraph, t_bgraph, depthT, drop)
 
     hroot = _root_vectors(sd, tree_feat, hmess, t_agraph, t_scope)
     return hroot, hnode, hinter, hatom
 
 
-def motif_encoder(sd: Dict[str, Tensor], rnn_type: str, depthT: int, tree_tensors: Sequence):
+def motif_encoder(sd: Dict[str, Tensor], rnn_type: str, depthT: int, tree_tensors: Sequence, drop=None):
     """MotifEncoder.forward, ggpm/encoder.py:330-341.  Returns (root, node)."""
     dtype = sd["W_root.0.weight"].dtype
     t_fnode, t_fmess, t_agraph, t_bgraph, _, t_scope = tree_tensors
-    motif_emb = sd["E_c.0.weight"].index_select(0, t_fnode[:, 0])
-    attach_emb = sd["E_i.0.weight"].index_select(0, t_fnode[:, 1])
+    motif_emb = _drop(drop, "E_c", sd["E_c.0.weight"].index_select(0, t_fnode[:, 0]))
+    attach_emb = _drop(drop, "E_i", sd["E_i.0.weight"].index_select(0, t_fnode[:, 1]))
     mess_in = torch.cat([attach_emb.index_select(0, t_fmess[:, 0]),
                          _onehot(t_fmess[:, 2], MAX_POS, dtype)], dim=-1)
-    node, hmess = mpn_layer(sd, "tree_encoder.", rnn_type, motif_emb, mess_in, t_agraph, t_bgraph, depthT)
+    node, hmess = mpn_layer(sd, "tree_encoder.", rnn_type, motif_emb, mess_in, t_agraph, t_bgraph, depthT, drop)
     root = _root_vectors(sd, motif_emb, hmess, t_agraph, t_scope)
     return root, node
 

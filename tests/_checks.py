@@ -12,9 +12,46 @@ from oracle import encoder_oracle as eo
 from oracle.ref_loader import FakePairVocab, IdAtomVocab
 
 OUT_NAMES = {"hier": ("hroot", "hnode", "hinter", "hatom"), "motif": ("hroot", "hnode")}
-# fp32 path vs fp64 reference: the north-star bar (1e-5 relative) for outputs; gradients get 2e-5 because
-# the reference's own fp32 run differs from its fp64 run by up to ~1e-6 per layer
-TOL_OUT, TOL_GRAD = 1e-5, 2e-5
+# fp32 path vs the fp64 reference run: the north-star bar, 1e-5 of max|ref|, for outputs AND gradients.
+# The one documented exception (`grad_tolerance`): a parameter gradient whose value the REFERENCE's own fp32 run
+# cannot reproduce to 1e-5 (a ReLU pre-activation within rounding of zero flips that unit's whole downstream
+# gradient) is held to twice the measured reference-fp32-vs-fp64 gap of that tensor instead.
+TOL_OUT, TOL_GRAD = 1e-5, 1e-5
+
+# measured worst case per tensor of every parity comparison of the session: {test: {tensor: {"err", "tol", ...}}};
+# tests/conftest.py writes it to gpurun_out/parity_report.json at session end on a GPU box
+REPORT = {}
+
+
+def record(test, tensor, err, tol, **extra):
+    REPORT.setdefault(test, {})[tensor] = dict(err=float(err), tol=float(tol), **extra)
+
+
+def grad_tolerance(gap32):
+    """gap32: rel(reference fp32 gradient, reference fp64 gradient) of one tensor, or None when not measured"""
+    return TOL_GRAD if gap32 is None else max(TOL_GRAD, 2.0 * gap32)
+
+
+def compare_with_oracle(test, names, outs, ref_outs, grads, ref_grads, ref_grads32=None):
+    """outputs at TOL_OUT; every parameter gradient at grad_tolerance(reference's own fp32 gap); everything recorded"""
+    bad = []
+    for n, a, b in zip(names, outs, ref_outs):
+        e = rel(a, b)
+        record(test, "out:" + n, e, TOL_OUT)
+        if e > TOL_OUT:
+            bad.append((n, e, TOL_OUT))
+    for k, g in ref_grads.items():
+        if g is None or float(g.abs().max()) == 0.0:
+            assert k not in grads or grads[k] is None or float(grads[k].abs().max()) == 0.0, k
+            continue
+        assert grads.get(k) is not None, "no gradient for " + k
+        gap = None if ref_grads32 is None or ref_grads32.get(k) is None else rel(ref_grads32[k], g)
+        tol = grad_tolerance(gap)
+        e = rel(grads[k], g)
+        record(test, "grad:" + k, e, tol, ref_fp32_gap=gap)
+        if e > tol:
+            bad.append((k, e, tol))
+    assert not bad, bad
 
 
 def build_model(meta, device, dropout=0.0):
@@ -54,9 +91,11 @@ def check_forward_backward_golden(name, device, packed=False):
     model = build_model(meta, device)
     outs = run(model, meta, tree, graph)
     names = OUT_NAMES[meta["kind"]]
+    tag = "golden:%s%s:engine%s" % (name, ":packed" if packed else "", _engine_tag())
     for nme, o in zip(names, outs):
         assert o.dtype == torch.float32 and o.is_contiguous()
         assert tuple(o.shape) == z["out_" + nme].shape
+        record(tag, "out:" + nme, rel(o, z["out_" + nme]), TOL_OUT)
         assert rel(o, z["out_" + nme]) <= TOL_OUT, (nme, rel(o, z["out_" + nme]))
     for o in outs[1:]:
         assert float(o[0].detach().abs().max()) == 0.0
@@ -67,7 +106,16 @@ def check_forward_backward_golden(name, device, packed=False):
             assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
         else:
             assert p.grad is not None, k
+            record(tag, "grad:" + k, rel(p.grad, ref), TOL_GRAD)
             assert rel(p.grad, ref) <= TOL_GRAD, (k, rel(p.grad, ref))
+
+
+def _engine_tag():
+    from ggpm_b200 import _lib
+    try:
+        return str(int(_lib.backend().ggpm_get_gemm_engine()))
+    except Exception:
+        return "?"
 
 
 def check_root_only_loss(device):
@@ -111,15 +159,92 @@ def check_no_grad_eval(device):
 
 
 def check_train_dropout(device):
+    """train mode with the real nn.Dropout modules: two calls differ, gradients are finite, and at the first dropout
+    site of the path (the atom read-out W_o, ggpm/encoder.py:15-19,33-34 — nothing upstream of it is random) every
+    element is either dropped or the eval-mode value / (1 - p), with a drop rate near p"""
     meta, z, tree, graph = load_golden("hier_lstm_small")
     tree, graph = to_dev(tree, device), to_dev(graph, device)
-    model = build_model(meta, device, dropout=0.5).train()
+    p = 0.5
+    model = build_model(meta, device, dropout=p).train()
     torch.manual_seed(0)
-    a = model(tree, graph)[0]
+    outs = model(tree, graph)
+    a = outs[0]
     b = model(tree, graph)[0]
     assert not torch.equal(a, b)
     a.sum().backward()
-    assert all(torch.isfinite(p.grad).all() for p in model.parameters() if p.grad is not None)
+    assert all(torch.isfinite(q.grad).all() for q in model.parameters() if q.grad is not None)
+    hatom_train = outs[3].detach()
+    with torch.no_grad():
+        hatom_eval = model.eval()(tree, graph)[3]
+    live = hatom_eval > 0                                   # ReLU zeros say nothing about dropout
+    kept = hatom_train != 0
+    scaled = hatom_eval / (1.0 - p)
+    assert torch.allclose(hatom_train[kept], scaled[kept], rtol=1e-5, atol=1e-6)
+    assert not bool((kept & ~live).any())
+    rate = 1.0 - float(kept[live].float().mean())
+    assert abs(rate - p) < 0.05, rate
+
+
+class FixedDrop(torch.nn.Module):
+    """stands in for an nn.Dropout of the model under test: multiplies by a fixed multiplier (mask / (1 - p)); the
+    product carries node tables at a padded width, extra columns get multiplier 0"""
+
+    def __init__(self, mult):
+        super().__init__()
+        self.mult = mult
+
+    def forward(self, x):
+        m = self.mult.to(x.device, x.dtype)
+        if m.shape[1] < x.shape[1]:
+            m = torch.nn.functional.pad(m, (0, x.shape[1] - m.shape[1]))
+        return x * m
+
+
+def install_fixed_dropout(model, kind, tree, graph, hidden, embed, p, seed):
+    """replaces every dropout module of a ggpm_b200 encoder by FixedDrop with seeded masks; returns the oracle's
+    `drop` dict (same multipliers, fp64)"""
+    gen = torch.Generator().manual_seed(seed)
+    n_t = tree[0].shape[0]
+    sites = {"E_i": (n_t, embed), "E_c": (n_t, embed), "tree_encoder.W_o": (n_t, hidden)}
+    if kind == "hier":
+        sites.update({"W_i": (n_t, hidden), "W_c": (n_t, hidden), "inter_encoder.W_o": (n_t, hidden),
+                      "graph_encoder.W_o": (graph[0].shape[0], hidden)})
+    drop = {k: (torch.rand(shape, generator=gen) >= p).double() / (1.0 - p) for k, shape in sites.items()}
+    model.E_i = torch.nn.Sequential(model.E_i[0], FixedDrop(drop["E_i"]))
+    model.E_c = torch.nn.Sequential(model.E_c[0], FixedDrop(drop["E_c"]))
+    model.tree_encoder.W_o[2] = FixedDrop(drop["tree_encoder.W_o"])
+    if kind == "hier":
+        model.W_i[2] = FixedDrop(drop["W_i"])
+        model.W_c[2] = FixedDrop(drop["W_c"])
+        model.inter_encoder.W_o[2] = FixedDrop(drop["inter_encoder.W_o"])
+        model.graph_encoder.W_o[2] = FixedDrop(drop["graph_encoder.W_o"])
+    return drop
+
+
+def check_fixed_mask_dropout_parity(name, device, p=0.1):
+    """train-mode parity (the benchmarked cfg2 / cfg5 run dropout 0.1 in train mode): the same fixed dropout
+    multipliers at every dropout site on both sides — the product with its nn.Dropout modules replaced by FixedDrop,
+    the fp64 oracle fed the same masks where the reference's nn.Dropout modules sit — outputs and all gradients"""
+    meta, z, tree, graph = load_golden(name)
+    kind, H = meta["kind"], meta["hidden"]
+    model = build_model(meta, device, dropout=p).train()
+    drop = install_fixed_dropout(model, kind, tree, graph, H, H, p, seed=17)
+    outs = run(model, meta, to_dev(tree, device), to_dev(graph, device))
+    names = OUT_NAMES[kind]
+    cots = [torch.from_numpy(z["cot_" + n]) for n in names]
+    sum((o * c.float().to(device)).sum() for o, c in zip(outs, cots)).backward()
+    nm, na = meta["vocab"]
+    sd = eo.random_state(kind, meta["rnn"], H, H, meta["weight_seed"], n_motif=nm, n_attach=na)
+    sdo = {k: v.double().requires_grad_(True) for k, v in sd.items()}
+    if kind == "hier":
+        ref = eo.hier_encoder(sdo, meta["rnn"], meta["depthT"], meta["depthG"], tree, graph, drop=drop)
+    else:
+        ref = eo.motif_encoder(sdo, meta["rnn"], meta["depthT"], tree, drop=drop)
+    sum((o * c.double()).sum() for o, c in zip(ref, cots)).backward()
+    # the masks must matter: the dropout-free golden outputs differ
+    assert rel(ref[0], z["out_" + names[0]]) > 1e-3
+    compare_with_oracle("fixed_mask_dropout:%s:p%.1f" % (name, p), names, outs, ref,
+                        {k: q.grad for k, q in model.named_parameters()}, {k: v.grad for k, v in sdo.items()})
 
 
 def check_inputs_not_mutated(device):

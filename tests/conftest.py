@@ -36,3 +36,27 @@ def load_golden(name):
 @pytest.fixture(scope="session")
 def root_dir():
     return ROOT
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """measured worst case per tensor of the parity comparisons (tests/_checks.py REPORT) -> gpurun_out/parity_report.json
+    (only when a GPU run produced entries; committed under profiles/ per round)"""
+    try:
+        import _checks
+        import torch
+        if not _checks.REPORT or not torch.cuda.is_available():
+            return
+        out_dir = os.path.join(ROOT, "gpurun_out")
+        os.makedirs(out_dir, exist_ok=True)
+        path = os.path.join(out_dir, "parity_report.json")
+        old = {}
+        if os.path.exists(path):
+            try:
+                old = json.load(open(path))
+            except Exception:
+                old = {}
+        old.update(_checks.REPORT)
+        with open(path, "w") as f:
+            json.dump(old, f, indent=1, sort_keys=True)
+    except Exception:
+        pass

@@ -1,6 +1,6 @@
 """B200: the real CUDA library behind the drop-in modules, against the golden vectors of the unmodified
 reference and the oracle on seeded inputs (fp32 path, tolerance 1e-5 relative on outputs as BASELINE.json's
-north_star states; 2e-5 on gradients).  Every call goes through the C ABI (ggpm_b200/_lib.py)."""
+north_star states, on outputs and on gradients).  Every call goes through the C ABI (ggpm_b200/_lib.py)."""
 import os
 import sys
 
@@ -45,6 +45,12 @@ def test_no_grad_and_eval_mode(engine):
 
 def test_train_mode_dropout_is_applied():
     C.check_train_dropout(DEV)
+
+
+@pytest.mark.parametrize("name", ["hier_lstm_small", "hier_lstm_deep", "hier_gru_small", "motif_lstm_small"])
+@pytest.mark.parametrize("p", [0.1, 0.5])
+def test_train_mode_parity_with_fixed_dropout_masks(name, p):
+    C.check_fixed_mask_dropout_parity(name, DEV, p=p)
 
 
 def test_inputs_are_not_mutated():

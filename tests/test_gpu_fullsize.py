@@ -20,7 +20,7 @@ from ggpm_b200 import _lib, ingest, synth, tensorize                            
 from oracle import encoder_oracle as eo                                                # noqa: E402
 
 pytestmark = pytest.mark.gpu
-TOL_OUT, TOL_GRAD = 1e-5, 2e-5
+TOL_OUT = 1e-5
 # Gradients at these sizes cross ReLU kinks: of the ~2 M ReLU units of a cfg2 batch one or two have a pre-activation
 # within rounding of zero, and whichever way fp32 rounding tips it switches that unit's whole downstream gradient (one
 # molecule's rows of E_i / E_c move by a few per cent).  The reference has the same property — its own fp32 run
@@ -62,15 +62,12 @@ def test_cfg2_shape_matches_fp64_oracle():
     sdo = {k: v.double().requires_grad_(True) for k, v in sd.items()}
     ref = eo.hier_encoder(sdo, "LSTM", 20, 20, as_long(tree_np), as_long(graph_np))
     ref[0].sum().backward()
-    for name, a, b in zip(C.OUT_NAMES["hier"], outs, ref):
-        assert C.rel(a, b) <= TOL_OUT, (name, C.rel(a, b))
-        if name != "hroot":
-            assert float(a[0].abs().max()) == 0.0
-    for k, g in sdo.items():
-        if g.grad is None or float(g.grad.abs().max()) == 0.0:
-            assert k not in grads or float(grads[k].abs().max()) == 0.0, k
-        else:
-            assert C.rel(grads[k], g.grad) <= TOL_GRAD, (k, C.rel(grads[k], g.grad))
+    sd32 = {k: v.clone().requires_grad_(True) for k, v in sd.items()}      # the reference's own fp32 evaluation
+    eo.hier_encoder(sd32, "LSTM", 20, 20, as_long(tree_np), as_long(graph_np))[0].sum().backward()
+    for name, a in zip(C.OUT_NAMES["hier"][1:], outs[1:]):
+        assert float(a[0].abs().max()) == 0.0
+    C.compare_with_oracle("full:hier_lstm_h250_d20_b256_cfg2", C.OUT_NAMES["hier"], outs, [r.detach() for r in ref], grads,
+                          {k: v.grad for k, v in sdo.items()}, {k: v.grad for k, v in sd32.items()})
 
 
 @pytest.mark.parametrize("H,B", [(250, 256), (500, 192)])

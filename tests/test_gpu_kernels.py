@@ -451,10 +451,10 @@ def test_lstm_layer_forward_backward(engine, H, Hp, depth, batch, with_k2):
     assert rel(c, hist["c"][-1]) <= 1e-5
     assert float(h[0].abs().max()) == 0 and float(h[:, H:].abs().max()) == 0
     (h * d["cot"].float().to(DEV)).sum().backward()
-    assert rel(u4.grad[:3 * Hp], dUg) <= 2e-5 and rel(u4.grad[3 * Hp:], dUf) <= 2e-5
-    assert rel(T.grad, dT) <= 2e-5
-    assert rel(Wx.grad, dYn.t() @ d["phi"]) <= 2e-5
-    assert rel(phi.grad, dYn @ d["Wx"]) <= 2e-5
+    assert rel(u4.grad[:3 * Hp], dUg) <= 1e-5 and rel(u4.grad[3 * Hp:], dUf) <= 1e-5
+    assert rel(T.grad, dT) <= 1e-5
+    assert rel(Wx.grad, dYn.t() @ d["phi"]) <= 1e-5
+    assert rel(phi.grad, dYn @ d["Wx"]) <= 1e-5
 
 
 @pytest.mark.parametrize("H,Hp,depth,batch,with_k2", [(20, 32, 3, 3, False), (250, 256, 4, 6, True)])
@@ -474,4 +474,4 @@ def test_gru_layer_forward_backward(engine, H, Hp, depth, batch, with_k2):
     assert rel(h, h_ref) <= 1e-5
     (h * d["cot"].float().to(DEV)).sum().backward()
     for got, want in ((uz, dUz), (ur, dUr), (uh, dUh), (b, dbr), (phi, dYn @ d["Wx"]), (Wx, dYn.t() @ d["phi"])):
-        assert rel(got.grad, want) <= 2e-5
+        assert rel(got.grad, want) <= 1e-5

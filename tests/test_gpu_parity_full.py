@@ -1,0 +1,148 @@
+"""B200: the CUDA path against the fp64 oracle (itself pinned to the live reference at 1e-12, tests/test_oracle_golden.py)
+on the configurations the performance claims stand on — the comparisons VERDICT round 1 found missing:
+
+  * hidden 500, depth 20/20 (BASELINE config #3's width: Hp = 512, K = 512 tensor-core tiles);
+  * hidden 250 with a batch whose atom layer crosses 32 768 message rows NATURALLY, so the forward takes the
+    `lstm_sgather` + plane-fed GEMM path every cfg3 / cfg4 atom layer takes (no environment override);
+  * MotifEncoder + the latent head at hidden 250, latent 24 (BASELINE config #5, the PropertyVAE encoder side);
+  * the graph GRU end to end at hidden 250, depth 20.
+
+Bar: outputs and every parameter gradient within 1e-5 of max|ref| (north star).  The documented exception
+(tests/_checks.py `grad_tolerance`): where the REFERENCE's own fp32 evaluation misses its fp64 evaluation by more
+than 5e-6 on a tensor (a ReLU pre-activation within rounding of zero flips that unit's downstream gradient), that
+tensor is held to twice the measured reference gap.  Every measured value lands in gpurun_out/parity_report.json.
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import _checks as C                                                                     # noqa: E402
+import ggpm_b200                                                                       # noqa: E402
+from ggpm_b200 import ingest, latent, synth, tensorize                                  # noqa: E402
+from oracle import encoder_oracle as eo                                                # noqa: E402
+from oracle import latent_oracle as lo                                                 # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+def _as_long(ts):
+    return [torch.from_numpy(np.asarray(t)).long() if not isinstance(t, list) else t for t in ts]
+
+
+def _oracle(kind, rnn, depthT, depthG, sd, tree_np, graph_np, dtype, loss):
+    """-> (outputs, {param: grad}) of the oracle at `dtype` for loss(outs)"""
+    torch.set_num_threads(os.cpu_count() or 1)
+    leaves = {k: v.to(dtype).requires_grad_(True) for k, v in sd.items()}
+    tree, graph = _as_long(tree_np), _as_long(graph_np)
+    if kind == "hier":
+        outs = eo.hier_encoder(leaves, rnn, depthT, depthG, tree, graph)
+    else:
+        outs = eo.motif_encoder(leaves, rnn, depthT, tree)
+    loss(outs, leaves).backward()
+    return [o.detach() for o in outs], {k: v.grad for k, v in leaves.items()}
+
+
+def _product(kind, rnn, H, depthT, depthG, sd, mols, loss, extra_modules=None):
+    cls = ggpm_b200.HierMPNEncoder if kind == "hier" else ggpm_b200.MotifEncoder
+    model = cls(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), rnn, H, H, depthT, depthG, 0.0)
+    model.load_state_dict({k: v for k, v in sd.items() if k in model.state_dict()}, strict=True)
+    model = model.cuda()
+    tree, graph = ingest.pack(tensorize.tensorize(mols)).to_device("cuda")
+    outs = model(tree, graph) if kind == "hier" else model(tree)
+    loss(outs, model).backward()
+    torch.cuda.synchronize()
+    return [o.detach() for o in outs], {k: p.grad for k, p in model.named_parameters()}, (tree, graph)
+
+
+def _root_sum(outs, _):
+    return outs[0].sum()
+
+
+def _all_outputs(seed):
+    """a fixed random cotangent on every output (so tree_encoder.W_o and every node table carry gradient)"""
+    def loss(outs, _):
+        gen = torch.Generator().manual_seed(seed)
+        return sum((o * torch.randn(o.shape, generator=gen, dtype=torch.float64).to(o.dtype).to(o.device)).sum() for o in outs)
+    return loss
+
+
+def _compare(tag, kind, rnn, H, depth, B, seed, loss, min_atom_rows=0):
+    mols = synth.random_batch(seed, B)
+    sd = eo.random_state(kind, rnn, H, H, seed % 97)
+    tree_np, graph_np = synth.tensorize(mols)
+    if min_atom_rows:
+        assert graph_np[1].shape[0] >= min_atom_rows, "batch too small to cross the plane-fed threshold: %d rows" % graph_np[1].shape[0]
+    outs, grads, _ = _product(kind, rnn, H, depth, depth, sd, mols, loss)
+    ref_outs, ref_grads = _oracle(kind, rnn, depth, depth, sd, tree_np, graph_np, torch.float64, loss)
+    _, ref_grads32 = _oracle(kind, rnn, depth, depth, sd, tree_np, graph_np, torch.float32, loss)
+    for name, a in zip(C.OUT_NAMES[kind][1:], outs[1:]):
+        assert float(a[0].abs().max()) == 0.0, name                  # row 0 of every node table is exactly zero
+    C.compare_with_oracle(tag, C.OUT_NAMES[kind], outs, ref_outs, grads, ref_grads, ref_grads32)
+
+
+def test_hidden_500_depth_20_matches_fp64_oracle():
+    _compare("full:hier_lstm_h500_d20_b32", "hier", "LSTM", 500, 20, 32, 50032, _root_sum)
+
+
+def test_hidden_500_all_outputs_cotangent_matches_fp64_oracle():
+    _compare("full:hier_lstm_h500_d20_b16_allout", "hier", "LSTM", 500, 20, 16, 50016, _all_outputs(3))
+
+
+def test_plane_fed_forward_reached_naturally_matches_fp64_oracle():
+    """480 molecules -> ~35.9k atom-layer message rows >= the library's 32 768-row threshold (api.cu sgather_min_rows):
+    lstm_sgather + two TMA-fed forward GEMMs per round, exactly as at cfg3 / cfg4, with no GGPM_SGATHER_MIN_ROWS"""
+    assert "GGPM_SGATHER_MIN_ROWS" not in os.environ
+    _compare("full:hier_lstm_h250_d20_b480_planes", "hier", "LSTM", 250, 20, 480, 48000, _root_sum, min_atom_rows=32768)
+
+
+def test_gru_hidden_250_depth_20_matches_fp64_oracle():
+    _compare("full:hier_gru_h250_d20_b32", "hier", "GRU", 250, 20, 32, 25032, _all_outputs(5))
+
+
+def test_motif_encoder_hidden_250_matches_fp64_oracle():
+    _compare("full:motif_lstm_h250_d20_b256", "motif", "LSTM", 250, 20, 256, 25256, _all_outputs(7))
+
+
+def test_cfg5_motif_encoder_plus_latent_head_matches_fp64_oracle():
+    """BASELINE config #5, encoder side of PropertyVAE.forward (ggpm/property_vae.py:95-99): MotifEncoder ->
+    rsample(R_mean, R_var) -> z, KL at hidden 250, latent 24, batch 256, same noise on both sides"""
+    H, L, B, depth = 250, 24, 256, 20
+    mols = synth.random_batch(55256, B)
+    sd = eo.random_state("motif", "LSTM", H, H, 11)
+    gen = torch.Generator().manual_seed(12)
+    lat = {"R_mean.weight": torch.randn(L, H, generator=gen) / H ** 0.5, "R_mean.bias": torch.randn(L, generator=gen) * 0.1,
+           "R_var.weight": torch.randn(L, H, generator=gen) / H ** 0.5, "R_var.bias": torch.randn(L, generator=gen) * 0.1}
+    eps = torch.randn(B, L, generator=gen)
+    cot = torch.randn(B, L, generator=gen)
+    tree_np, graph_np = synth.tensorize(mols)
+
+    model = ggpm_b200.MotifEncoder(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H, depth, depth, 0.0)
+    model.load_state_dict(sd, strict=True)
+    model.R_mean, model.R_var = torch.nn.Linear(H, L), torch.nn.Linear(H, L)
+    with torch.no_grad():
+        for k, v in lat.items():
+            dict(model.named_parameters())[k].copy_(v)
+    model = model.cuda()
+    tree, _ = ingest.pack((tensorize.tensorize(mols)[0], None)).to_device("cuda")
+    root = model(tree)[0]
+    z, kl = latent.rsample(root, model.R_mean, model.R_var, True, epsilon=eps.cuda())
+    ((z * cot.cuda()).sum() + 0.7 * kl).backward()
+    grads = {k: p.grad for k, p in model.named_parameters()}
+
+    def oracle(dtype):
+        torch.set_num_threads(os.cpu_count() or 1)
+        leaves = {k: v.to(dtype).requires_grad_(True) for k, v in {**sd, **lat}.items()}
+        r = eo.motif_encoder(leaves, "LSTM", depth, _as_long(tree_np))[0]
+        zz, kk = lo.rsample(r, leaves["R_mean.weight"], leaves["R_mean.bias"], leaves["R_var.weight"],
+                            leaves["R_var.bias"], eps.to(dtype), True)
+        ((zz * cot.to(dtype)).sum() + 0.7 * kk).backward()
+        return [r.detach(), zz.detach(), kk.detach()], {k: v.grad for k, v in leaves.items()}
+
+    ref_outs, ref_grads = oracle(torch.float64)
+    _, ref_grads32 = oracle(torch.float32)
+    C.compare_with_oracle("full:cfg5_motif_latent_h250_l24_b256", ("hroot", "z", "kl"), [root.detach(), z.detach(), kl.detach()],
+                          ref_outs, grads, ref_grads, ref_grads32)

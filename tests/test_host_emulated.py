@@ -55,6 +55,11 @@ def test_train_mode_dropout_is_applied(emu):
     C.check_train_dropout(DEV)
 
 
+@pytest.mark.parametrize("name", ["hier_lstm_small", "hier_gru_small", "motif_lstm_small"])
+def test_train_mode_parity_with_fixed_dropout_masks(emu, name):
+    C.check_fixed_mask_dropout_parity(name, DEV, p=0.1)
+
+
 def test_inputs_are_not_mutated(emu):
     C.check_inputs_not_mutated(DEV)
 
