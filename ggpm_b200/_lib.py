@@ -28,6 +28,7 @@ SIGNATURES = {
     "ggpm_prof_enable": (I, [I]),
     "ggpm_prof_collect": (I, [P, P, P, I]),
     "ggpm_csr_from_padded": (I, [P, I, I, I, I, P, P, P, P]),
+    "ggpm_check_ids": (I, [P, I, c_longlong, c_longlong, c_longlong, c_longlong, P, I, P]),
     "ggpm_csr_transpose": (I, [P, P, I, I, P, P, P, P, P]),
     "ggpm_gather_sum": (I, [P, I, P, P, P, I, I, I, I, P]),
     "ggpm_embedding_bwd": (I, [P, I, P, I, c_longlong, I, I, I, P, I, P]),
@@ -49,7 +50,7 @@ SIGNATURES = {
     "ggpm_table_wgrad": (I, [P, I, I, I, P, P, P, I, I, P]),
     "ggpm_lstm_plan": (I, [I, I]),
     "ggpm_lstm_fwd": (I, [I, I, I, I, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, P]),
-    "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 27 + [I, P]),
+    "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 28 + [I, P]),
     "ggpm_gru_fwd": (I, [I, I, I, I] + [P] * 13 + [I, P]),
     "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
     "ggpm_rsample_fwd": (I, [P, I, I, P, I, I, I, P, I, P, P, P]),
@@ -97,8 +98,12 @@ def backend():
 
 
 def _install_test_backend(obj):
-    """TEST SEAM ONLY (tests/_emu_lib.py): route the C-ABI calls to a host emulator."""
+    """TEST SEAM ONLY (tests/_emu_lib.py): route the C-ABI calls to a host emulator.  Refused unless the process was
+    started with GGPM_ALLOW_TEST_BACKEND=1 (tests/conftest.py sets it; bench.py aborts when it is set), so no product
+    run can end up on a CPU route by accident."""
     global _TEST_BACKEND
+    if obj is not None and os.environ.get("GGPM_ALLOW_TEST_BACKEND") != "1":
+        raise RuntimeError("ggpm_b200: the C-ABI emulator seam is for tests only (set GGPM_ALLOW_TEST_BACKEND=1)")
     _TEST_BACKEND = obj
 
 

@@ -415,9 +415,10 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
 extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                              const int32_t* bt_ptr, const int32_t* bt_row, const float* Yn, const int32_t* src,
                              const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
-                             const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
-                             float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
-                             float* w_split, const void* hist_h16, void* z_planes, int h_rotate, void* stream) {
+                             const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final,
+                             const float* dC_final, float* dX, float* dUg, float* dUf, float* dA, float* dC, float* dP,
+                             float* dS, float* S, float* dHn, float* w_split, const void* hist_h16, void* z_planes,
+                             int h_rotate, void* stream) {
     GGPM_TRY(check_dims("lstm_bwd", E1, H, Hp, depth));
     GGPM_REQUIRE(b_ptr && b_col && bt_ptr && bt_row && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp &&
                      dH_final && dX && dUg && dUf && dA && dC && dP && dS && S && dHn,
@@ -427,7 +428,8 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     const XTabArgs x{Yn, src, T, k1, k2};
     float* dH = dH_final;
     float* dH_next = dHn;
-    const float* dC_cur = nullptr;   // dL/dc^depth = 0
+    const float* dC_cur = dC_final;  // dL/dc^depth (NULL: zero — the encoders consume only h)
+    GGPM_REQUIRE(((uintptr_t)dC_final & 15) == 0, "lstm_bwd: dC_final must be 16-byte aligned");
     const bool tc_ok = tc_layer_ok(Hp, {hist_h, hist_c, hist_gp, Ug, Uf, dUg, dUf, dA, dP, dH_final, dHn});
     const bool fused_w = tc_ok && Uf == Ug + (size_t)3 * Hp * Hp && dUf == dUg + (size_t)3 * Hp * Hp && Hp % 128 == 0;
     // state gradient dH = [..] [Ug; Uf]: the transposed weights [Hp, 4Hp] are split into tf32 planes once, then TMA-fed

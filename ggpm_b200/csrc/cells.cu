@@ -465,13 +465,13 @@ table_wgrad_kernel(const float* __restrict__ dX, int ld_dx, int rows, int width,
     if (c < width) {
         for (int r = r0 + w; r < r1; r += 8) {
             const float4 v = ld4(dX + (size_t)r * ld_dx + c);
-            const int a = __ldg(k1 + r);
+            const int a = min(max(__ldg(k1 + r), 0), ntab - 1);      // ids are validated by the callers; clamp so a bad one cannot write outside acc
             atomicAdd(&acc[a][lane], v.x);
             atomicAdd(&acc[a][32 + lane], v.y);
             atomicAdd(&acc[a][64 + lane], v.z);
             atomicAdd(&acc[a][96 + lane], v.w);
             if (k2) {
-                const int b = __ldg(k2 + r);
+                const int b = min(max(__ldg(k2 + r), 0), ntab - 1);
                 atomicAdd(&acc[b][lane], v.x);
                 atomicAdd(&acc[b][32 + lane], v.y);
                 atomicAdd(&acc[b][64 + lane], v.z);

@@ -30,7 +30,7 @@ __global__ void csr_fill_kernel(const IdxT* __restrict__ idx, int rows, int widt
     for (int k = 0; k < width; ++k) {
         IdxT v = p[k];
         if (v != 0) {
-            if (v < 0 || v >= (IdxT)n_src) { atomicExch(bad, 1); v = 0; }
+            if (v < 0 || v >= (IdxT)n_src) { atomicOr(bad, 1); v = 0; }
             col[o++] = (int)v;
         }
     }
@@ -123,6 +123,18 @@ __global__ void tr_sort_kernel(const int* __restrict__ t_ptr, int n_src, int* __
     }
 }
 
+// ids[i * stride] in [lo, hi) for all i, else *bad |= bit.  One pass, no host synchronisation.
+template <typename IdxT>
+__global__ void check_ids_kernel(const IdxT* __restrict__ ids, long long n, long long stride, long long lo, long long hi,
+                                 int* __restrict__ bad, int bit) {
+    int any = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const long long v = (long long)ids[i * stride];
+        any |= (v < lo || v >= hi);
+    }
+    if (__any_sync(0xffffffffu, any) && (threadIdx.x & 31) == 0) atomicOr(bad, bit);
+}
+
 template <typename IdxT>
 static int csr_from_padded_impl(const IdxT* idx, int rows, int width, int n_src, int* row_ptr, int* col,
                                 int* bad_flag, cudaStream_t st) {
@@ -146,6 +158,21 @@ extern "C" int ggpm_csr_from_padded(const void* idx, int idx_is_64bit, int rows,
     if (idx_is_64bit)
         return csr_from_padded_impl<long long>((const long long*)idx, rows, width, n_src_rows, row_ptr, col, bad_flag, st);
     return csr_from_padded_impl<int>((const int*)idx, rows, width, n_src_rows, row_ptr, col, bad_flag, st);
+}
+
+extern "C" int ggpm_check_ids(const void* ids, int ids_are_64bit, long long n, long long stride, long long lo, long long hi,
+                              int32_t* bad_flag, int bit, void* stream) {
+    GGPM_REQUIRE(bad_flag && (ids || n == 0) && n >= 0 && stride >= 1 && bit != 0, "check_ids: bad arguments");
+    if (n == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int T = 256;
+    long long want = ceil_div_ll(n, T);
+    const int blocks = (int)(want < 4LL * sm_count() ? want : 4LL * sm_count());
+    if (ids_are_64bit)
+        check_ids_kernel<long long><<<blocks, T, 0, st>>>((const long long*)ids, n, stride, lo, hi, bad_flag, bit);
+    else
+        check_ids_kernel<int><<<blocks, T, 0, st>>>((const int*)ids, n, stride, lo, hi, bad_flag, bit);
+    return check_launch("check_ids");
 }
 
 extern "C" int ggpm_csr_transpose(const int32_t* row_ptr, const int32_t* col, int rows, int n_src_rows,

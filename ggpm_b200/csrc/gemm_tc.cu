@@ -529,7 +529,9 @@ struct F16Params {
     const int* a_deg;
     const float* a_scale;                  // when given: the A scale itself (A already is fp16 planes)
     const float* b_scale; float b_scale_const;
-    unsigned long long* dbg;               // optional [gridDim.x][8] globaltimer stamps (GGPM_F16_TRACE experiments)
+#ifdef GGPM_TRACE
+    unsigned long long* dbg;               // [gridDim.x][8] globaltimer stamps; only in -DGGPM_TRACE builds (tools/f16_trace.py)
+#endif
 };
 
 __device__ __forceinline__ unsigned long long gtimer() {
@@ -537,7 +539,11 @@ __device__ __forceinline__ unsigned long long gtimer() {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
+#ifdef GGPM_TRACE
 #define F16_STAMP(i) do { if (fp.dbg) fp.dbg[blockIdx.x * 8 + (i)] = gtimer(); } while (0)
+#else
+#define F16_STAMP(i) do { } while (0)       // the stamp hook is compiled out of production builds
+#endif
 
 // modes of gemm_f16_kernel
 enum { F16_A_REGS = 0,      // A: fp32 K-major rows through registers (gather-sum, scaling, split); B: K-major planes by TMA
@@ -1220,8 +1226,10 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
     p.beta = g.beta; p.bias = g.bias; p.act = g.act; p.zero_row0 = g.zero_row0;
     fp.a_amax = g.a_amax; fp.a_amax_n = g.a_amax_n; fp.a_amax_const = g.a_amax_const; fp.a_deg = g.a_deg;
     fp.a_scale = g.a_scale; fp.b_scale = g.b_scale; fp.b_scale_const = g.b_scale_const;
+#ifdef GGPM_TRACE
     fp.dbg = nullptr;
     if (const char* tr = getenv("GGPM_F16_TRACE")) fp.dbg = (unsigned long long*)strtoull(tr, nullptr, 0);
+#endif
     const bool plain_epilogue = !g.bias && g.act == GGPM_ACT_NONE && !g.zero_row0 && (g.beta == 0.f || g.beta == 1.f);
     bool wide = g.N > 128;
     // state gradient of a small layer (N = Hp = 256, fewer than two waves of 128 x 256 tiles): 128-wide tiles double the

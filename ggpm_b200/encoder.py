@@ -29,16 +29,25 @@ def _i32(t: torch.Tensor) -> torch.Tensor:
     return t.to(torch.int32).contiguous()
 
 
-def _message_graph(fmess, bgraph, n_nodes, n_table_rows, k2_offset=None) -> Fn.MessageGraph:
-    """bgraph CSR + per-message source / one-hot column ids; prepared on the host when the batch came through
-    ingest.PackedBatch, else derived here (fmess columns: src, dst, label, position — ggpm/mol_graph.py:262-270)"""
-    b = Fn.csr_from_padded(bgraph, fmess.shape[0])
+def _message_graph(fmess, bgraph, n_nodes, n_table_rows, k2_offset=None, guard=None) -> Fn.MessageGraph:
+    """bgraph CSR + per-message source / one-hot column ids; prepared (and range-checked) on the host when the batch
+    came through ingest.PackedBatch, else derived and checked here (fmess columns: src, dst, label, position —
+    ggpm/mol_graph.py:262-270).  The ids index the node table (src) and the one-hot weight-column table (k1, k2)
+    inside the cell kernels; the reference's index_select raises on the same violations (ggpm/encoder.py:103-106,
+    114-116, 121-125)."""
+    b = Fn.csr_from_padded(bgraph, fmess.shape[0], guard=guard)
     cols = getattr(fmess, "_ggpm_cols", None)
     if cols is not None:
         src, k1, k2 = cols
         if k2_offset is None:
             k2 = None
     else:
+        if guard is not None:
+            k1_hi = n_table_rows if k2_offset is None else k2_offset
+            guard.check(fmess[:, 0], 0, n_nodes, "message source node (fmess[:, 0])")
+            guard.check(fmess[:, 2], 0, k1_hi, "message label (fmess[:, 2])")
+            if k2_offset is not None:
+                guard.check(fmess[:, 3], 0, n_table_rows - k2_offset, "message position (fmess[:, 3])")
         src, k1 = _i32(fmess[:, 0]), _i32(fmess[:, 2])
         k2 = None if k2_offset is None else _i32(fmess[:, 3] + k2_offset)
     mg = Fn.MessageGraph(b, src, k1, k2, n_nodes, n_table_rows)
@@ -102,8 +111,10 @@ class MPNEncoder(nn.Module):
         from .rnn import _identity_graph
         if fnode.shape[0] != agraph.shape[0]:
             raise ValueError("fnode and agraph disagree on the number of nodes")
-        mg = _identity_graph(fmess, bgraph)
-        a_csr = Fn.csr_from_padded(agraph, fmess.shape[0])
+        guard = Fn.IndexGuard(fmess.device)
+        mg = _identity_graph(fmess, bgraph, guard)
+        a_csr = Fn.csr_from_padded(agraph, fmess.shape[0], guard=guard)
+        guard.raise_if_bad()
         H = self.hidden_size
         F = self.W_o[0].in_features - H
         out = self.rnn.messages(fmess, mg, self.input_size, 1)
@@ -117,16 +128,19 @@ class MPNEncoder(nn.Module):
 class _TreeBatch:
     """Per-batch index structures shared by the attachment and motif layers."""
 
-    def __init__(self, tree_tensors):
+    def __init__(self, tree_tensors, guard=None):
         fnode, fmess, agraph, bgraph, cgraph, scope = tree_tensors
         self.n_nodes, self.n_mess = fnode.shape[0], fmess.shape[0]
         self.fnode = fnode
         self.cgraph = cgraph
-        self.a = Fn.csr_from_padded(agraph, self.n_mess)
-        self.mg = _message_graph(fmess, bgraph, self.n_nodes, MAX_POS)
+        self.a = Fn.csr_from_padded(agraph, self.n_mess, guard=guard)
+        self.mg = _message_graph(fmess, bgraph, self.n_nodes, MAX_POS, guard=guard)
         roots = getattr(scope, "roots_dev", None)
         if roots is None or roots.device != fnode.device:
-            roots = ints_to_device([st for st, le in scope], fnode.device)
+            starts = [st for st, le in scope]
+            if starts and not (0 <= min(starts) and max(starts) < self.n_nodes):
+                raise IndexError("malformed batch: scope start outside [0, %d)" % self.n_nodes)
+            roots = ints_to_device(starts, fnode.device)
         self.roots = roots
 
 
@@ -171,19 +185,22 @@ class HierMPNEncoder(nn.Module):
     def forward(self, tree_tensors, graph_tensors):
         H = self.hidden_size
         g_fnode, g_fmess, g_agraph, g_bgraph, _ = graph_tensors
-        tb = _TreeBatch(tree_tensors)
+        guard = Fn.IndexGuard(g_fnode.device)
+        tb = _TreeBatch(tree_tensors, guard)
 
         # atom layer: x_e = [E_a[atom(src_e)] | E_b[bond_e] | E_apos[pos_e]]  (embed_graph, :119-126)
         n_atoms, n_bonds = g_fnode.shape[0], g_fmess.shape[0]
         pad = (-self.atom_size) % 4                       # 16-byte rows: both uses below read it at this width
         atom_feat = nn.functional.pad(self.E_a, (0, pad)).index_select(0, g_fnode)
-        mg = _message_graph(g_fmess, g_bgraph, n_atoms, N_BOND_TYPES + MAX_POS, k2_offset=N_BOND_TYPES)
-        hatom, _, _ = self.graph_encoder.encode(atom_feat, atom_feat, mg, Fn.csr_from_padded(g_agraph, n_bonds),
-                                                self.atom_size, N_BOND_TYPES)
+        mg = _message_graph(g_fmess, g_bgraph, n_atoms, N_BOND_TYPES + MAX_POS, k2_offset=N_BOND_TYPES, guard=guard)
+        a_csr = Fn.csr_from_padded(g_agraph, n_bonds, guard=guard)
+        c_csr = Fn.csr_from_padded(tb.cgraph, n_atoms, guard=guard)
+        guard.raise_if_bad()                              # one read-back per forward, before any consumer of the ids runs
+        hatom, _, _ = self.graph_encoder.encode(atom_feat, atom_feat, mg, a_csr, self.atom_size, N_BOND_TYPES)
 
         # attachment layer (embed_inter, :96-107)
         attach_emb = _embed(self.E_i, tb.fnode[:, 1])
-        atoms_of_motif = Fn.gather_sum(hatom, Fn.csr_from_padded(tb.cgraph, n_atoms))
+        atoms_of_motif = Fn.gather_sum(hatom, c_csr)
         wi = self.W_i[0].weight
         E = attach_emb.shape[1]
         inter_feat = Fn.linear_act_split([attach_emb, atoms_of_motif], wi, [E, wi.shape[1] - E], self.W_i[0].bias,
@@ -227,7 +244,9 @@ class MotifEncoder(nn.Module):
 
     def forward(self, tree_tensors):
         H = self.hidden_size
-        tb = _TreeBatch(tree_tensors)
+        guard = Fn.IndexGuard(tree_tensors[0].device)
+        tb = _TreeBatch(tree_tensors, guard)
+        guard.raise_if_bad()
         motif_emb = _embed(self.E_c, tb.fnode[:, 0])         # node feature of the read-out (embed_tree, :305-317)
         attach_emb = _embed(self.E_i, tb.fnode[:, 1])        # feeds the message inputs
         node, _, incoming = self.tree_encoder.encode(motif_emb, attach_emb, tb.mg, tb.a, H, MAX_POS)
@@ -292,6 +311,25 @@ class IncMPNEncoder(MPNEncoder):
         return Fn.scatter_into_zeros(node_hiddens, subnode, num_nodes), h      # index_scatter into a zero node_buf
 
 
+def _check_tables_once(guard, tensors, n_mess_rows, n_atom_rows=None):
+    """range-check the neighbour tables of one batch the first time an incremental encoder sees them (they are the
+    same tensor objects for every decoder step of the batch; the row subsets taken from them per step go through
+    torch's own index_select, which asserts its indices): agraph / bgraph entries index the message state table
+    (n_mess_rows = its row count, appended per-molecule rows included), cgraph entries the atom table"""
+    fnode, fmess, agraph, bgraph = tensors[:4]
+    if getattr(bgraph, "_ggpm_checked", None) == (n_mess_rows, n_atom_rows):
+        return
+    for t, hi, what in ((agraph, n_mess_rows, "agraph"), (bgraph, n_mess_rows, "bgraph")):
+        if isinstance(t, torch.Tensor) and t.dtype in (torch.int32, torch.int64) and t.numel():
+            guard.check(t.reshape(-1), 0, hi, what)
+    if len(tensors) == 6 and n_atom_rows is not None and isinstance(tensors[4], torch.Tensor) and tensors[4].numel():
+        guard.check(tensors[4].reshape(-1), 0, n_atom_rows, "cgraph")
+    try:
+        bgraph._ggpm_checked = (n_mess_rows, n_atom_rows)
+    except Exception:
+        pass
+
+
 def _sub_tensors(tensors, subset):
     """rows of (fnode, fmess, agraph, bgraph[, cgraph]) selected by (subnode, submess) — ggpm/encoder.py:197-208"""
     subnode, submess = subset
@@ -352,6 +390,12 @@ class IncHierMPNEncoder(HierMPNEncoder):
     def forward(self, tree_tensors, inter_tensors, graph_tensors, htree, hinter, hgraph, subtree, subgraph):
         num_tree_nodes = tree_tensors[0].size(0)
         num_graph_nodes = graph_tensors[0].size(0)
+        guard = Fn.IndexGuard(tree_tensors[0].device)
+        rows = lambda state: self.graph_encoder.rnn.get_hidden_state(state).shape[0]
+        _check_tables_once(guard, graph_tensors, rows(hgraph.mess))
+        _check_tables_once(guard, inter_tensors, rows(hinter.mess), num_graph_nodes)
+        _check_tables_once(guard, tree_tensors, rows(htree.mess))
+        guard.raise_if_bad()                               # a read-back only on the first step of a batch
         if len(subgraph[0]) + len(subgraph[1]) > 0:
             sub_graph_tensors = _sub_tensors(graph_tensors, subgraph)[:-1]     # already embedded by embed_graph
             hgraph.node, hgraph.mess = self.graph_encoder(sub_graph_tensors, hgraph.mess, num_graph_nodes, subgraph)
@@ -384,6 +428,9 @@ class IncEncoder(MotifEncoder):
 
     def forward(self, tree_tensors, htree, subtree):
         num_tree_nodes = tree_tensors[0].size(0)
+        guard = Fn.IndexGuard(tree_tensors[0].device)
+        _check_tables_once(guard, tree_tensors, self.tree_encoder.rnn.get_hidden_state(htree.mess).shape[0])
+        guard.raise_if_bad()
         if len(subtree[0]) + len(subtree[1]) > 0:
             sub_tree_tensors = self.embed_sub_tree(tree_tensors, subtree)
             htree.node, htree.mess = self.tree_encoder(sub_tree_tensors, htree.mess, num_tree_nodes, subtree)

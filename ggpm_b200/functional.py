@@ -52,9 +52,63 @@ class CSR:
         return self._t
 
 
-def csr_from_padded(index: torch.Tensor, n_src: int, check: bool = False) -> CSR:
+class IndexGuard:
+    """Range validation of the index tensors of one batch on the make_cuda path (tensors that came through
+    ingest.PackedBatch were validated on the host when they were packed).  The reference's own index_select / embedding
+    calls raise on a bad label, position or node id; here the ids feed hand-written kernels, so they are checked first:
+    every check is one small kernel OR-ing a bit into one device flag, and `raise_if_bad()` reads the flag back ONCE
+    per forward, before any kernel that indexes with these ids is launched.  GGPM_SKIP_INDEX_CHECK=1 skips the checks
+    (and the read-back) for callers that validate their batches elsewhere."""
+
+    _skip = None
+
+    def __init__(self, device):
+        import os
+        if IndexGuard._skip is None:
+            IndexGuard._skip = os.environ.get("GGPM_SKIP_INDEX_CHECK", "0") == "1"
+        self.device = device
+        self.flag = None
+        self.names: List[str] = []
+
+    def _bit(self, what: str) -> int:
+        if self.flag is None:
+            self.flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        if what not in self.names:
+            self.names.append(what)
+        return 1 << min(self.names.index(what) + 1, 30)          # bit 0: neighbour entries (csr_from_padded)
+
+    def check(self, ids: torch.Tensor, lo: int, hi: int, what: str):
+        """ids: any int32 / int64 view with a single stride (1-D, e.g. a column of fmess)"""
+        if IndexGuard._skip or ids.numel() == 0:
+            return
+        _lib.require_device(ids, what)
+        if ids.dim() != 1 or ids.dtype not in (torch.int32, torch.int64):
+            raise ValueError("%s: expected a 1-D int32 / int64 id tensor" % what)
+        call("ggpm_check_ids", ids.data_ptr(), int(ids.dtype == torch.int64), ids.numel(), max(ids.stride(0), 1), lo, hi,
+             iptr(self._flag()), self._bit("%s outside [%d, %d)" % (what, lo, hi)), stream_ptr(ids.device))
+
+    def _flag(self):
+        if self.flag is None:
+            self.flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        return self.flag
+
+    def csr_flag(self):
+        return None if IndexGuard._skip else self._flag()
+
+    def raise_if_bad(self):
+        if self.flag is None or IndexGuard._skip:
+            return
+        bits = int(self.flag.item())
+        if bits:
+            bad = ["neighbour index outside its table"] if bits & 1 else []
+            bad += [n for i, n in enumerate(self.names) if bits & (1 << min(i + 1, 30))]
+            raise IndexError("malformed batch: " + "; ".join(bad))
+
+
+def csr_from_padded(index: torch.Tensor, n_src: int, check: bool = False, guard: Optional[IndexGuard] = None) -> CSR:
     """index: [rows, width] int64 (what make_cuda yields, ggpm/nnutils.py:210-214) or int32, on the GPU.
-    Tensors that came out of ingest.PackedBatch.to_device() carry their CSR (built on the host, same encoding)."""
+    Tensors that came out of ingest.PackedBatch.to_device() carry their CSR (built on the host, same encoding).
+    `guard`: entries outside [0, n_src) set bit 0 of the guard's flag (read back once per forward)."""
     pre = getattr(index, "_ggpm_csr", None)
     if pre is not None and pre.n_src == n_src and pre.row_ptr.device == index.device:
         return pre
@@ -72,7 +126,8 @@ def csr_from_padded(index: torch.Tensor, n_src: int, check: bool = False) -> CSR
     dev = index.device
     row_ptr = torch.empty(rows + 1, dtype=torch.int32, device=dev)
     col = torch.empty(max(1, rows * width), dtype=torch.int32, device=dev)
-    bad = torch.zeros(1, dtype=torch.int32, device=dev)
+    shared = None if guard is None else guard.csr_flag()
+    bad = torch.zeros(1, dtype=torch.int32, device=dev) if shared is None else shared
     call("ggpm_csr_from_padded", index.data_ptr(), int(index.dtype == torch.int64), rows, width, n_src,
          iptr(row_ptr), iptr(col), iptr(bad), stream_ptr(dev))
     if check and int(bad.item()) != 0:
@@ -493,18 +548,21 @@ class LSTMMessages(torch.autograd.Function):
         ctx.mg, ctx.depth, ctx.H, ctx.Hp = mg, depth, H, Hp
         ctx.hist = (hist_h, hist_c, hist_gp, Yn, hist_h16) if keep else None
         ctx.save_for_backward(phi_x, Wx, T, U4)
-        h, c = hist_h[h_last], hist_c[last]
-        ctx.mark_non_differentiable(c)
-        return h, c
+        # fresh tensors, not views of the history the backward pass reads: an in-place edit of a returned state by the
+        # caller must not be able to corrupt the saved activations (autograd's version counters do not cover ctx.hist)
+        return hist_h[h_last].clone(), hist_c[last].clone()
 
     @staticmethod
-    def backward(ctx, dh, _dc):
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, dh, dc):
         phi_x, Wx, T, U4 = ctx.saved_tensors
         mg, depth, H, Hp = ctx.mg, ctx.depth, ctx.H, ctx.Hp
         Ug, Uf = U4[:3 * Hp], U4[3 * Hp:]
         hist_h, hist_c, hist_gp, Yn, hist_h16 = ctx.hist
         E1, dev = mg.E1, Uf.device
-        dH = dh.clone(memory_format=torch.contiguous_format)
+        dH = (torch.zeros(E1, Hp, dtype=torch.float32, device=dev) if dh is None
+              else dh.clone(memory_format=torch.contiguous_format))
+        dCf = None if dc is None else dc.contiguous()       # gradient of the returned cell state (ggpm/rnn.py:108)
         z_planes = None if hist_h16 is None else torch.empty(2, E1, 4 * Hp, dtype=torch.float16, device=dev)
         dX = _empty(E1, 4 * Hp, device=dev)
         dU4 = torch.zeros(4 * Hp, Hp, dtype=torch.float32, device=dev)     # [dUg; dUf] contiguous (single-launch wgrad)
@@ -515,7 +573,8 @@ class LSTMMessages(torch.autograd.Function):
         bt = mg.b.T
         call("ggpm_lstm_bwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), iptr(bt.row_ptr), iptr(bt.col),
              fptr(Yn), iptr(mg.src), fptr(T), iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf),
-             fptr(hist_h), fptr(hist_c), fptr(hist_gp), fptr(dH), fptr(dX), fptr(dUg), fptr(dUf), fptr(dA), fptr(dC),
+             fptr(hist_h), fptr(hist_c), fptr(hist_gp), fptr(dH), None if dCf is None else fptr(dCf), fptr(dX), fptr(dUg),
+             fptr(dUf), fptr(dA), fptr(dC),
              fptr(dP), fptr(dS), fptr(S), fptr(dHn), fptr(_empty(2, Hp, 4 * Hp, device=dev)),
              None if hist_h16 is None else hist_h16.data_ptr(), None if z_planes is None else z_planes.data_ptr(),
              int(ctx.rotate), stream_ptr(dev))

@@ -30,6 +30,7 @@ import torch
 from . import functional as Fn
 
 N_BOND_TYPES = 4     # len(MolGraph.BOND_LIST), ggpm/mol_graph.py:14
+MAX_POS = 20         # MolGraph.MAX_POS, ggpm/mol_graph.py:15
 _ALIGN = 4           # int32 elements: every segment starts on a 16-byte boundary
 _MAGIC = b"GGPMPB01"
 
@@ -125,6 +126,15 @@ class PackedBatch:
         tree_scope = tree_tensors[5]
         lay = _Layout()
         n_tm = t_fmess.shape[0]
+
+        def in_range(col, hi, what):
+            # the ids below index tables inside the cell kernels; the reference's index_select raises on the same
+            # violations (ggpm/encoder.py:103-106, 114-116, 121-125).  Neighbour tables are checked by _add_csr.
+            col = np.asarray(col)
+            if col.size and (int(col.min()) < 0 or int(col.max()) >= hi):
+                raise IndexError("malformed batch: %s outside [0, %d)" % (what, hi))
+        in_range(t_fmess[:, 2], MAX_POS, "tree message position (fmess[:, 2])")
+        in_range([st for st, _ in tree_scope], t_fnode.shape[0], "scope start")
         lay.add("tree.fnode", t_fnode)
         lay.add("tree.fmess", t_fmess)
         lay.add("tree.agraph", t_agraph)
@@ -141,6 +151,8 @@ class PackedBatch:
             g_fnode, g_fmess, g_agraph, g_bgraph = [as_np(a) for a in graph_tensors[:4]]
             graph_scope = graph_tensors[4]
             n_gm = g_fmess.shape[0]
+            in_range(g_fmess[:, 2], N_BOND_TYPES, "bond type (fmess[:, 2])")
+            in_range(g_fmess[:, 3], MAX_POS, "bond position (fmess[:, 3])")
             lay.add("graph.fnode", g_fnode)
             lay.add("graph.fmess", g_fmess)
             lay.add("graph.agraph", g_agraph)

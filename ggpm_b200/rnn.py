@@ -16,13 +16,20 @@ from . import packing
 _STEP_PACKS = weakref.WeakKeyDictionary()      # module -> (key, packed operands), see _GraphRNN._packed_for_steps
 
 
-def _identity_graph(fmess: torch.Tensor, bgraph: torch.Tensor) -> Fn.MessageGraph:
-    """dense message inputs: every message is its own 'node', one table row carries the bias"""
+def _identity_graph(fmess: torch.Tensor, bgraph: torch.Tensor, guard=None) -> Fn.MessageGraph:
+    """dense message inputs: every message is its own 'node', one table row carries the bias.  Neighbour entries are
+    range-checked (Fn.IndexGuard; read back here unless the caller passes its own guard and reads it back itself)."""
     E1 = fmess.shape[0]
     dev = fmess.device
     src = torch.arange(E1, dtype=torch.int32, device=dev)
     k1 = torch.zeros(E1, dtype=torch.int32, device=dev)
-    return Fn.MessageGraph(Fn.csr_from_padded(bgraph, E1), src, k1, None, E1, 1)
+    own = guard is None
+    if own:
+        guard = Fn.IndexGuard(dev)
+    csr = Fn.csr_from_padded(bgraph, E1, guard=guard)
+    if own:
+        guard.raise_if_bad()
+    return Fn.MessageGraph(csr, src, k1, None, E1, 1)
 
 
 class _GraphRNN(nn.Module):

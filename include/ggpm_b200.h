@@ -56,9 +56,18 @@ int ggpm_prof_collect(double* ms, long long* count, double* work, int n_class);
  * MolGraph.tensorize_graph, ggpm/mol_graph.py:238-281) -> CSR of its non-zero entries in slot order.
  * idx: [rows, width] int64 (idx_is_64bit=1, the dtype make_cuda produces, ggpm/nnutils.py:210-214) or
  * int32.  row_ptr: [rows+1]; col: capacity rows*width; *bad_flag is set to 1 if an entry is outside
- * [0, n_src_rows).  nnz stays on the device (row_ptr[rows]). */
+ * [0, n_src_rows) (bit 0 is OR-ed in; such an entry is stored as 0, the padding id).  nnz stays on the device
+ * (row_ptr[rows]). */
 int ggpm_csr_from_padded(const void* idx, int idx_is_64bit, int rows, int width, int n_src_rows,
                          int32_t* row_ptr, int32_t* col, int32_t* bad_flag, void* stream);
+
+/* Range check of an id column before it reaches a kernel that indexes with it (the reference's index_select raises
+ * on a label >= table rows, a position >= MAX_POS or a source node >= n_nodes: ggpm/encoder.py:103-106,121-125;
+ * torch raises IndexError / a device assert).  ids: n entries at `stride` elements apart (a column of fmess),
+ * int64 or int32; *bad_flag |= bit if any entry is outside [lo, hi).  The caller zeroes the flag, may OR several
+ * checks into it with distinct bits, and reads it back once (no synchronisation in here). */
+int ggpm_check_ids(const void* ids, int ids_are_64bit, long long n, long long stride, long long lo, long long hi,
+                   int32_t* bad_flag, int bit, void* stream);
 
 /* Reverse CSR: for every source row n the destination rows that list it (t_row, ascending) and the
  * position of that entry in the forward `col` array (t_pos).  This is the deterministic form of the
@@ -193,7 +202,9 @@ int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const 
                   float* s_scratch, float* w_split, void* hist_h16, int keep_history, int h_rotate, void* stream);
 
 /* Back-propagation through time of the above (what autograd does for ggpm/rnn.py:96-108).
- * dH_final: [E1, Hp] gradient w.r.t. the final hidden state (consumed, used as scratch).
+ * dH_final: [E1, Hp] gradient w.r.t. the final hidden state (consumed, used as scratch); dC_final: [E1, Hp]
+ * gradient w.r.t. the final cell state, or NULL for zero (LSTM.forward returns (h, c), ggpm/rnn.py:108; the
+ * encoders only consume h).
  * Outputs: dX [E1, 4Hp] = accumulated gradient of the hoisted x-projection (zeroed here), dUg [3Hp, Hp] and
  * dUf [Hp, Hp] (accumulated into: caller zeroes).  bt_*: reverse CSR of (b_ptr, b_col).
  * Scratch: dA [E1, 4Hp], dC [2, E1, Hp], dP [E1, Hp], dS [E1, Hp], S [E1, Hp], dHn [E1, Hp];
@@ -201,9 +212,10 @@ int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const 
 int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                   const int32_t* bt_ptr, const int32_t* bt_row, const float* Yn, const int32_t* src,
                   const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
-                  const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final, float* dX,
-                  float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS, float* S, float* dHn,
-                  float* w_split, const void* hist_h16, void* z_planes, int h_rotate, void* stream);
+                  const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final,
+                  const float* dC_final, float* dX, float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS,
+                  float* S, float* dHn, float* w_split, const void* hist_h16, void* z_planes, int h_rotate,
+                  void* stream);
 
 /* Which optional buffers the two calls above will use under the current engine, so the caller can size them:
  * bit 0: f16x3 gate GEMMs; bit 1: fp16 h planes + Z planes (then hist_h may be 2 rotating slots: h_rotate = 1). */

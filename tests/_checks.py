@@ -291,3 +291,71 @@ def check_index_select_nd(device):
     got = nnutils.index_select_ND(src, 0, idx)
     assert torch.allclose(got, src[idx.reshape(-1)].reshape(3, 3, 8))
     assert torch.allclose(nnutils.index_select_sum(src, idx), (src[idx] * (idx != 0).unsqueeze(-1)).sum(1))
+
+
+def check_malformed_batches_raise(device):
+    """a bad label / position / source node / neighbour id must raise IndexError (as the reference's index_select
+    does) instead of reaching a kernel: on the make_cuda path through the device-side IndexGuard, on the ingest path
+    on the host when the batch is packed"""
+    from ggpm_b200 import ingest
+    meta, z, tree, graph = load_golden("hier_lstm_small")
+    model = build_model(meta, device)
+
+    def corrupt(which, col, value):
+        t, g = [x.clone() if isinstance(x, torch.Tensor) else x for x in tree], [x.clone() if isinstance(x, torch.Tensor) else x for x in graph]
+        tgt = (t if which[0] == "t" else g)[{"fmess": 1, "agraph": 2, "bgraph": 3, "cgraph": 4}[which[1:]]]
+        if col is None:
+            tgt[1, 0] = value
+        else:
+            tgt[1, col] = value
+        return t, g
+
+    cases = [("tfmess", 2, 20), ("tfmess", 0, tree[0].shape[0]), ("gfmess", 2, 4), ("gfmess", 3, 20), ("gfmess", 0, graph[0].shape[0]),
+             ("tbgraph", None, tree[1].shape[0]), ("gagraph", None, graph[1].shape[0]), ("tcgraph", None, graph[0].shape[0]),
+             ("gbgraph", None, -1)]
+    for which, col, value in cases:
+        t, g = corrupt(which, col, value)
+        with pytest.raises(IndexError):
+            model(to_dev(t, device), to_dev(g, device))
+        with pytest.raises(IndexError):
+            ingest.PackedBatch.from_tensors(t, g)
+    # the untouched batch still runs
+    model(to_dev(tree, device), to_dev(graph, device))
+
+
+def check_lstm_cell_state_gradient(device):
+    """LSTM.forward returns (h, c) as the reference does (ggpm/rnn.py:108): a loss on c must reach the parameters and
+    the inputs, and an in-place edit of the returned tensors must not corrupt the backward pass"""
+    meta, z, tree, graph = load_golden("motif_lstm_small")
+    H, IN, depth = 12, 9, 4
+    torch.manual_seed(4)
+    rnn = ggpm_b200.LSTM(IN, H, depth)
+    for p in rnn.parameters():
+        torch.nn.init.normal_(p, std=0.3)
+    rnn = rnn.to(device)
+    bgraph = tree[3]
+    E1 = tree[1].shape[0]
+    x = torch.randn(E1, IN)
+    ca, cb = torch.randn(E1, H), torch.randn(E1, H)
+    xd = x.clone().to(device).requires_grad_(True)
+    h, c = rnn(xd, bgraph.to(device))
+    loss = (h * ca.to(device)).sum() + (c * cb.to(device)).sum()
+    with torch.no_grad():          # the returned states are the caller's: scribbling on them must be harmless
+        h.zero_()
+        c.zero_()
+    loss.backward()
+    sd = {"rnn." + k: v.detach().cpu().double().requires_grad_(True) for k, v in rnn.state_dict().items()}
+    xo = x.clone().double().requires_grad_(True)
+    ho, co = eo.lstm_messages(sd, "rnn.", xo, bgraph, depth)
+    ((ho * ca.double()).sum() + (co * cb.double()).sum()).backward()
+    assert rel(xd.grad, xo.grad) <= TOL_GRAD, rel(xd.grad, xo.grad)
+    for k, p in rnn.named_parameters():
+        assert rel(p.grad, sd["rnn." + k].grad) <= TOL_GRAD, (k, rel(p.grad, sd["rnn." + k].grad))
+    # c alone
+    rnn.zero_grad(set_to_none=True)
+    rnn(x.to(device), bgraph.to(device))[1].sum().backward()
+    for v in sd.values():
+        v.grad = None
+    eo.lstm_messages(sd, "rnn.", x.double(), bgraph, depth)[1].sum().backward()
+    for k, p in rnn.named_parameters():
+        assert rel(p.grad, sd["rnn." + k].grad) <= TOL_GRAD, (k, rel(p.grad, sd["rnn." + k].grad))

@@ -76,12 +76,22 @@ class EmuLib:
         n = rows * width
         a = _arr(idx, n, ctypes.c_int64 if is64 else ctypes.c_int32, np.int64 if is64 else np.int32)
         index = torch.from_numpy(a.astype(np.int64)).reshape(rows, width)
-        if ((index < 0) | (index >= n_src)).any():
-            _i(bad, 1)[0] = 1
-            index = index.clamp(0, n_src - 1)
+        oob = (index < 0) | (index >= n_src)
+        if oob.any():
+            _i(bad, 1)[0] |= 1
+            index = index.masked_fill(oob, 0)
         rp, c = P.csr_from_padded(index)
         _i(row_ptr, rows + 1).copy_(rp.int())
         _i(col, len(c)).copy_(c.int())
+        return 0
+
+    def ggpm_check_ids(self, ids, is64, n, stride, lo, hi, bad, bit, stream):
+        self._tick("check_ids")
+        if n == 0:
+            return 0
+        a = _arr(ids, (n - 1) * stride + 1, ctypes.c_int64 if is64 else ctypes.c_int32, np.int64 if is64 else np.int32)[::stride]
+        if ((a < lo) | (a >= hi)).any():
+            _i(bad, 1)[0] |= bit
         return 0
 
     def ggpm_csr_transpose(self, row_ptr, col, rows, n_src, t_ptr, t_row, t_pos, cursor, stream):
@@ -318,7 +328,8 @@ class EmuLib:
         return 0
 
     def ggpm_lstm_bwd(self, E1, H, Hp, depth, b_ptr, b_col, bt_ptr, bt_row, Yn, src, T, k1, k2, Ug, Uf, hist_h,
-                      hist_c, hist_gp, dH_final, dX, dUg, dUf, dA, dC, dP, dS, S, dHn, w_split, hist_h16, z_planes, h_rotate, stream):
+                      hist_c, hist_gp, dH_final, dC_final, dX, dUg, dUf, dA, dC, dP, dS, S, dHn, w_split, hist_h16, z_planes,
+                      h_rotate, stream):
         self._tick("lstm_bwd")
         rp, col = _csr(b_ptr, b_col, E1)
         trp, tcol = _csr(bt_ptr, bt_row, E1)
@@ -333,7 +344,8 @@ class EmuLib:
         gp = _f(hist_gp, depth * E1 * 4 * Hp).view(depth, E1, 4 * Hp).to(DT)
         hist = dict(X=X, h=list(hh), c=list(hc), G=[None] + [gp[t][:, :3 * Hp] for t in range(1, depth)],
                     P=[None] + [gp[t][:, 3 * Hp:] for t in range(1, depth)])
-        dx, dug, duf = P.lstm_layer_bwd(hist, _tab(dH_final, E1, Hp, Hp).to(DT), ug, uf, rp, col, depth, H, Hp)
+        dx, dug, duf = P.lstm_layer_bwd(hist, _tab(dH_final, E1, Hp, Hp).to(DT), ug, uf, rp, col, depth, H, Hp,
+                                        dC_final=None if not dC_final else _tab(dC_final, E1, Hp, Hp).to(DT))
         _tab(dX, E1, 4 * Hp, 4 * Hp).copy_(dx.float())
         g = _tab(dUg, 3 * Hp, Hp, Hp)
         g.copy_((g.to(DT) + dug).float())

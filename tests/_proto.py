@@ -120,12 +120,12 @@ def lstm_cell_bwd(X, G, P_prev, c_prev, c_cur, dH, dC, row_ptr, col, H, Hp):
     return torch.cat([dai, dao, dau, daf_sum], 1), dP, dCp
 
 
-def lstm_layer_bwd(hist, dH_final, Ug, Uf, row_ptr, col, depth, H, Hp):
+def lstm_layer_bwd(hist, dH_final, Ug, Uf, row_ptr, col, depth, H, Hp, dC_final=None):
     """Returns dX [E1, 4Hp], dUg [3Hp, Hp], dUf [Hp, Hp]."""
     X = hist["X"]
     E1 = X.shape[0]
     dH = dH_final.clone()
-    dC = torch.zeros_like(dH)
+    dC = torch.zeros_like(dH) if dC_final is None else dC_final.clone()
     dX = torch.zeros_like(X)
     dUg = torch.zeros_like(Ug)
     dUf = torch.zeros_like(Uf)

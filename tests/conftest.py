@@ -5,6 +5,7 @@ import sys
 import numpy as np
 import pytest
 
+os.environ["GGPM_ALLOW_TEST_BACKEND"] = "1"      # the CPU tests route the C ABI to tests/_emu_lib.py (ggpm_b200/_lib.py seam)
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

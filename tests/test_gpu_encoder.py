@@ -53,6 +53,10 @@ def test_train_mode_parity_with_fixed_dropout_masks(name, p):
     C.check_fixed_mask_dropout_parity(name, DEV, p=p)
 
 
+def test_malformed_batches_raise_index_error():
+    C.check_malformed_batches_raise(DEV)
+
+
 def test_inputs_are_not_mutated():
     C.check_inputs_not_mutated(DEV)
 
@@ -60,6 +64,10 @@ def test_inputs_are_not_mutated():
 @pytest.mark.parametrize("rnn", ["LSTM", "GRU"])
 def test_mpn_encoder_reference_signature(engine, rnn):
     C.check_mpn_reference_signature(rnn, DEV)
+
+
+def test_lstm_cell_state_gradient(engine):
+    C.check_lstm_cell_state_gradient(DEV)
 
 
 def test_index_select_nd():

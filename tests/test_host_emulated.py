@@ -60,6 +60,10 @@ def test_train_mode_parity_with_fixed_dropout_masks(emu, name):
     C.check_fixed_mask_dropout_parity(name, DEV, p=0.1)
 
 
+def test_malformed_batches_raise_index_error(emu):
+    C.check_malformed_batches_raise(DEV)
+
+
 def test_inputs_are_not_mutated(emu):
     C.check_inputs_not_mutated(DEV)
 
@@ -67,6 +71,10 @@ def test_inputs_are_not_mutated(emu):
 @pytest.mark.parametrize("rnn", ["LSTM", "GRU"])
 def test_mpn_encoder_reference_signature(emu, rnn):
     C.check_mpn_reference_signature(rnn, DEV)
+
+
+def test_lstm_cell_state_gradient(emu):
+    C.check_lstm_cell_state_gradient(DEV)
 
 
 def test_index_select_nd(emu):
