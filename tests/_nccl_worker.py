@@ -41,9 +41,20 @@ def main():
         model.zero_grad(set_to_none=True)
         model(tree, graph)[0].sum().backward()
 
-    bucket = GradBucket(model.parameters())
-    grads_of(mine)
-    bucket.all_reduce_mean(weight=1.0 if mode == "equal" else float(len(mine)))
+    early = None
+    if mode == "equal":
+        # grouped, overlapped reduction: step 0 learns which parameters receive gradients, step 1 launches the early
+        # group's all-reduce on the side stream from the autograd hooks while the atom layer's backward still runs
+        bucket = GradBucket.for_encoder(model)
+        for _ in range(2):
+            bucket.arm()
+            grads_of(mine)
+            early = bool(bucket._launched[0])
+            bucket.all_reduce_mean()
+    else:
+        bucket = GradBucket(model.parameters())
+        grads_of(mine)
+        bucket.all_reduce_mean(weight=float(len(mine)))
     torch.cuda.synchronize()
     reduced = {k: p.grad.detach().clone() for k, p in model.named_parameters()}
     # every rank must hold the same reduced gradient
@@ -91,7 +102,7 @@ def main():
                 if e > worst:
                     worst, worst_key = e, k
         print(json.dumps({"mode": mode, "world": world, "same_on_all_ranks": bool(ok.item()), "worst_rel_err": worst,
-                          "worst_key": worst_key, "backend": dist.get_backend()}))
+                          "worst_key": worst_key, "backend": dist.get_backend(), "early_group_launched_in_backward": early}))
     dist.barrier()
     dist.destroy_process_group()
 

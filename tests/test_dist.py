@@ -51,10 +51,28 @@ def _worker(rank, world, port, weighted, out_dir):
     mols = synth.random_batch(77, 6, n_motif_vocab=50, n_attach_vocab=60)
     mine = mols[:2] if (weighted and rank == 0) else mols[2:] if weighted else [mols[i] for i in shard_batches(6, rank, world)]
     model = _model()
-    bucket = GradBucket(model.parameters())
-    _grads(model, mine)
-    assert model.tree_encoder.W_o[0].weight.grad is None            # root-only loss: contributes zeros to the bucket
-    bucket.all_reduce_mean(weight=float(len(mine)) if weighted else 1.0)
+    if weighted:
+        bucket = GradBucket(model.parameters())
+        _grads(model, mine)
+        assert model.tree_encoder.W_o[0].weight.grad is None        # root-only loss: contributes zeros to the bucket
+        bucket.all_reduce_mean(weight=float(len(mine)))
+    else:
+        # two groups (the atom layer last), early group launched from autograd hooks: the first step learns which
+        # parameters receive gradients and reduces everything at the end, the second launches the early group while
+        # the backward pass is still running
+        bucket = GradBucket.for_encoder(model)
+        assert len(bucket.bounds) == 2
+        for step in range(2):
+            bucket.arm()
+            _grads(model, mine)
+            early_launched = bucket._launched[0]
+            bucket.all_reduce_mean()
+            assert early_launched == (step == 1), (step, early_launched)
+        _grads(model, mine)                                          # an un-armed backward pass launches nothing
+        assert not any(bucket._launched) and not bucket._works
+        bucket.arm()
+        _grads(model, mine)
+        bucket.all_reduce_mean()
     torch.save({k: p.grad.clone() for k, p in model.named_parameters()}, os.path.join(out_dir, "rank%d.pt" % rank))
     dist.barrier()
     dist.destroy_process_group()

@@ -36,4 +36,6 @@ def test_nccl_reduced_gradients_equal_single_gpu_gradient_of_concatenated_batch(
         f.write(line + "\n")
     assert res["backend"] == "nccl" and res["world"] == 2
     assert res["same_on_all_ranks"]
+    if mode == "equal":
+        assert res["early_group_launched_in_backward"] is True
     assert res["worst_rel_err"] <= 1e-5, res
