@@ -21,6 +21,12 @@ the reference is defined bit-for-bit.  For train-mode parity the encoders take `
 ``nn.Dropout`` modules sit (E_i / E_c: ggpm/encoder.py:51-55,98,111; W_i / W_c: :60-72; W_o of each MPNEncoder:
 :15-19); tests install the same fixed multipliers in place of the product's dropout modules.
 
+ReLU kinks: ``relu`` (dict ``site -> 0/1 mask``) makes the five ReLU sites (W_i, W_c, W_o of each MPNEncoder) evaluate
+``pre * mask`` instead of ``relu(pre)``, i.e. the gradient of a PRESCRIBED linear branch; ``trace`` (dict) receives the
+pre-activations.  Full-size parity tests use it to compare gradients on the activation pattern the implementation
+under test actually took, and to prove that every unit whose pattern differs from the fp64 one sits on a kink
+(|pre-activation| at rounding level) — see tests/test_gpu_parity_full.py.
+
 PARITY PIN: the reference ships no tests or golden vectors for this path, so the pin
 is the reference itself executed in the build container: ``oracle/make_golden.py`` runs the
 unmodified reference modules from /root/reference (fp64 and fp32) on seeded inputs, asserts this
@@ -103,8 +109,16 @@ def _drop(drop, site: str, x: Tensor) -> Tensor:
     return x if not drop or site not in drop else x * drop[site].to(x.dtype)
 
 
+def _relu(pre: Tensor, site: str, relu=None, trace=None) -> Tensor:
+    if trace is not None:
+        trace[site] = pre.detach()
+    if relu is not None and site in relu:
+        return pre * relu[site].to(pre.dtype)
+    return torch.relu(pre)
+
+
 def mpn_layer(sd, prefix: str, rnn_type: str, fnode: Tensor, fmess: Tensor, agraph: Tensor,
-              bgraph: Tensor, depth: int, drop=None) -> Tuple[Tensor, Tensor]:
+              bgraph: Tensor, depth: int, drop=None, relu=None, trace=None) -> Tuple[Tensor, Tensor]:
     """ggpm/encoder.py:28-38: message RNN, messages->nodes sum, W_o + ReLU, row-0 mask."""
     if rnn_type == "LSTM":
         h, _ = lstm_messages(sd, prefix + "rnn.", fmess, bgraph, depth)
@@ -113,7 +127,7 @@ def mpn_layer(sd, prefix: str, rnn_type: str, fnode: Tensor, fmess: Tensor, agra
     else:
         raise ValueError("unsupported rnn cell type " + rnn_type)
     incoming = gather_padded(h, agraph).sum(1)
-    node = torch.relu(_affine(sd, prefix + "W_o.0", torch.cat([fnode, incoming], dim=-1)))
+    node = _relu(_affine(sd, prefix + "W_o.0", torch.cat([fnode, incoming], dim=-1)), prefix + "W_o", relu, trace)
     node = _drop(drop, prefix + "W_o", node)
     return node * _row0_mask(node.shape[0], node), h
 
@@ -131,7 +145,7 @@ def _root_vectors(sd, node_feat: Tensor, hmess: Tensor, agraph: Tensor, scope) -
 
 
 def hier_encoder(sd: Dict[str, Tensor], rnn_type: str, depthT: int, depthG: int,
-                 tree_tensors: Sequence, graph_tensors: Sequence, drop=None):
+                 tree_tensors: Sequence, graph_tensors: Sequence, drop=None, relu=None, trace=None):
     """HierMPNEncoder.forward, ggpm/encoder.py:140-157.  Index tensors are torch.long (make_cuda,
     ggpm/nnutils.py:210-214).  Returns (hroot, hnode, hinter, hatom)."""
     dtype = sd["W_root.0.weight"].dtype
@@ -144,29 +158,30 @@ def hier_encoder(sd: Dict[str, Tensor], rnn_type: str, depthT: int, depthG: int,
     bond_in = torch.cat([atom_feat.index_select(0, g_fmess[:, 0]),
                          _onehot(g_fmess[:, 2], N_BOND_TYPES, dtype),
                          _onehot(g_fmess[:, 3], MAX_POS, dtype)], dim=-1)
-    hatom, _ = mpn_layer(sd, "graph_encoder.", rnn_type, atom_feat, bond_in, g_agraph, g_bgraph, depthG, drop)
+    hatom, _ = mpn_layer(sd, "graph_encoder.", rnn_type, atom_feat, bond_in, g_agraph, g_bgraph, depthG, drop, relu, trace)
 
     # attachment layer (embed_inter, ggpm/encoder.py:96-107)
     attach_emb = _drop(drop, "E_i", sd["E_i.0.weight"].index_select(0, t_fnode[:, 1]))
     atoms_of_motif = gather_padded(hatom, t_cgraph).sum(1)
-    inter_feat = torch.relu(_affine(sd, "W_i.0", torch.cat([attach_emb, atoms_of_motif], dim=-1)))
+    inter_feat = _relu(_affine(sd, "W_i.0", torch.cat([attach_emb, atoms_of_motif], dim=-1)), "W_i", relu, trace)
     inter_feat = _drop(drop, "W_i", inter_feat)
     pos = _onehot(t_fmess[:, 2], MAX_POS, dtype)
     inter_in = torch.cat([inter_feat.index_select(0, t_fmess[:, 0]), pos], dim=-1)
-    hinter, _ = mpn_layer(sd, "inter_encoder.", rnn_type, inter_feat, inter_in, t_agraph, t_bgraph, depthT, drop)
+    hinter, _ = mpn_layer(sd, "inter_encoder.", rnn_type, inter_feat, inter_in, t_agraph, t_bgraph, depthT, drop, relu, trace)
 
     # motif layer (embed_tree, ggpm/encoder.py:109-117)
     motif_emb = _drop(drop, "E_c", sd["E_c.0.weight"].index_select(0, t_fnode[:, 0]))
-    tree_feat = torch.relu(_affine(sd, "W_c.0", torch.cat([motif_emb, hinter], dim=-1)))
+    tree_feat = _relu(_affine(sd, "W_c.0", torch.cat([motif_emb, hinter], dim=-1)), "W_c", relu, trace)
     tree_feat = _drop(drop, "W_c", tree_feat)
     tree_in = torch.cat([tree_feat.index_select(0, t_fmess[:, 0]), pos], dim=-1)
-    hnode, hmess = mpn_layer(sd, "tree_encoder.", rnn_type, tree_feat, tree_in, t_agraph, t_bgraph, depthT, drop)
+    hnode, hmess = mpn_layer(sd, "tree_encoder.", rnn_type, tree_feat, tree_in, t_agraph, t_bgraph, depthT, drop, relu, trace)
 
     hroot = _root_vectors(sd, tree_feat, hmess, t_agraph, t_scope)
     return hroot, hnode, hinter, hatom
 
 
-def motif_encoder(sd: Dict[str, Tensor], rnn_type: str, depthT: int, tree_tensors: Sequence, drop=None):
+def motif_encoder(sd: Dict[str, Tensor], rnn_type: str, depthT: int, tree_tensors: Sequence, drop=None, relu=None,
+                  trace=None):
     """MotifEncoder.forward, ggpm/encoder.py:330-341.  Returns (root, node)."""
     dtype = sd["W_root.0.weight"].dtype
     t_fnode, t_fmess, t_agraph, t_bgraph, _, t_scope = tree_tensors
@@ -174,7 +189,7 @@ def motif_encoder(sd: Dict[str, Tensor], rnn_type: str, depthT: int, tree_tensor
     attach_emb = _drop(drop, "E_i", sd["E_i.0.weight"].index_select(0, t_fnode[:, 1]))
     mess_in = torch.cat([attach_emb.index_select(0, t_fmess[:, 0]),
                          _onehot(t_fmess[:, 2], MAX_POS, dtype)], dim=-1)
-    node, hmess = mpn_layer(sd, "tree_encoder.", rnn_type, motif_emb, mess_in, t_agraph, t_bgraph, depthT, drop)
+    node, hmess = mpn_layer(sd, "tree_encoder.", rnn_type, motif_emb, mess_in, t_agraph, t_bgraph, depthT, drop, relu, trace)
     root = _root_vectors(sd, motif_emb, hmess, t_agraph, t_scope)
     return root, node
 

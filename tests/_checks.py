@@ -32,14 +32,21 @@ def grad_tolerance(gap32):
     return TOL_GRAD if gap32 is None else max(TOL_GRAD, 2.0 * gap32)
 
 
-def compare_with_oracle(test, names, outs, ref_outs, grads, ref_grads, ref_grads32=None):
-    """outputs at TOL_OUT; every parameter gradient at grad_tolerance(reference's own fp32 gap); everything recorded"""
+def compare_with_oracle(test, names, outs, ref_outs, grads, ref_grads, ref_grads32=None, ref_outs32=None, raise_on_bad=True,
+                        skip_outputs=False):
+    """outputs at TOL_OUT, every parameter gradient at TOL_GRAD — each relaxed to twice the reference's OWN fp32-vs-fp64
+    gap on that tensor where that gap was measured and is larger (grad_tolerance); everything recorded.  Returns the
+    list of violations when raise_on_bad is False."""
     bad = []
-    for n, a, b in zip(names, outs, ref_outs):
+    for i, (n, a, b) in enumerate(zip(names, outs, ref_outs)):
+        if skip_outputs:
+            break
         e = rel(a, b)
-        record(test, "out:" + n, e, TOL_OUT)
-        if e > TOL_OUT:
-            bad.append((n, e, TOL_OUT))
+        gap = None if ref_outs32 is None else rel(ref_outs32[i], b)
+        tol = grad_tolerance(gap)
+        record(test, "out:" + n, e, tol, ref_fp32_gap=gap)
+        if e > tol:
+            bad.append((n, e, tol))
     for k, g in ref_grads.items():
         if g is None or float(g.abs().max()) == 0.0:
             assert k not in grads or grads[k] is None or float(grads[k].abs().max()) == 0.0, k
@@ -51,7 +58,9 @@ def compare_with_oracle(test, names, outs, ref_outs, grads, ref_grads, ref_grads
         record(test, "grad:" + k, e, tol, ref_fp32_gap=gap)
         if e > tol:
             bad.append((k, e, tol))
-    assert not bad, bad
+    if raise_on_bad:
+        assert not bad, bad
+    return bad
 
 
 def build_model(meta, device, dropout=0.0):

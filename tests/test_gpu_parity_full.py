@@ -7,10 +7,19 @@ on the configurations the performance claims stand on — the comparisons VERDIC
   * MotifEncoder + the latent head at hidden 250, latent 24 (BASELINE config #5, the PropertyVAE encoder side);
   * the graph GRU end to end at hidden 250, depth 20.
 
-Bar: outputs and every parameter gradient within 1e-5 of max|ref| (north star).  The documented exception
-(tests/_checks.py `grad_tolerance`): where the REFERENCE's own fp32 evaluation misses its fp64 evaluation by more
-than 5e-6 on a tensor (a ReLU pre-activation within rounding of zero flips that unit's downstream gradient), that
-tensor is held to twice the measured reference gap.  Every measured value lands in gpurun_out/parity_report.json.
+Bar: outputs and every parameter gradient within 1e-5 of max|ref| (north star).  Two documented, MEASURED exceptions,
+both recorded in gpurun_out/parity_report.json:
+
+  * where the REFERENCE's own fp32 evaluation misses its fp64 evaluation by more than 5e-6 on a tensor, that tensor is
+    held to twice the measured reference gap (tests/_checks.py `grad_tolerance`; e.g. the GRU, whose state is an
+    unsquashed neighbour sum that grows with depth, ggpm/rnn.py:38);
+  * ReLU kinks.  At these sizes (10^5-10^6 ReLU units) a few pre-activations sit within fp32 rounding of zero, and
+    whichever side an evaluation lands on switches that unit's whole downstream gradient — the reference's own fp32 run
+    has the same property.  When the plain comparison fails, the test (1) reads the activation pattern the product took
+    (forward hooks on its five ReLU sites), (2) requires that every unit whose pattern differs from the fp64 oracle's
+    has an fp64 pre-activation below 1e-5 of the site's scale, and that there are at most 16 of them, and (3) re-runs
+    the fp64 oracle on the product's pattern (`relu=` of oracle/encoder_oracle.py: gradient of a prescribed linear
+    branch) and holds every gradient to 1e-5 against THAT.  A wrong kernel fails (2) or (3); a kink passes both.
 """
 import os
 import sys
@@ -33,17 +42,27 @@ def _as_long(ts):
     return [torch.from_numpy(np.asarray(t)).long() if not isinstance(t, list) else t for t in ts]
 
 
-def _oracle(kind, rnn, depthT, depthG, sd, tree_np, graph_np, dtype, loss):
-    """-> (outputs, {param: grad}) of the oracle at `dtype` for loss(outs)"""
+def _oracle(kind, rnn, depthT, depthG, sd, tree_np, graph_np, dtype, loss, relu=None):
+    """-> (outputs, {param: grad}, {site: pre-activation}) of the oracle at `dtype` for loss(outs)"""
     torch.set_num_threads(os.cpu_count() or 1)
     leaves = {k: v.to(dtype).requires_grad_(True) for k, v in sd.items()}
     tree, graph = _as_long(tree_np), _as_long(graph_np)
+    trace = {}
     if kind == "hier":
-        outs = eo.hier_encoder(leaves, rnn, depthT, depthG, tree, graph)
+        outs = eo.hier_encoder(leaves, rnn, depthT, depthG, tree, graph, relu=relu, trace=trace)
     else:
-        outs = eo.motif_encoder(leaves, rnn, depthT, tree)
+        outs = eo.motif_encoder(leaves, rnn, depthT, tree, relu=relu, trace=trace)
     loss(outs, leaves).backward()
-    return [o.detach() for o in outs], {k: v.grad for k, v in leaves.items()}
+    return [o.detach() for o in outs], {k: v.grad for k, v in leaves.items()}, trace
+
+
+def _relu_sites(model, kind):
+    """site name (oracle/encoder_oracle.py) -> the nn.Dropout module that receives that site's post-ReLU activations"""
+    sites = {"tree_encoder.W_o": model.tree_encoder.W_o[2]}
+    if kind == "hier":
+        sites.update({"W_i": model.W_i[2], "W_c": model.W_c[2], "inter_encoder.W_o": model.inter_encoder.W_o[2],
+                      "graph_encoder.W_o": model.graph_encoder.W_o[2]})
+    return sites
 
 
 def _product(kind, rnn, H, depthT, depthG, sd, mols, loss, extra_modules=None):
@@ -52,10 +71,16 @@ def _product(kind, rnn, H, depthT, depthG, sd, mols, loss, extra_modules=None):
     model.load_state_dict({k: v for k, v in sd.items() if k in model.state_dict()}, strict=True)
     model = model.cuda()
     tree, graph = ingest.pack(tensorize.tensorize(mols)).to_device("cuda")
+    masks, hooks = {}, []
+    for site, mod in _relu_sites(model, kind).items():
+        hooks.append(mod.register_forward_hook(
+            lambda m, inp, out, site=site: masks.__setitem__(site, (inp[0][:, :H] > 0).cpu())))
     outs = model(tree, graph) if kind == "hier" else model(tree)
+    for h in hooks:
+        h.remove()
     loss(outs, model).backward()
     torch.cuda.synchronize()
-    return [o.detach() for o in outs], {k: p.grad for k, p in model.named_parameters()}, (tree, graph)
+    return [o.detach() for o in outs], {k: p.grad for k, p in model.named_parameters()}, masks
 
 
 def _root_sum(outs, _):
@@ -76,12 +101,37 @@ def _compare(tag, kind, rnn, H, depth, B, seed, loss, min_atom_rows=0):
     tree_np, graph_np = synth.tensorize(mols)
     if min_atom_rows:
         assert graph_np[1].shape[0] >= min_atom_rows, "batch too small to cross the plane-fed threshold: %d rows" % graph_np[1].shape[0]
-    outs, grads, _ = _product(kind, rnn, H, depth, depth, sd, mols, loss)
-    ref_outs, ref_grads = _oracle(kind, rnn, depth, depth, sd, tree_np, graph_np, torch.float64, loss)
-    _, ref_grads32 = _oracle(kind, rnn, depth, depth, sd, tree_np, graph_np, torch.float32, loss)
+    outs, grads, masks = _product(kind, rnn, H, depth, depth, sd, mols, loss)
+    ref_outs, ref_grads, trace = _oracle(kind, rnn, depth, depth, sd, tree_np, graph_np, torch.float64, loss)
+    ref_outs32, ref_grads32, _ = _oracle(kind, rnn, depth, depth, sd, tree_np, graph_np, torch.float32, loss)
     for name, a in zip(C.OUT_NAMES[kind][1:], outs[1:]):
         assert float(a[0].abs().max()) == 0.0, name                  # row 0 of every node table is exactly zero
-    C.compare_with_oracle(tag, C.OUT_NAMES[kind], outs, ref_outs, grads, ref_grads, ref_grads32)
+    bad = C.compare_with_oracle(tag, C.OUT_NAMES[kind], outs, ref_outs, grads, ref_grads, ref_grads32, ref_outs32,
+                                raise_on_bad=False)
+    out_names = set(C.OUT_NAMES[kind])
+    assert not [b for b in bad if b[0] in out_names], bad             # outputs are continuous across a kink: no excuse
+    if bad:
+        _kink_analysis(tag, kind, rnn, depth, sd, tree_np, graph_np, loss, masks, trace, outs, ref_outs, grads, bad)
+
+
+def _kink_analysis(tag, kind, rnn, depth, sd, tree_np, graph_np, loss, masks, trace, outs, ref_outs, grads, bad):
+    """gradient mismatches must be explained by ReLU units sitting on a kink: see the module docstring"""
+    flips, worst_pre = 0, 0.0
+    for site, mask in masks.items():
+        pre = trace[site]
+        diff = mask != (pre > 0)
+        diff[0] = False                                               # row 0 is masked to zero after the ReLU anyway
+        n = int(diff.sum())
+        if n:
+            flips += n
+            worst_pre = max(worst_pre, float(pre[diff].abs().max() / pre.abs().max()))
+    C.record(tag, "kink:flipped_relu_units", flips, 16, max_flipped_preactivation_rel=worst_pre, first_mismatch=str(bad[0]))
+    assert 0 < flips <= 16, ("gradient mismatch without a ReLU pattern difference" if flips == 0 else "too many flips", flips, bad)
+    assert worst_pre <= 1e-5, ("a unit far from its kink took the other branch", worst_pre, bad)
+    _, branch_grads, _ = _oracle(kind, rnn, depth, depth, sd, tree_np, graph_np, torch.float64, loss,
+                                 relu={k: v.double() for k, v in masks.items()})
+    C.compare_with_oracle(tag + ":on_product_relu_pattern", C.OUT_NAMES[kind], outs, ref_outs, grads, branch_grads,
+                          skip_outputs=True)
 
 
 def test_hidden_500_depth_20_matches_fp64_oracle():
@@ -143,6 +193,6 @@ def test_cfg5_motif_encoder_plus_latent_head_matches_fp64_oracle():
         return [r.detach(), zz.detach(), kk.detach()], {k: v.grad for k, v in leaves.items()}
 
     ref_outs, ref_grads = oracle(torch.float64)
-    _, ref_grads32 = oracle(torch.float32)
+    ref_outs32, ref_grads32 = oracle(torch.float32)
     C.compare_with_oracle("full:cfg5_motif_latent_h250_l24_b256", ("hroot", "z", "kl"), [root.detach(), z.detach(), kl.detach()],
-                          ref_outs, grads, ref_grads, ref_grads32)
+                          ref_outs, grads, ref_grads, ref_grads32, ref_outs32)

@@ -71,13 +71,15 @@ def _batch(seed=31, n=6):
 
 def _wrapper_case(kind, device, tmp_path):
     ref = rl.load_reference()
-    ref.nnutils.device = torch.device(device)          # the reference's global device (ggpm/nnutils.py:9-10); one process per GPU
     pv, hp = rl.load_reference_module("property_vae"), rl.load_reference_module("hpgnn")
     cls_of = lambda: {"hier-prop": pv.HierPropertyVAE, "hier": hp.HierVAE, "prop": pv.PropertyVAE}[kind]
     args = _args()
 
-    # 1. the unpatched reference model: its state_dict is what checkpoints hold
+    # 1. the unpatched reference model (kept on the host: its one-hot tables are plain tensors placed at construction,
+    #    ggpm/encoder.py:74-77): its state_dict is what checkpoints hold
+    ref.nnutils.device = torch.device("cpu")
     ref_model = cls_of()(args)
+    ref.nnutils.device = torch.device(device)          # the reference's global device (ggpm/nnutils.py:9-10); one process per GPU
     assert type(ref_model.encoder).__module__ == "ggpm.encoder"
     _init(ref_model, 5)
     ref_sd = {k: v.detach().clone() for k, v in ref_model.state_dict().items()}
