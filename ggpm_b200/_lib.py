@@ -55,6 +55,8 @@ SIGNATURES = {
     "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
     "ggpm_rsample_fwd": (I, [P, I, I, P, I, I, I, P, I, P, P, P]),
     "ggpm_rsample_bwd": (I, [P, I, I, P, I, I, I, P, I, P, P, I, I, P]),
+    "ggpm_mlp_heads_fwd": (I, [P, I, I, I, I, I, I, P]),
+    "ggpm_mlp_heads_bwd": (I, [P, P, I, I, I, I, I, I, I, P]),
     "ggpm_rows_gather": (I, [P, I, P, I, I, I, I, P, I, P, I, P]),
     "ggpm_rows_scatter": (I, [P, I, P, I, I, P, I, P]),
     "ggpm_rows_scatter_add": (I, [P, I, P, I, I, I, P, I, P, I, P]),

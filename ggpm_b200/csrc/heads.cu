@@ -99,24 +99,27 @@ __global__ void __launch_bounds__(256) mlp_head_loss_kernel(HeadPair hp, int B) 
 }
 
 // dy_b = dout_b + dloss * 2 (y_b - t_b) / B ;  da = dy w2 mult [a > 0] ;  dW1 += da^T x, db1 += sum da, dw2 += sum dy a mult,
-// db2 += sum dy, dx = da W1
+// db2 += sum dy, dx = da W1.  Thread j owns hidden unit j: its weight-gradient row is accumulated in registers over the
+// block's rows and leaves the block as ONE atomicAdd per element.
+constexpr int kHeadBwdRows = 32;
 __global__ void __launch_bounds__(kHeadThreads)
 mlp_head_bwd_kernel(HeadPair hp, int B, int In, int Hd) {
     extern __shared__ float smem[];
     float* sW = smem;                              // [Hd][In]
-    float* sx = sW + Hd * In;                      // [kHeadRows][In]
-    float* sdy = sx + kHeadRows * In;              // [kHeadRows]
-    float* sdx = sdy + kHeadRows;                  // [kHeadRows][In] accumulated with shared atomics
+    float* sx = sW + Hd * In;                      // [kHeadBwdRows][In]
+    float* sdy = sx + kHeadBwdRows * In;           // [kHeadBwdRows]
+    float* sdx = sdy + kHeadBwdRows;               // [kHeadBwdRows][In] accumulated with shared atomics
     const HeadArgs& a = hp.h[blockIdx.y];
     const int tid = threadIdx.x;
-    const int r0 = blockIdx.x * kHeadRows;
+    const int r0 = blockIdx.x * kHeadBwdRows;
+    const int nr = min(kHeadBwdRows, B - r0);
     for (int i = tid; i < Hd * In; i += kHeadThreads) sW[i] = __ldg(a.W1 + i);
-    for (int i = tid; i < kHeadRows * In; i += kHeadThreads) {
+    for (int i = tid; i < kHeadBwdRows * In; i += kHeadThreads) {
         const int r = r0 + i / In;
         sx[i] = r < B ? a.x[(size_t)r * a.ldx + i % In] : 0.f;
         sdx[i] = 0.f;
     }
-    if (tid < kHeadRows) {
+    if (tid < kHeadBwdRows) {
         float dy = 0.f;
         const int r = r0 + tid;
         if (r < B) {
@@ -128,14 +131,17 @@ mlp_head_bwd_kernel(HeadPair hp, int B, int In, int Hd) {
     __syncthreads();
     if (tid == 0) {
         float s = 0.f;
-        for (int r = 0; r < kHeadRows; ++r) s += sdy[r];
+        for (int r = 0; r < nr; ++r) s += sdy[r];
         if (s != 0.f) atomicAdd(a.db2, s);
     }
     for (int j = tid; j < Hd; j += kHeadThreads) {
         const float wj = __ldg(a.w2 + j);
         const float* w = sW + j * In;
+        float gw[kHeadMaxIn];
+#pragma unroll
+        for (int k = 0; k < kHeadMaxIn; ++k) gw[k] = 0.f;
         float g2 = 0.f, g1 = 0.f;
-        for (int r = 0; r < kHeadRows && r0 + r < B; ++r) {
+        for (int r = 0; r < nr; ++r) {
             const float act = a.hid[(size_t)(r0 + r) * Hd + j];
             const float m = a.mult != nullptr ? a.mult[(size_t)(r0 + r) * a.ld_mult + j] : 1.f;
             const float dy = sdy[r];
@@ -143,18 +149,23 @@ mlp_head_bwd_kernel(HeadPair hp, int B, int In, int Hd) {
             const float da = act > 0.f ? dy * wj * m : 0.f;
             if (da != 0.f) {
                 g1 += da;
-                for (int k = 0; k < In; ++k) {
-                    atomicAdd(a.dW1 + (size_t)j * In + k, da * sx[r * In + k]);
-                    atomicAdd(sdx + r * In + k, da * w[k]);
-                }
+#pragma unroll
+                for (int k = 0; k < kHeadMaxIn; ++k)
+                    if (k < In) {
+                        gw[k] = fmaf(da, sx[r * In + k], gw[k]);
+                        atomicAdd(sdx + r * In + k, da * w[k]);
+                    }
             }
         }
+#pragma unroll
+        for (int k = 0; k < kHeadMaxIn; ++k)
+            if (k < In && gw[k] != 0.f) atomicAdd(a.dW1 + (size_t)j * In + k, gw[k]);
         if (g2 != 0.f) atomicAdd(a.dw2 + j, g2);
         if (g1 != 0.f) atomicAdd(a.db1 + j, g1);
     }
     __syncthreads();
     if (a.dx != nullptr)
-        for (int i = tid; i < kHeadRows * In; i += kHeadThreads) {
+        for (int i = tid; i < kHeadBwdRows * In; i += kHeadThreads) {
             const int r = r0 + i / In;
             if (r < B) a.dx[(size_t)r * a.ld_dx + i % In] = sdx[i];
         }
@@ -216,7 +227,7 @@ extern "C" int ggpm_mlp_heads_bwd(const void* const* ptrs, float* db2, int ldx0,
         GGPM_CUDA(cudaMemsetAsync(a.dw2, 0, sizeof(float) * (size_t)Hd, st));
     }
     GGPM_CUDA(cudaMemsetAsync(db2, 0, sizeof(float) * 2, st));
-    const size_t smem = sizeof(float) * ((size_t)Hd * In + 2 * kHeadRows * In + kHeadRows);
-    mlp_head_bwd_kernel<<<dim3(ceil_div(B, kHeadRows), 2), kHeadThreads, smem, st>>>(hp, B, In, Hd);
+    const size_t smem = sizeof(float) * ((size_t)Hd * In + 2 * kHeadBwdRows * In + kHeadBwdRows);
+    mlp_head_bwd_kernel<<<dim3(ceil_div(B, kHeadBwdRows), 2), kHeadThreads, smem, st>>>(hp, B, In, Hd);
     return check_launch("mlp_heads_bwd");
 }

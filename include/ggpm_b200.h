@@ -258,6 +258,18 @@ int ggpm_rsample_fwd(const float* Y, int ldy, int var_off, const float* eps, int
 int ggpm_rsample_bwd(const float* Y, int ldy, int var_off, const float* eps, int ld_eps, int B, int L, const float* dz,
                      int ld_dz, const float* dkl, float* dY, int ld_dy, int width, void* stream);
 
+/* ---- property heads behind the latent head ---------------------------------------------------
+ * PropertyOptimizer of ggpm/property_optimizer.py:5-51 in its shipped shape: two one-hidden-layer regressors (HOMO,
+ * LUMO; PropertyRegressor :54-66) on [B, In] inputs,  a = relu(W1 x + b1),  y = w2 . (a * mult) + b2,  loss = mean
+ * (y - t)^2, both heads in one launch.  ptrs: 2 x 17 device pointers, head 0 then head 1, each
+ *   {x [B, ldx], W1 [Hd, In], b1 [Hd], w2 [Hd], b2 [1], mult [B, ld_mult] | NULL (dropout multiplier), target [B] | NULL,
+ *    hid [B, Hd] (out: saved activations), out [B], sq [B] (scratch), loss [1],
+ *    dout [B] | NULL, dloss [1] | NULL, dx [B, ld_dx], dW1 [Hd, In], db1 [Hd], dw2 [Hd]}
+ * (the last six are used by the backward call only; db2 [2] is passed separately).  In <= 64, Hd * In <= 8192. */
+int ggpm_mlp_heads_fwd(const void* const* ptrs, int ldx0, int ldx1, int ld_mult, int B, int In, int Hd, void* stream);
+int ggpm_mlp_heads_bwd(const void* const* ptrs, float* db2, int ldx0, int ldx1, int ld_mult, int ld_dx, int B, int In, int Hd,
+                       void* stream);
+
 /* ---- incremental ("sparse") message passing of the decoder's encoder ---------------------
  * Replaces GRU.sparse_forward / LSTM.sparse_forward (ggpm/rnn.py:52-59, 110-121) and index_scatter
  * (ggpm/nnutils.py:124-128): M sub-messages of an R-row state table are recomputed for `depth` rounds, each round

@@ -198,6 +198,8 @@ class FixedDrop(torch.nn.Module):
     """stands in for an nn.Dropout of the model under test: multiplies by a fixed multiplier (mask / (1 - p)); the
     product carries node tables at a padded width, extra columns get multiplier 0"""
 
+    p = 0.5         # any non-zero rate: callers that ask a dropout module for its multiplier only skip p == 0
+
     def __init__(self, mult):
         super().__init__()
         self.mult = mult

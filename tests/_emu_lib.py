@@ -246,6 +246,50 @@ class EmuLib:
         _tab(dY, B, ld_dy, width).copy_(out.float())
         return 0
 
+    # -- property heads (csrc/heads.cu) -------------------------------------------------------------------------
+    @staticmethod
+    def _head(ptrs, h, ldx, ld_mult, B, In, Hd):
+        q = [ptrs[h * 17 + i] for i in range(17)]
+        d = dict(x=_tab(q[0], B, ldx, In), W1=_tab(q[1], Hd, In, In), b1=_f(q[2], Hd), w2=_f(q[3], Hd), b2=_f(q[4], 1),
+                 mult=None if not q[5] else _tab(q[5], B, ld_mult, Hd), target=None if not q[6] else _f(q[6], B),
+                 hid=_tab(q[7], B, Hd, Hd), out=_f(q[8], B), sq=None if not q[9] else _f(q[9], B),
+                 loss=None if not q[10] else _f(q[10], 1), dout=None if not q[11] else _f(q[11], B),
+                 dloss=None if not q[12] else _f(q[12], 1), q=q)
+        return d
+
+    def ggpm_mlp_heads_fwd(self, ptrs, ldx0, ldx1, ld_mult, B, In, Hd, stream):
+        self._tick("mlp_heads_fwd")
+        for h, ldx in ((0, ldx0), (1, ldx1)):
+            d = self._head(ptrs, h, ldx, ld_mult, B, In, Hd)
+            a = torch.relu(d["x"].to(DT) @ d["W1"].to(DT).t() + d["b1"].to(DT))
+            d["hid"].copy_(a.float())
+            am = a if d["mult"] is None else a * d["mult"].to(DT)
+            y = am @ d["w2"].to(DT) + d["b2"].to(DT)
+            d["out"].copy_(y.float())
+            if d["target"] is not None:
+                d["loss"].copy_(((y - d["target"].to(DT)) ** 2).mean().reshape(1).float())
+        return 0
+
+    def ggpm_mlp_heads_bwd(self, ptrs, db2, ldx0, ldx1, ld_mult, ld_dx, B, In, Hd, stream):
+        self._tick("mlp_heads_bwd")
+        for h, ldx in ((0, ldx0), (1, ldx1)):
+            d = self._head(ptrs, h, ldx, ld_mult, B, In, Hd)
+            q = d["q"]
+            dy = torch.zeros(B, dtype=DT)
+            if d["dout"] is not None:
+                dy += d["dout"].to(DT)
+            if d["dloss"] is not None and d["target"] is not None:
+                dy += d["dloss"].to(DT) * 2.0 * (d["out"].to(DT) - d["target"].to(DT)) / B
+            a = d["hid"].to(DT)
+            m = torch.ones_like(a) if d["mult"] is None else d["mult"].to(DT)
+            da = dy[:, None] * d["w2"].to(DT)[None, :] * m * (a > 0)
+            _tab(q[13], B, ld_dx, In).copy_((da @ d["W1"].to(DT)).float())
+            _tab(q[14], Hd, In, In).copy_((da.t() @ d["x"].to(DT)).float())
+            _f(q[15], Hd).copy_(da.sum(0).float())
+            _f(q[16], Hd).copy_(((a * m) * dy[:, None]).sum(0).float())
+            _f(db2, 2)[h] = float(dy.sum())
+        return 0
+
     def ggpm_embedding_bwd(self, dOut, ld, idx, is64, idx_stride, rows, width, n_tab, dW, ldw, stream):
         self._tick("embedding_bwd")
         n = (rows - 1) * idx_stride + 1 if rows > 0 else 0
