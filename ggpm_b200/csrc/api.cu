@@ -415,14 +415,15 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
 extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                              const int32_t* bt_ptr, const int32_t* bt_row, const float* Yn, const int32_t* src,
                              const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
-                             const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final,
-                             const float* dC_final, float* dX, float* dUg, float* dUf, float* dA, float* dC, float* dP,
+                             const float* hist_h, float* hist_c, float* hist_gp, float* dH_final,
+                             const float* dC_final, float* dX, float* dUg, float* dUf, float* dA_unused, float* dC, float* dP,
                              float* dS, float* S, float* dHn, float* w_split, const void* hist_h16, void* z_planes,
                              int h_rotate, void* stream) {
     GGPM_TRY(check_dims("lstm_bwd", E1, H, Hp, depth));
     GGPM_REQUIRE(b_ptr && b_col && bt_ptr && bt_row && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp &&
-                     dH_final && dX && dUg && dUf && dA && dC && dP && dS && S && dHn,
+                     dH_final && dX && dUg && dUf && dC && dP && dS && S && dHn,
                  "lstm_bwd: null pointer");
+    (void)dA_unused;   // round-1 ABI scratch: the gate gradients of a round now overwrite that round's slot of hist_gp
     cudaStream_t st = (cudaStream_t)stream;
     const size_t row = (size_t)E1 * Hp;
     const XTabArgs x{Yn, src, T, k1, k2};
@@ -430,7 +431,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     float* dH_next = dHn;
     const float* dC_cur = dC_final;  // dL/dc^depth (NULL: zero — the encoders consume only h)
     GGPM_REQUIRE(((uintptr_t)dC_final & 15) == 0, "lstm_bwd: dC_final must be 16-byte aligned");
-    const bool tc_ok = tc_layer_ok(Hp, {hist_h, hist_c, hist_gp, Ug, Uf, dUg, dUf, dA, dP, dH_final, dHn});
+    const bool tc_ok = tc_layer_ok(Hp, {hist_h, hist_c, hist_gp, Ug, Uf, dUg, dUf, dP, dH_final, dHn});
     const bool fused_w = tc_ok && Uf == Ug + (size_t)3 * Hp * Hp && dUf == dUg + (size_t)3 * Hp * Hp && Hp % 128 == 0;
     // state gradient dH = [..] [Ug; Uf]: the transposed weights [Hp, 4Hp] are split into tf32 planes once, then TMA-fed
     const size_t wn = (size_t)4 * Hp * Hp;
@@ -454,12 +455,12 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     SideStream* side = zmode ? side_stream() : nullptr;
     bool side_busy = false;                               // a weight-gradient GEMM may still be reading the Z planes
     for (int t = depth; t >= 1; --t) {
-        const float* c_cur = hist_c + (size_t)(t - 1) * row;
-        const float* gp = hist_gp + (size_t)(t - 1) * 4 * row;
-        const bool overwrite = (t == depth);
+        float* c_cur = hist_c + (size_t)(t - 1) * row;          // consumed: receives sum_n daf_en of the round
+        float* gp = hist_gp + (size_t)(t - 1) * 4 * row;        // consumed: [G_i|G_o|G_u] become [dai|dao|dau]
+        float* dA = gp;
         if (t == 1) {
-            GGPM_TRY(launch_lstm_cell_bwd(true, E1, H, Hp, b_ptr, b_col, x, nullptr, nullptr, c_cur, dH, dC_cur, dA, dX,
-                                          overwrite, nullptr, nullptr, nullptr, st));
+            GGPM_TRY(launch_lstm_cell_bwd(true, E1, H, Hp, b_ptr, b_col, x, gp, nullptr, c_cur, dH, dC_cur, nullptr, nullptr,
+                                          nullptr, st));
             break;
         }
         const float* h_prev = h_rotate ? nullptr : hist_h + (size_t)(t - 2) * row;     // only read without the plane path
@@ -468,8 +469,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
         GGPM_TRY(launch_zero2(dP, dC_prev, row, st));
         // the cell kernel also records max |gate-gradient term| of this round (16 slots): the scale of the f16x3 GEMM
         float* amax_t = f16 ? fw.scal + 16 + 16 * (size_t)t : nullptr;
-        GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_cur, dA, dX, overwrite,
-                                      dP, dC_prev, amax_t, st));
+        GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_cur, dP, dC_prev, amax_t, st));
         if (zmode) {
             // Z = [gather^T(dA[:, :3Hp]) | dP] as scaled fp16 planes; then dH^{t-1} = Z [Ug; Uf] and
             // [dUg; dUf] += Z^T h^{t-1}: two plain GEMMs whose operands all arrive by TMA
@@ -549,6 +549,8 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
         dC_cur = dC_prev;
     }
     if (side_busy) GGPM_CUDA(cudaStreamWaitEvent(st, side->join, 0));   // dUg / dUf complete for the caller's stream
+    // gradient of the hoisted x-projection: the per-round gate gradients, summed over the rounds in one streaming pass
+    GGPM_TRY(launch_lstm_dx_reduce(E1, Hp, depth, hist_gp, hist_c, dX, st));
     return 0;
 }
 

@@ -195,14 +195,19 @@ lstm_sgather_kernel(int E1, int Hp, const int* __restrict__ rp, const int* __res
 
 // ------------------------------------------------------------------------------------------------
 // LSTM backward cell (one round).  dP / dC_prev are accumulated with vector reductions (zeroed by caller).
+// The gate gradients of the round overwrite the round's saved pre-activations IN PLACE (gp: [G_i|G_o|G_u] of row e are
+// read, then [dai|dao|dau] written to the same words by the same thread; the P block, which other rows gather, is left
+// alone) and the forget-gate input gradient sum_n daf_en overwrites the round's saved cell state c_cur (read by this
+// thread only; neighbours gather the PREVIOUS slot).  Nothing is accumulated across rounds here: the sum over rounds
+// that the x-projection gradient needs is one streaming pass after the loop (lstm_dx_reduce_kernel), instead of a
+// read-modify-write of a [E, 4Hp] accumulator in every round (8 row-units of HBM traffic per message per round).
 // ------------------------------------------------------------------------------------------------
 template <bool FIRST>
 __global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
-                     const float* __restrict__ gp, const float* __restrict__ c_prev, const float* __restrict__ c_cur,
-                     const float* __restrict__ dH, const float* __restrict__ dC, float* __restrict__ dA,
-                     float* __restrict__ dX, int dx_overwrite, float* __restrict__ dP, float* __restrict__ dC_prev,
-                     float* __restrict__ amax16) {
+                     float* gp, const float* __restrict__ c_prev, float* c_cur,
+                     const float* __restrict__ dH, const float* __restrict__ dC, float* __restrict__ dP,
+                     float* __restrict__ dC_prev, float* __restrict__ amax16) {
     pdl_wait();
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
@@ -210,18 +215,15 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
     const int n_warps = (gridDim.x * blockDim.x) >> 5;
     float tmax = 0.f;      // max |dai|, |dao|, |dau|, |daf_en| seen by this thread (scale of the f16x3 state-gradient GEMM)
     for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < E1; e += n_warps) {
-    float* dAe = dA + (size_t)e * ld4h;
-    float* dXe = dX + (size_t)e * ld4h;
+    float* ge = gp + (size_t)e * ld4h;
+    float* ce = c_cur + (size_t)e * Hp;
     if (e == 0) {
-        for (int c = lane * 4; c < ld4h; c += 128) {
-            if (c < 3 * Hp) st4(dAe + c, f4zero());
-            if (dx_overwrite) st4(dXe + c, f4zero());
-        }
+        for (int c = lane * 4; c < 3 * Hp; c += 128) st4(ge + c, f4zero());
+        for (int c = lane * 4; c < Hp; c += 128) st4(ce + c, f4zero());
         continue;
     }
     const XRow xr = xrow(xt, e);
     const int b = FIRST ? 0 : __ldg(rp + e), en = FIRST ? 0 : __ldg(rp + e + 1);
-    const float* ge = gp + (size_t)e * ld4h;
     const float4 one = make_float4(1.f, 1.f, 1.f, 1.f);
     for (int c = lane * 4; c < Hp; c += 128) {
         float4 ai = xval(xr, c), ao = xval(xr, Hp + c), au = xval(xr, 2 * Hp + c);
@@ -231,7 +233,7 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
             au += ld4(ge + 2 * Hp + c);
         }
         const float4 gi = sigmoid4(ai), go = sigmoid4(ao), gu = tanh4(au);
-        const float4 th = tanh4(ld4(c_cur + (size_t)e * Hp + c));
+        const float4 th = tanh4(ld4(ce + c));
         const float4 dh = clip_cols(ld4(dH + (size_t)e * Hp + c), c, H);
         float4 dchat = dh * go * (one - th * th);
         if (dC) dchat += clip_cols(ld4(dC + (size_t)e * Hp + c), c, H);
@@ -253,26 +255,43 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
             }
         }
         tmax = fmaxf(tmax, fmaxf(amax4(dai), fmaxf(amax4(dao), amax4(dau))));
-        st4(dAe + c, dai);
-        st4(dAe + Hp + c, dao);
-        st4(dAe + 2 * Hp + c, dau);      // the forget block of dA has no reader (dP carries it): only dX gets dafs
-        if (dx_overwrite) {
-            st4(dXe + c, dai);
-            st4(dXe + Hp + c, dao);
-            st4(dXe + 2 * Hp + c, dau);
-            st4(dXe + 3 * Hp + c, dafs);
-        } else {
-            st4(dXe + c, ld4(dXe + c) + dai);
-            st4(dXe + Hp + c, ld4(dXe + Hp + c) + dao);
-            st4(dXe + 2 * Hp + c, ld4(dXe + 2 * Hp + c) + dau);
-            st4(dXe + 3 * Hp + c, ld4(dXe + 3 * Hp + c) + dafs);
-        }
+        st4(ge + c, dai);
+        st4(ge + Hp + c, dao);
+        st4(ge + 2 * Hp + c, dau);
+        st4(ce + c, dafs);
     }
     }
     if (amax16 != nullptr) {
         // non-negative floats order like their bit patterns
         const unsigned u = __reduce_max_sync(0xffffffffu, __float_as_uint(tmax));
         if (lane == 0 && u != 0) atomicMax(reinterpret_cast<unsigned*>(amax16) + (blockIdx.x & 15), u);
+    }
+}
+
+// dX[e] = [ sum_t dai_t | sum_t dao_t | sum_t dau_t | sum_t sum_n daf_en,t ](e): the gradient of the hoisted x-projection,
+// summed over the rounds in the order the backward loop produced them (t = depth first), one streaming pass.
+// hist_gp: [depth, E1, 4Hp] (gate-gradient blocks written by lstm_cell_bwd_kernel), hist_c: [depth, E1, Hp] (slots 1..
+// depth-1 hold the forget-gate sums; round 1 has no neighbours and contributes none).
+__global__ void __launch_bounds__(256)
+lstm_dx_reduce_kernel(int E1, int Hp, int depth, const float* __restrict__ hist_gp, const float* __restrict__ hist_c,
+                      float* __restrict__ dX) {
+    const int ld4h = 4 * Hp, q = ld4h >> 2;
+    const size_t n4 = (size_t)E1 * q;
+    const size_t gp_slot = (size_t)E1 * ld4h, c_slot = (size_t)E1 * Hp;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t e = i / q;
+        const int c = (int)(i % q) * 4;
+        float4 acc = f4zero();
+        if (c < 3 * Hp) {
+            const float* p = hist_gp + e * ld4h + c;
+            acc = ld4(p + (size_t)(depth - 1) * gp_slot);
+            for (int t = depth - 2; t >= 0; --t) acc += ld4(p + (size_t)t * gp_slot);
+        } else if (depth > 1) {
+            const float* p = hist_c + e * Hp + (c - 3 * Hp);
+            acc = ld4(p + (size_t)(depth - 1) * c_slot);
+            for (int t = depth - 2; t >= 1; --t) acc += ld4(p + (size_t)t * c_slot);
+        }
+        st4(dX + e * ld4h + c, acc);
     }
 }
 
@@ -551,14 +570,22 @@ int launch_lstm_sgather(int E1, int Hp, const int* b_ptr, const int* b_col, cons
 }
 
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
-                         const float* gp, const float* c_prev, const float* c_cur, const float* dH, const float* dC,
-                         float* dA, float* dX, bool dx_overwrite, float* dP, float* dC_prev, float* amax16,
-                         cudaStream_t st) {
+                         float* gp, const float* c_prev, float* c_cur, const float* dH, const float* dC,
+                         float* dP, float* dC_prev, float* amax16, cudaStream_t st) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_BWD, st, 0.0);
     launch_pdl(first ? lstm_cell_bwd_kernel<true> : lstm_cell_bwd_kernel<false>, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0,
-               st, E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dA, dX, (int)dx_overwrite, dP, dC_prev, amax16);
+               st, E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dP, dC_prev, amax16);
     return check_launch("lstm_cell_bwd");
+}
+
+int launch_lstm_dx_reduce(int E1, int Hp, int depth, const float* hist_gp, const float* hist_c, float* dX, cudaStream_t st) {
+    const size_t n4 = (size_t)E1 * Hp;
+    const size_t want = (n4 + 255) / 256;
+    const int blocks = (int)(want < (size_t)(16 * sm_count()) ? want : (size_t)(16 * sm_count()));
+    ProfScope prof(PROF_CELL_BWD, st, 0.0);
+    lstm_dx_reduce_kernel<<<blocks > 0 ? blocks : 1, 256, 0, st>>>(E1, Hp, depth, hist_gp, hist_c, dX);
+    return check_launch("lstm_dx_reduce");
 }
 
 int launch_gru_gate(int E1, int Hp, const int* rp, const int* col, const XTabArgs& x, const float* h_prev, float* aux,

@@ -78,9 +78,9 @@ int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const
                          const float* gp, const float* c_prev, float* h_out, float* c_out, void* h16_hi, void* h16_lo,
                          cudaStream_t st);
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
-                         const float* gp, const float* c_prev, const float* c_cur, const float* dH, const float* dC,
-                         float* dA, float* dX, bool dx_overwrite, float* dP, float* dC_prev, float* amax16,
-                         cudaStream_t st);
+                         float* gp, const float* c_prev, float* c_cur, const float* dH, const float* dC,
+                         float* dP, float* dC_prev, float* amax16, cudaStream_t st);
+int launch_lstm_dx_reduce(int E1, int Hp, int depth, const float* hist_gp, const float* hist_c, float* dX, cudaStream_t st);
 int launch_gru_gate(int E1, int Hp, const int* rp, const int* col, const XTabArgs& x, const float* h_prev, float* aux,
                     cudaStream_t st);
 int launch_gru_out(int E1, int H, int Hp, const XTabArgs& x, const float* aux, float* h_out, cudaStream_t st);

@@ -558,7 +558,11 @@ class LSTMMessages(torch.autograd.Function):
         phi_x, Wx, T, U4 = ctx.saved_tensors
         mg, depth, H, Hp = ctx.mg, ctx.depth, ctx.H, ctx.Hp
         Ug, Uf = U4[:3 * Hp], U4[3 * Hp:]
+        if ctx.hist is None:
+            raise RuntimeError("LSTMMessages: the saved activations were consumed by a previous backward pass "
+                               "(the library back-propagates in place; run the forward again)")
         hist_h, hist_c, hist_gp, Yn, hist_h16 = ctx.hist
+        ctx.hist = None
         E1, dev = mg.E1, Uf.device
         dH = (torch.zeros(E1, Hp, dtype=torch.float32, device=dev) if dh is None
               else dh.clone(memory_format=torch.contiguous_format))
@@ -567,14 +571,13 @@ class LSTMMessages(torch.autograd.Function):
         dX = _empty(E1, 4 * Hp, device=dev)
         dU4 = torch.zeros(4 * Hp, Hp, dtype=torch.float32, device=dev)     # [dUg; dUf] contiguous (single-launch wgrad)
         dUg, dUf = dU4[:3 * Hp], dU4[3 * Hp:]
-        dA = _empty(E1, 4 * Hp, device=dev)
         dC, dP, dS = _empty(2, E1, Hp, device=dev), _empty(E1, Hp, device=dev), _empty(E1, Hp, device=dev)
         S, dHn = _empty(E1, Hp, device=dev), _empty(E1, Hp, device=dev)
         bt = mg.b.T
         call("ggpm_lstm_bwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), iptr(bt.row_ptr), iptr(bt.col),
              fptr(Yn), iptr(mg.src), fptr(T), iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf),
              fptr(hist_h), fptr(hist_c), fptr(hist_gp), fptr(dH), None if dCf is None else fptr(dCf), fptr(dX), fptr(dUg),
-             fptr(dUf), fptr(dA), fptr(dC),
+             fptr(dUf), None, fptr(dC),
              fptr(dP), fptr(dS), fptr(S), fptr(dHn), fptr(_empty(2, Hp, 4 * Hp, device=dev)),
              None if hist_h16 is None else hist_h16.data_ptr(), None if z_planes is None else z_planes.data_ptr(),
              int(ctx.rotate), stream_ptr(dev))

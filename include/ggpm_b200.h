@@ -205,14 +205,17 @@ int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const 
  * dH_final: [E1, Hp] gradient w.r.t. the final hidden state (consumed, used as scratch); dC_final: [E1, Hp]
  * gradient w.r.t. the final cell state, or NULL for zero (LSTM.forward returns (h, c), ggpm/rnn.py:108; the
  * encoders only consume h).
- * Outputs: dX [E1, 4Hp] = accumulated gradient of the hoisted x-projection (zeroed here), dUg [3Hp, Hp] and
- * dUf [Hp, Hp] (accumulated into: caller zeroes).  bt_*: reverse CSR of (b_ptr, b_col).
- * Scratch: dA [E1, 4Hp], dC [2, E1, Hp], dP [E1, Hp], dS [E1, Hp], S [E1, Hp], dHn [E1, Hp];
+ * Outputs: dX [E1, 4Hp] = gradient of the hoisted x-projection summed over the rounds (written once, after the
+ * loop), dUg [3Hp, Hp] and dUf [Hp, Hp] (accumulated into: caller zeroes).  bt_*: reverse CSR of (b_ptr, b_col).
+ * hist_gp and hist_c are CONSUMED: every round's gate gradients overwrite that round's [G_i|G_o|G_u] block of hist_gp
+ * and its forget-gate input gradient overwrites that round's slot of hist_c (each is dead once its round has been
+ * back-propagated), so no [E1, 4Hp] accumulator is read and re-written per round; a second call needs a new forward.
+ * Scratch: dA (unused since round 2, may be NULL), dC [2, E1, Hp], dP [E1, Hp], dS [E1, Hp], S [E1, Hp], dHn [E1, Hp];
  * w_split: optional [2, Hp, 4Hp] (may be NULL) for the tf32 planes of [Ug; Uf]^T streamed by TMA. */
 int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
                   const int32_t* bt_ptr, const int32_t* bt_row, const float* Yn, const int32_t* src,
                   const float* T, const int32_t* k1, const int32_t* k2, const float* Ug, const float* Uf,
-                  const float* hist_h, const float* hist_c, const float* hist_gp, float* dH_final,
+                  const float* hist_h, float* hist_c, float* hist_gp, float* dH_final,
                   const float* dC_final, float* dX, float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS,
                   float* S, float* dHn, float* w_split, const void* hist_h16, void* z_planes, int h_rotate,
                   void* stream);
