@@ -376,6 +376,8 @@ def run_ours(args, workload):
     if workload["batch"] >= 4096:
         n_batches = min(n_batches, 2)
     n_batches = workload.get("pool", n_batches)
+    if args.pool:
+        n_batches = args.pool
     batches = make_batches(workload, n_batches, seed=rank + 1)
     # resident inputs of the device-timed arm: the batch in the ingest format (index tensors + the CSR / reverse CSR the
     # host prepared), already in HBM; --resident make_cuda keeps the reference's int64 tensors instead (index structures
@@ -684,6 +686,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--resident", default="packed", choices=["packed", "make_cuda"],
                     help="format of the HBM-resident inputs of the device-timed arm")
+    ap.add_argument("--pool", type=int, default=0, help="number of distinct batches per rank (profiling runs: 2 starts faster)")
     ap.add_argument("--profile-step", action="store_true",
                     help="run one extra step between cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     args = ap.parse_args()

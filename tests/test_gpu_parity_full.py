@@ -45,7 +45,7 @@ def _as_long(ts):
 def _oracle(kind, rnn, depthT, depthG, sd, tree_np, graph_np, dtype, loss, relu=None):
     """-> (outputs, {param: grad}, {site: pre-activation}) of the oracle at `dtype` for loss(outs)"""
     torch.set_num_threads(os.cpu_count() or 1)
-    leaves = {k: v.to(dtype).requires_grad_(True) for k, v in sd.items()}
+    leaves = {k: v.detach().clone().to(dtype).requires_grad_(True) for k, v in sd.items()}
     tree, graph = _as_long(tree_np), _as_long(graph_np)
     trace = {}
     if kind == "hier":
@@ -185,7 +185,7 @@ def test_cfg5_motif_encoder_plus_latent_head_matches_fp64_oracle():
 
     def oracle(dtype):
         torch.set_num_threads(os.cpu_count() or 1)
-        leaves = {k: v.to(dtype).requires_grad_(True) for k, v in {**sd, **lat}.items()}
+        leaves = {k: v.detach().clone().to(dtype).requires_grad_(True) for k, v in {**sd, **lat}.items()}
         r = eo.motif_encoder(leaves, "LSTM", depth, _as_long(tree_np))[0]
         zz, kk = lo.rsample(r, leaves["R_mean.weight"], leaves["R_mean.bias"], leaves["R_var.weight"],
                             leaves["R_var.bias"], eps.to(dtype), True)
