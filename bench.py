@@ -2,7 +2,7 @@
 """Benchmark of the hierarchical message-passing encoder hot path (BASELINE.json metric:
 "HierMPN encoder molecules/sec (fwd+bwd)").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg1|cfg2|cfg3s|cfg3|cfg4|cfg5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg1|cfg2|cfg3s|cfg3|cfg4|cfg5|cfg5h]
 
 One step = HierMPNEncoder forward + backward (loss = hroot.sum(), the only output the VAEs consume,
 ggpm/property_vae.py:50) over one synthetic batch.  The default workload is BASELINE config #4, the one the
@@ -58,6 +58,9 @@ WORKLOADS = {
     "cfg5": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256, encoder="motif", latent=24,
                  desc="PropertyVAE encoder side of one pre-training step: MotifEncoder + R_mean/R_var rsample/KL "
                       "(ggpm/property_vae.py:79-99), batch 256 per GPU, decoder excluded"),
+    "cfg5h": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256, latent=24,
+                  desc="HierPropertyVAE ('hier-prop', ggpm/opvnet.py:7) encoder side of one pre-training step: HierMPNEncoder + "
+                       "R_mean/R_var rsample/KL (ggpm/property_vae.py:48-52), batch 256 per GPU, decoder excluded"),
 }
 METRIC = "HierMPN encoder molecules/sec (fwd+bwd)"
 UNIT = "molecules/s"
@@ -234,7 +237,7 @@ def _reference_step_fn(workload, sample_mols):
         cls = ref.encoder.MotifEncoder if motif else ref.encoder.HierMPNEncoder
         model = cls(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H, workload["depthT"],
                     workload["depthG"], workload["dropout"])
-        if motif:
+        if L:
             model.R_mean, model.R_var = torch.nn.Linear(H, L), torch.nn.Linear(H, L)
         for p in model.parameters():                       # vae_train.py:49-53
             if p.dim() == 1:
@@ -245,8 +248,8 @@ def _reference_step_fn(workload, sample_mols):
 
         def step():
             model.zero_grad(set_to_none=True)
-            if motif:      # PropertyVAE.forward's encoder side (ggpm/property_vae.py:95-99): encoder + rsample / KL
-                root = model(tree)[0]
+            if L:          # (Hier)PropertyVAE.forward's encoder side (ggpm/property_vae.py:48-52, 95-99): encoder + rsample / KL
+                root = model(tree)[0] if motif else model(tree, graph)[0]
                 z_mean = model.R_mean(root)
                 z_log_var = -torch.abs(model.R_var(root))
                 kl = -0.5 * torch.sum(1.0 + z_log_var - z_mean * z_mean - torch.exp(z_log_var)) / root.size(0)
@@ -259,7 +262,7 @@ def _reference_step_fn(workload, sample_mols):
     from oracle import encoder_oracle as eo
     sd = {k: v.requires_grad_(True)
           for k, v in eo.random_state("motif" if motif else "hier", "LSTM", H, H, 0, bias_std=0.0).items()}
-    if motif:
+    if L:
         from oracle import latent_oracle as lo
         lat = [torch.randn(L, H) / H ** 0.5, torch.zeros(L), torch.randn(L, H) / H ** 0.5, torch.zeros(L)]
         lat = [t.requires_grad_(True) for t in lat]
@@ -267,8 +270,9 @@ def _reference_step_fn(workload, sample_mols):
     def step():
         for v in sd.values():
             v.grad = None
-        if motif:
-            root = eo.motif_encoder(sd, "LSTM", workload["depthT"], tree)[0]
+        if L:
+            root = (eo.motif_encoder(sd, "LSTM", workload["depthT"], tree)[0] if motif else
+                    eo.hier_encoder(sd, "LSTM", workload["depthT"], workload["depthG"], tree, graph)[0])
             z, kl = lo.rsample(root, *lat, torch.randn(root.shape[0], L), True)
             (z.sum() + kl).backward()
         else:
@@ -361,7 +365,7 @@ def run_ours(args, workload):
     enc_cls = ggpm_b200.MotifEncoder if motif else ggpm_b200.HierMPNEncoder
     model = enc_cls(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H,
                     workload["depthT"], workload["depthG"], workload["dropout"])
-    if motif:                             # PropertyVAE keeps the latent head next to the encoder (property_vae.py:86-87)
+    if workload.get("latent"):            # the VAEs keep the latent head next to the encoder (property_vae.py:23-24, 86-87)
         model.R_mean = torch.nn.Linear(H, workload["latent"])
         model.R_var = torch.nn.Linear(H, workload["latent"])
     for p in model.parameters():          # vae_train.py:49-53
@@ -393,8 +397,9 @@ def run_ours(args, workload):
     from ggpm_b200 import latent as latent_head
 
     def forward_loss(tree, graph):
-        if motif:        # MotifEncoder -> rsample -> (z, KL): the encoder side of PropertyVAE.forward (property_vae.py:95-99)
-            z, kl = latent_head.rsample(model(tree)[0], model.R_mean, model.R_var, True)
+        if workload.get("latent"):     # encoder -> rsample -> (z, KL): the encoder side of (Hier)PropertyVAE.forward
+            root = model(tree)[0] if motif else model(tree, graph)[0]
+            z, kl = latent_head.rsample(root, model.R_mean, model.R_var, True)
             return z.sum() + kl
         return model(tree, graph)[0].sum()
 

@@ -346,6 +346,10 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
     }
     const bool h16 = f16 && keep_history && hist_h16 != nullptr && ((uintptr_t)hist_h16 & 15) == 0;
     GGPM_REQUIRE(!h_rotate || !keep_history || h16, "lstm_fwd: a rotating hist_h needs the fp16 h planes (ggpm_lstm_plan bit 1)");
+    // large layers (the plane-fed path below) read h^{t-1} only through its fp16 planes: the fp32 copy is written by the
+    // last round alone (it is what the call returns)
+    const bool planes_only = f16 && h16 && E1 >= sgather_min_rows() && Hp % 64 == 0 && ((uintptr_t)s_scratch & 15) == 0 &&
+                             fused_w && tc_ok;
     for (int t = 1; t <= depth; ++t) {
         const int cur = keep_history ? (t - 1) : ((t - 1) & 1);
         const int prev = keep_history ? (t - 2) : ((t - 2) & 1);
@@ -355,8 +359,9 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
         // fp16 planes of h^t (2 bytes per element): [cur][hi | lo][E1 * Hp]
         char* h16_hi = h16 ? (char*)hist_h16 + (size_t)cur * 4 * row : nullptr;
         char* h16_lo = h16 ? h16_hi + 2 * row : nullptr;
+        float* h_out = (planes_only && t < depth) ? nullptr : h_cur;
         if (t == 1) {
-            GGPM_TRY(launch_lstm_cell_fwd(true, E1, H, Hp, b_ptr, b_col, x, nullptr, nullptr, h_cur, c_cur, h16_hi, h16_lo, st));
+            GGPM_TRY(launch_lstm_cell_fwd(true, E1, H, Hp, b_ptr, b_col, x, nullptr, nullptr, h_out, c_cur, h16_hi, h16_lo, st));
             continue;
         }
         const float* h_prev = hist_h + (h_rotate ? (prev & 1) : prev) * row;
@@ -369,21 +374,21 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
             g.M = E1; g.K = Hp; g.a_row_ptr = b_ptr; g.a_col = b_col;
             if (fused_w) {   // one launch: columns >= 3Hp (the forget projection) read h_prev un-gathered
                 g.N = 4 * Hp; g.split_dim = 1; g.split_at = 3 * Hp;
-                if (f16 && h16 && t >= 2 && E1 >= sgather_min_rows() && Hp % 64 == 0 && ((uintptr_t)s_scratch & 15) == 0) {
+                if (planes_only) {
                     // large layer: S as fp16 planes from one gather kernel (s_scratch holds both planes), then two GEMMs
                     // whose operands all arrive by TMA: [G_i|G_o|G_u] = S Ug^T and P = h^{t-1} Uf^T from the saved h planes
                     char* s_hi = (char*)s_scratch;
                     char* s_lo = s_hi + 2 * row;
                     float* s_scale = fw.scal + 5;
-                    GGPM_TRY(launch_lstm_sgather(E1, Hp, b_ptr, b_col, h_prev, reinterpret_cast<const int*>(fw.scal + 2), s_hi,
-                                                 s_lo, s_scale, st));
+                    const char* hp_hi = (const char*)hist_h16 + (size_t)prev * 4 * row;
+                    GGPM_TRY(launch_lstm_sgather16(E1, Hp, b_ptr, b_col, hp_hi, hp_hi + 2 * row,
+                                                   reinterpret_cast<const int*>(fw.scal + 2), s_hi, s_lo, s_scale, st));
                     GemmArgs a;
                     a.Ah_hi = s_hi; a.Ah_lo = s_lo; a.lda_h = Hp; a.a_scale = s_scale;
                     a.Bh_hi = fw.hi; a.Bh_lo = fw.lo; a.sbn = Hp; a.b_scale = fw.scal + 1;
                     a.C = gp; a.ldc = 4 * Hp; a.M = E1; a.N = 3 * Hp; a.K = Hp;
                     GGPM_TRY(launch_gemm_f16(a, st));
                     GemmArgs q;
-                    const char* hp_hi = (const char*)hist_h16 + (size_t)prev * 4 * row;
                     q.Ah_hi = hp_hi; q.Ah_lo = hp_hi + 2 * row; q.lda_h = Hp; q.a_scale = fw.scal + 6;      // = 2^13
                     q.Bh_hi = (const char*)fw.hi + (size_t)3 * Hp * Hp * 2; q.Bh_lo = (const char*)fw.lo + (size_t)3 * Hp * Hp * 2;
                     q.sbn = Hp; q.b_scale = fw.scal + 1;
@@ -407,7 +412,7 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
             GGPM_TRY(gemm_nt(s_scratch, Hp, Ug, Hp, gp, 4 * Hp, E1, 3 * Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
             GGPM_TRY(gemm_nt(h_prev, Hp, Uf, Hp, gp + 3 * Hp, 4 * Hp, E1, Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
         }
-        GGPM_TRY(launch_lstm_cell_fwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, h_cur, c_cur, h16_hi, h16_lo, st));
+        GGPM_TRY(launch_lstm_cell_fwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, h_out, c_cur, h16_hi, h16_lo, st));
     }
     return 0;
 }

@@ -56,7 +56,7 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
     for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < E1; e += n_warps) {
     if (e == 0) {   // padding row: forced to zero after every round (ggpm/rnn.py:106-107)
         for (int c = lane * 4; c < Hp; c += 128) {
-            st4(h_out + c, f4zero());
+            if (h_out) st4(h_out + c, f4zero());
             st4(c_out + c, f4zero());
             if (h16_hi) { h16_hi[c >> 2] = make_uint2(0u, 0u); h16_lo[c >> 2] = make_uint2(0u, 0u); }
         }
@@ -94,7 +94,7 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
         chat = clip_cols(chat, c, H);
         float4 h = clip_cols(sigmoid4(ao) * tanh4(chat), c, H);
         st4(c_out + (size_t)e * Hp + c, chat);
-        st4(h_out + (size_t)e * Hp + c, h);
+        if (h_out) st4(h_out + (size_t)e * Hp + c, h);      // large layers read h through the fp16 planes below only
         if (h16_hi) {   // fp16 hi / lo planes of h * 2^13 (|h| <= 1): the B operand of the f16x3 weight-gradient GEMM
             uint2 hi, lo;
             tc::split2_f16(h.x * kH16Scale, h.y * kH16Scale, hi.x, lo.x);
@@ -187,6 +187,52 @@ lstm_sgather_kernel(int E1, int Hp, const int* __restrict__ rp, const int* __res
             }
             uint4 hi, lo;
             tc::split8_f16(a0, a1, s, hi, lo);
+            s_hi[((size_t)e * Hp + c) >> 3] = hi;
+            s_lo[((size_t)e * Hp + c) >> 3] = lo;
+        }
+    }
+}
+
+// The same from the fp16 hi / lo planes of h^{t-1} * 2^13 that the forward cell kernel saves anyway (the operands of the
+// forget-projection and weight-gradient GEMMs): large layers then never write or read an fp32 copy of h between rounds.
+__device__ __forceinline__ void add_h16(uint4 hi, uint4 lo, float4& a0, float4& a1) {
+    const __half2* ph = reinterpret_cast<const __half2*>(&hi);
+    const __half2* pl = reinterpret_cast<const __half2*>(&lo);
+    const float2 h0 = __half22float2(ph[0]), h1 = __half22float2(ph[1]), h2 = __half22float2(ph[2]), h3 = __half22float2(ph[3]);
+    const float2 l0 = __half22float2(pl[0]), l1 = __half22float2(pl[1]), l2 = __half22float2(pl[2]), l3 = __half22float2(pl[3]);
+    a0.x += h0.x + l0.x; a0.y += h0.y + l0.y; a0.z += h1.x + l1.x; a0.w += h1.y + l1.y;
+    a1.x += h2.x + l2.x; a1.y += h2.y + l2.y; a1.z += h3.x + l3.x; a1.w += h3.y + l3.y;
+}
+
+__global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
+lstm_sgather16_kernel(int E1, int Hp, const int* __restrict__ rp, const int* __restrict__ col,
+                      const uint4* __restrict__ h_hi, const uint4* __restrict__ h_lo, const int* __restrict__ deg,
+                      uint4* __restrict__ s_hi, uint4* __restrict__ s_lo, float* __restrict__ scale_out) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31;
+    // the planes hold h * 2^13: the sum of <= deg rows is scaled so that deg * 2^13 lands in [2^13, 2^14)
+    const float s = tc::pow2_scale((float)max(1, __ldg(deg)));
+    const float s_in = s / kH16Scale;                 // planes -> S * s
+    if (blockIdx.x == 0 && threadIdx.x == 0) *scale_out = s;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < E1; e += n_warps) {
+        const int b = __ldg(rp + e), en = __ldg(rp + e + 1);
+        for (int c = lane * 8; c < Hp; c += 256) {
+            float4 a0 = f4zero(), a1 = f4zero();
+            int j = b;
+            for (; j + 2 <= en; j += 2) {
+                const size_t o0 = ((size_t)__ldg(col + j) * Hp + c) >> 3, o1 = ((size_t)__ldg(col + j + 1) * Hp + c) >> 3;
+                const uint4 x0 = h_hi[o0], x1 = h_lo[o0], y0 = h_hi[o1], y1 = h_lo[o1];
+                add_h16(x0, x1, a0, a1);
+                add_h16(y0, y1, a0, a1);
+            }
+            if (j < en) {
+                const size_t o0 = ((size_t)__ldg(col + j) * Hp + c) >> 3;
+                add_h16(h_hi[o0], h_lo[o0], a0, a1);
+            }
+            uint4 hi, lo;
+            tc::split8_f16(a0, a1, s_in, hi, lo);
             s_hi[((size_t)e * Hp + c) >> 3] = hi;
             s_lo[((size_t)e * Hp + c) >> 3] = lo;
         }
@@ -567,6 +613,14 @@ int launch_lstm_sgather(int E1, int Hp, const int* b_ptr, const int* b_col, cons
     launch_pdl(lstm_sgather_kernel, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0, st, E1, Hp, b_ptr, b_col, h, deg,
                (uint4*)s_hi, (uint4*)s_lo, scale_out);
     return check_launch("lstm_sgather");
+}
+
+int launch_lstm_sgather16(int E1, int Hp, const int* b_ptr, const int* b_col, const void* h_hi, const void* h_lo, const int* deg,
+                          void* s_hi, void* s_lo, float* scale_out, cudaStream_t st) {
+    ProfScope prof(PROF_GATHER, st, 0.0);
+    launch_pdl(lstm_sgather16_kernel, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0, st, E1, Hp, b_ptr, b_col,
+               (const uint4*)h_hi, (const uint4*)h_lo, deg, (uint4*)s_hi, (uint4*)s_lo, scale_out);
+    return check_launch("lstm_sgather16");
 }
 
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,

@@ -80,6 +80,8 @@ int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          float* gp, const float* c_prev, float* c_cur, const float* dH, const float* dC,
                          float* dP, float* dC_prev, float* amax16, cudaStream_t st);
+int launch_lstm_sgather16(int E1, int Hp, const int* b_ptr, const int* b_col, const void* h_hi, const void* h_lo, const int* deg,
+                          void* s_hi, void* s_lo, float* scale_out, cudaStream_t st);
 int launch_lstm_dx_reduce(int E1, int Hp, int depth, const float* hist_gp, const float* hist_c, float* dX, cudaStream_t st);
 int launch_gru_gate(int E1, int Hp, const int* rp, const int* col, const XTabArgs& x, const float* h_prev, float* aux,
                     cudaStream_t st);
