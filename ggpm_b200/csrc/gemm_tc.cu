@@ -1235,6 +1235,10 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
     // state gradient of a small layer (N = Hp = 256, fewer than two waves of 128 x 256 tiles): 128-wide tiles double the
     // tile count and leave TMEM room for a second accumulator set (measured -0.2 ms per cfg2 step, neutral at cfg3)
     if (mode == F16_A_TMA && g.tile_n == 0 && g.N == 256 && ceil_div(g.M, BM) < 2 * sm_count()) wide = false;
+    // plane-fed GEMMs of large layers (forward gate / forget projections, state gradient): 128-wide tiles leave TMEM room
+    // for a second accumulator set, so the epilogue of tile i overlaps the MMAs of tile i + 1 — measured on cfg4 (A/B in
+    // one gpurun call, profiles/r2_s4_*): GEMM class 35.7 -> 32.2 ms per step, step 138.2 -> 136.2 ms
+    if (mode == F16_A_TMA && g.tile_n == 0 && g.K <= 1024) wide = false;
     // (weight gradients keep 256-wide tiles: 128-wide ones measured -4 % (cfg2) / -12 % (cfg1) on that class, -0.5 % on the
     // step, but the doubled number of row-range partial sums moved the K = 19001 kernel test from 1.9e-6 to 2.7e-6)
     if (g.tile_n == 128) wide = false;
