@@ -192,11 +192,47 @@ class ClockSampler:
                 "nvml_call_ms_max": round(max(self.call_ms), 2) if self.call_ms else None}
 
 
-def make_batches(workload, n_batches, seed):
+_MEAN_ROWS = {}
+
+
+def _mol_rows(m):
+    """message rows a molecule contributes to the three layers: atom messages + 2 x tree messages"""
+    return len(m.bonds) + 2 * len(m.tree_edges)
+
+
+def balanced_batch(seed, B, slack=0.125):
+    """B molecules whose total message-row count is within ~0.05 % of B x (mean rows per molecule of the generator):
+    drawn as B + slack*B candidates, then single swaps between the chosen and the spare ones.  Data-parallel steps are
+    synchronous, so the step time is the MAX over ranks: SURVEY 8(e) asks to equalise the sum of messages per rank rather
+    than the molecule count.  The target is a constant of the generator (fixed-seed sample), identical on every rank and
+    for every N, so no cross-rank exchange is needed and N = 1 runs the same distribution."""
+    from ggpm_b200 import synth
+    if "mean" not in _MEAN_ROWS:
+        sample = synth.random_batch(987654321, 2048)
+        _MEAN_ROWS["mean"] = float(np.mean([_mol_rows(m) for m in sample]))
+    extra = max(8, int(B * slack))
+    mols = synth.random_batch(seed, B + extra)
+    w = np.asarray([_mol_rows(m) for m in mols], dtype=np.int64)
+    chosen, spare = list(range(B)), list(range(B, B + extra))
+    target = int(round(B * _MEAN_ROWS["mean"]))
+    for _ in range(64):
+        diff = int(w[chosen].sum()) - target                 # > 0: too heavy
+        if abs(diff) <= max(1, target // 4000):
+            break
+        gain = w[chosen][:, None] - w[spare][None, :]        # swapping chosen i for spare j lowers the sum by gain[i, j]
+        i, j = np.unravel_index(np.argmin(np.abs(gain - diff)), gain.shape)
+        if abs(diff - int(gain[i, j])) >= abs(diff):
+            break
+        chosen[i], spare[j] = spare[j], chosen[i]
+    return [mols[i] for i in chosen]
+
+
+def make_batches(workload, n_batches, seed, balance=True):
     from ggpm_b200 import synth, tensorize
     out = []
     for i in range(n_batches):
-        mols = synth.random_batch(seed * 1000 + i, workload["batch"])
+        mols = (balanced_batch(seed * 1000 + i, workload["batch"]) if balance
+                else synth.random_batch(seed * 1000 + i, workload["batch"]))
         tree, graph = tensorize.tensorize(mols)      # C++ index builder (bit-identical to synth.tensorize)
         out.append((tree, graph, synth.batch_stats(tree, graph)))
     return out
@@ -374,7 +410,12 @@ def run_ours(args, workload):
         else:
             torch.nn.init.xavier_normal_(p)
     model = model.to(dev).train()
-    bucket = GradBucket.for_encoder(model)      # late group = the atom layer; the rest is reduced under its backward
+    # late group = the atom layer; the rest is reduced under its backward (GGPM_BUCKET_OVERLAP=0: one group, reduced after
+    # the backward pass — A/B of the overlap)
+    if os.environ.get("GGPM_BUCKET_OVERLAP", "1") == "0":
+        bucket = GradBucket(model.parameters())
+    else:
+        bucket = GradBucket.for_encoder(model)
 
     n_batches = min(4, max(1, args.warmup))      # every batch shape is seen once before the timed region (allocator warm)
     if workload["batch"] >= 4096:
@@ -382,7 +423,9 @@ def run_ours(args, workload):
     n_batches = workload.get("pool", n_batches)
     if args.pool:
         n_batches = args.pool
-    batches = make_batches(workload, n_batches, seed=rank + 1)
+    # (diagnostics: GGPM_BENCH_SAME_SEED=1 gives every rank the same batches, GGPM_BENCH_NO_REDUCE=1 skips the collective)
+    batches = make_batches(workload, n_batches, seed=1 if os.environ.get("GGPM_BENCH_SAME_SEED") == "1" else rank + 1,
+                           balance=not args.no_balance)
     # resident inputs of the device-timed arm: the batch in the ingest format (index tensors + the CSR / reverse CSR the
     # host prepared), already in HBM; --resident make_cuda keeps the reference's int64 tensors instead (index structures
     # are then rebuilt on the device every step)
@@ -396,6 +439,8 @@ def run_ours(args, workload):
 
     from ggpm_b200 import latent as latent_head
 
+    reduce_grads = world > 1 and os.environ.get("GGPM_BENCH_NO_REDUCE") != "1"
+
     def forward_loss(tree, graph):
         if workload.get("latent"):     # encoder -> rsample -> (z, KL): the encoder side of (Hier)PropertyVAE.forward
             root = model(tree)[0] if motif else model(tree, graph)[0]
@@ -406,10 +451,10 @@ def run_ours(args, workload):
     def step(tree, graph, read_loss=False):
         model.zero_grad(set_to_none=True)
         loss = forward_loss(tree, graph)
-        if world > 1:
+        if reduce_grads:
             bucket.arm()
         loss.backward()
-        if world > 1:
+        if reduce_grads:
             bucket.all_reduce_mean()
         return float(loss.item()) if read_loss else None
 
@@ -485,6 +530,18 @@ def run_ours(args, workload):
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
     value = mols_per_step * args.steps / (ms / 1e3)
+    if args.quick:
+        if rank == 0:
+            print(json.dumps({"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                              "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                              "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "quick": True,
+                              "config": {"workload": args.workload + ": " + workload["desc"], "batch_per_gpu": workload["batch"],
+                                         "parallelism": "dp%d" % world,
+                                         "bucket_overlap": os.environ.get("GGPM_BUCKET_OVERLAP", "1")},
+                              "gpu_launches": int(launches), "clocks": clocks}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     # ---- end to end from pinned host buffers ("e2e") ------------------------------------------------
     # (1) through the ingest API (ggpm_b200.ingest.PackedBatch): the batch was packed once at
@@ -652,6 +709,10 @@ def run_ours(args, workload):
                        "gemm_engine": {0: "auto (tcgen05 f16x3 + 3xtf32)", 1: "fp32-simt", 2: "tcgen05-3xtf32", 3: "tcgen05-f16x3"}[lib.ggpm_get_gemm_engine()],
                        "l2": "no explicit flush: %d distinct batches rotate and each step streams its saved "
                              "activations (>> 126 MB L2) between forward and backward" % n_batches,
+                       "load_balance": ("none (i.i.d. batches)" if args.no_balance else
+                                        "every batch is drawn with 12.5 % spare molecules and trimmed by single swaps to the "
+                                        "generator's mean message-row count x batch (+-0.05 %), the same constant on every "
+                                        "rank and for every N: synchronous data-parallel steps wait for the slowest rank"),
                        "shape_per_batch": stats},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                     "ms_per_step": e2e_ms / args.steps, "passes_ms_per_step": e2e_passes,
@@ -691,6 +752,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--resident", default="packed", choices=["packed", "make_cuda"],
                     help="format of the HBM-resident inputs of the device-timed arm")
+    ap.add_argument("--no-balance", action="store_true",
+                    help="plain i.i.d. batches instead of batches equalised in total message rows (SURVEY 8(e))")
+    ap.add_argument("--quick", action="store_true", help="device-timed value only (scaling sweeps): no e2e legs, no per-class pass")
     ap.add_argument("--pool", type=int, default=0, help="number of distinct batches per rank (profiling runs: 2 starts faster)")
     ap.add_argument("--profile-step", action="store_true",
                     help="run one extra step between cudaProfilerStart/Stop (for ncu --profile-from-start off)")
