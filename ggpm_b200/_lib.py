@@ -50,7 +50,7 @@ SIGNATURES = {
     "ggpm_table_wgrad": (I, [P, I, I, I, P, P, P, I, I, P]),
     "ggpm_lstm_plan": (I, [I, I]),
     "ggpm_lstm_fwd": (I, [I, I, I, I, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, P]),
-    "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 28 + [I, P]),
+    "ggpm_lstm_bwd": (I, [I, I, I, I] + [P] * 28 + [I, P, P, c_longlong, P]),
     "ggpm_gru_fwd": (I, [I, I, I, I] + [P] * 13 + [I, P]),
     "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
     "ggpm_rsample_fwd": (I, [P, I, I, P, I, I, I, P, I, P, P, P]),

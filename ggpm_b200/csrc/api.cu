@@ -423,7 +423,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
                              const float* hist_h, float* hist_c, float* hist_gp, float* dH_final,
                              const float* dC_final, float* dX, float* dUg, float* dUf, float* dA_unused, float* dC, float* dP,
                              float* dS, float* S, float* dHn, float* w_split, const void* hist_h16, void* z_planes,
-                             int h_rotate, void* stream) {
+                             int h_rotate, const int32_t* bt_pos, float* pair_buf, long long pair_rows, void* stream) {
     GGPM_TRY(check_dims("lstm_bwd", E1, H, Hp, depth));
     GGPM_REQUIRE(b_ptr && b_col && bt_ptr && bt_row && Yn && src && T && k1 && Ug && Uf && hist_h && hist_c && hist_gp &&
                      dH_final && dX && dUg && dUf && dC && dP && dS && S && dHn,
@@ -457,31 +457,41 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     GGPM_REQUIRE(zmode || !h_rotate, "lstm_bwd: the forward kept only a rotating hist_h, which needs the fp16-plane path");
     char* z_hi = (char*)z_planes;
     char* z_lo = z_hi + (size_t)8 * row;                  // 4 * row halves
+    // pair mode (plane path only): the two per-pair terms of a round are stored in pair order and gathered over the
+    // reverse CSR where they are consumed, instead of being reduced into zeroed tables with atomics
+    // pair_buf: [3, pair_rows, Hp] = daf pairs | dchat * f pairs of even rounds | of odd rounds; pair_rows >= nnz
+    const bool pairs = zmode && bt_pos != nullptr && pair_buf != nullptr && pair_rows > 0 && ((uintptr_t)pair_buf & 15) == 0;
+    const size_t pair_slot = (size_t)(pair_rows > 0 ? pair_rows : 0) * Hp;
     SideStream* side = zmode ? side_stream() : nullptr;
     bool side_busy = false;                               // a weight-gradient GEMM may still be reading the Z planes
     for (int t = depth; t >= 1; --t) {
         float* c_cur = hist_c + (size_t)(t - 1) * row;          // consumed: receives sum_n daf_en of the round
         float* gp = hist_gp + (size_t)(t - 1) * 4 * row;        // consumed: [G_i|G_o|G_u] become [dai|dao|dau]
         float* dA = gp;
+        float* pairA = pairs ? pair_buf : nullptr;
+        float* pairB = pairs ? pair_buf + (size_t)(1 + (t & 1)) * pair_slot : nullptr;
+        const float* pairB_in = (pairs && t < depth) ? pair_buf + (size_t)(1 + ((t + 1) & 1)) * pair_slot : nullptr;
+        const float* dC_dense = pairs ? (t == depth ? dC_final : nullptr) : dC_cur;
         if (t == 1) {
-            GGPM_TRY(launch_lstm_cell_bwd(true, E1, H, Hp, b_ptr, b_col, x, gp, nullptr, c_cur, dH, dC_cur, nullptr, nullptr,
-                                          nullptr, st));
+            GGPM_TRY(launch_lstm_cell_bwd(true, E1, H, Hp, b_ptr, b_col, x, gp, nullptr, c_cur, dH, dC_dense, nullptr, nullptr,
+                                          nullptr, st, bt_ptr, bt_pos, pairB_in, pairA, pairB, pairs));
             break;
         }
         const float* h_prev = h_rotate ? nullptr : hist_h + (size_t)(t - 2) * row;     // only read without the plane path
         const float* c_prev = hist_c + (size_t)(t - 2) * row;
         float* dC_prev = dC + (size_t)(t & 1) * row;
-        GGPM_TRY(launch_zero2(dP, dC_prev, row, st));
+        if (!pairs) GGPM_TRY(launch_zero2(dP, dC_prev, row, st));
         // the cell kernel also records max |gate-gradient term| of this round (16 slots): the scale of the f16x3 GEMM
         float* amax_t = f16 ? fw.scal + 16 + 16 * (size_t)t : nullptr;
-        GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_cur, dP, dC_prev, amax_t, st));
+        GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_dense, dP, dC_prev, amax_t, st,
+                                      bt_ptr, bt_pos, pairB_in, pairA, pairB, pairs));
         if (zmode) {
             // Z = [gather^T(dA[:, :3Hp]) | dP] as scaled fp16 planes; then dH^{t-1} = Z [Ug; Uf] and
             // [dUg; dUf] += Z^T h^{t-1}: two plain GEMMs whose operands all arrive by TMA
             float* z_scale = fw.scal + 4;
             if (side_busy) GGPM_CUDA(cudaStreamWaitEvent(st, side->join, 0));     // Z planes / scale are rewritten next
-            GGPM_TRY(launch_lstm_zgather(E1, Hp, bt_ptr, bt_row, dA, dP, amax_t, reinterpret_cast<const int*>(fw.scal + 2),
-                                         z_hi, z_lo, z_scale, st));
+            GGPM_TRY(launch_lstm_zgather(E1, Hp, bt_ptr, bt_row, dA, dP, bt_pos, pairA, amax_t,
+                                         reinterpret_cast<const int*>(fw.scal + 2), z_hi, z_lo, z_scale, st));
             GemmArgs w;
             w.f16_tn = 1; w.Ah_hi = z_hi; w.Ah_lo = z_lo; w.lda_h = 4 * Hp; w.a_scale = z_scale;
             w.Bh_hi = (const char*)hist_h16 + (size_t)(t - 2) * 4 * row; w.Bh_lo = (const char*)w.Bh_hi + 2 * row;

@@ -113,7 +113,8 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_zgather_kernel(int E1, int Hp, const int* __restrict__ tp, const int* __restrict__ trow,
-                    const float* __restrict__ dA, const float* __restrict__ dP, const float* __restrict__ amax16,
+                    const float* __restrict__ dA, const float* __restrict__ dP, const int* __restrict__ tpos,
+                    const float* __restrict__ pairA, const float* __restrict__ amax16,
                     const int* __restrict__ deg, uint4* __restrict__ z_hi, uint4* __restrict__ z_lo,
                     float* __restrict__ scale_out) {
     pdl_wait();
@@ -141,6 +142,14 @@ lstm_zgather_kernel(int E1, int Hp, const int* __restrict__ tp, const int* __res
             if (j < en) {
                 const float* r0 = dA + (size_t)__ldg(trow + j) * ld4h + c;
                 a0 += ld4(r0); a1 += ld4(r0 + 4);
+            }
+        } else if (pairA != nullptr) {
+            // dP[n] = sum over the pairs (e, n) of daf_en, which the cell kernel stored in pair order: the scatter-add of
+            // autograd as a gather over the reverse CSR (deterministic, no atomics, nothing to zero)
+            const int cc = c - 3 * Hp;
+            for (int j = b; j < en; ++j) {
+                const float* r = pairA + (size_t)__ldg(tpos + j) * Hp + cc;
+                a0 += ld4(r); a1 += ld4(r + 4);
             }
         } else {
             const float* r = dP + (size_t)n * Hp + (c - 3 * Hp);
@@ -248,12 +257,19 @@ lstm_sgather16_kernel(int E1, int Hp, const int* __restrict__ rp, const int* __r
 // that the x-projection gradient needs is one streaming pass after the loop (lstm_dx_reduce_kernel), instead of a
 // read-modify-write of a [E, 4Hp] accumulator in every round (8 row-units of HBM traffic per message per round).
 // ------------------------------------------------------------------------------------------------
-template <bool FIRST>
+// PAIRS: instead of reducing daf_en into dP[n] and dchat_e f_en into dC_prev[n] with red.global.add (targets zeroed by a
+// kernel of their own right before), the two per-pair terms are STORED in pair order (pairA / pairB, [nnz, Hp], coalesced:
+// the pairs of a row are consecutive) and summed where they are consumed, through the reverse CSR: dP by the zgather kernel
+// of this round, dC of the previous round's rows by THIS kernel one round later (tp / tpos / pairB_in).  Same bytes as the
+// zero + reduce + re-read they replace, but plain stores and gathers: deterministic, no atomics, one launch less per round.
+template <bool FIRST, bool PAIRS>
 __global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
                      float* gp, const float* __restrict__ c_prev, float* c_cur,
                      const float* __restrict__ dH, const float* __restrict__ dC, float* __restrict__ dP,
-                     float* __restrict__ dC_prev, float* __restrict__ amax16) {
+                     float* __restrict__ dC_prev, float* __restrict__ amax16, const int* __restrict__ tp,
+                     const int* __restrict__ tpos, const float* __restrict__ pairB_in, float* __restrict__ pairA,
+                     float* __restrict__ pairB) {
     pdl_wait();
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
@@ -270,6 +286,7 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
     }
     const XRow xr = xrow(xt, e);
     const int b = FIRST ? 0 : __ldg(rp + e), en = FIRST ? 0 : __ldg(rp + e + 1);
+    const int tb = (PAIRS && pairB_in != nullptr) ? __ldg(tp + e) : 0, te = (PAIRS && pairB_in != nullptr) ? __ldg(tp + e + 1) : 0;
     const float4 one = make_float4(1.f, 1.f, 1.f, 1.f);
     for (int c = lane * 4; c < Hp; c += 128) {
         float4 ai = xval(xr, c), ao = xval(xr, Hp + c), au = xval(xr, 2 * Hp + c);
@@ -283,6 +300,11 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
         const float4 dh = clip_cols(ld4(dH + (size_t)e * Hp + c), c, H);
         float4 dchat = dh * go * (one - th * th);
         if (dC) dchat += clip_cols(ld4(dC + (size_t)e * Hp + c), c, H);
+        if (PAIRS) {       // dL/dc of this row from the round processed before: the pairs (e', this row) in reverse-CSR order
+            float4 acc = f4zero();
+            for (int j = tb; j < te; ++j) acc += ld4(pairB_in + (size_t)__ldg(tpos + j) * Hp + c);
+            dchat += clip_cols(acc, c, H);
+        }
         const float4 dai = dchat * gu * gi * (one - gi);
         const float4 dao = dh * th * go * (one - go);
         const float4 dau = dchat * gi * (one - gu * gu);
@@ -296,8 +318,13 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
                 const float4 daf = dchat * cn * f * (one - f);
                 tmax = fmaxf(tmax, amax4(daf));
                 dafs += daf;
-                red_add4(dP + (size_t)n * Hp + c, daf);
-                red_add4(dC_prev + (size_t)n * Hp + c, dchat * f);
+                if (PAIRS) {
+                    st4(pairA + (size_t)j * Hp + c, daf);
+                    st4(pairB + (size_t)j * Hp + c, dchat * f);
+                } else {
+                    red_add4(dP + (size_t)n * Hp + c, daf);
+                    red_add4(dC_prev + (size_t)n * Hp + c, dchat * f);
+                }
             }
         }
         tmax = fmaxf(tmax, fmaxf(amax4(dai), fmaxf(amax4(dao), amax4(dau))));
@@ -600,10 +627,11 @@ int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const
 }
 
 int launch_lstm_zgather(int E1, int Hp, const int* t_ptr, const int* t_row, const float* dA, const float* dP,
-                        const float* amax16, const int* deg, void* z_hi, void* z_lo, float* scale_out, cudaStream_t st) {
+                        const int* t_pos, const float* pairA, const float* amax16, const int* deg, void* z_hi, void* z_lo,
+                        float* scale_out, cudaStream_t st) {
     ProfScope prof(PROF_GATHER, st, 0.0);
-    launch_pdl(lstm_zgather_kernel, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0, st, E1, Hp, t_ptr, t_row, dA, dP, amax16,
-               deg, (uint4*)z_hi, (uint4*)z_lo, scale_out);
+    launch_pdl(lstm_zgather_kernel, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0, st, E1, Hp, t_ptr, t_row, dA, dP,
+               t_pos, pairA, amax16, deg, (uint4*)z_hi, (uint4*)z_lo, scale_out);
     return check_launch("lstm_zgather");
 }
 
@@ -625,11 +653,14 @@ int launch_lstm_sgather16(int E1, int Hp, const int* b_ptr, const int* b_col, co
 
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          float* gp, const float* c_prev, float* c_cur, const float* dH, const float* dC,
-                         float* dP, float* dC_prev, float* amax16, cudaStream_t st) {
+                         float* dP, float* dC_prev, float* amax16, cudaStream_t st, const int* t_ptr, const int* t_pos,
+                         const float* pairB_in, float* pairA, float* pairB, bool pairs) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_BWD, st, 0.0);
-    launch_pdl(first ? lstm_cell_bwd_kernel<true> : lstm_cell_bwd_kernel<false>, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0,
-               st, E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH, dC, dP, dC_prev, amax16);
+    auto kern = pairs ? (first ? lstm_cell_bwd_kernel<true, true> : lstm_cell_bwd_kernel<false, true>)
+                      : (first ? lstm_cell_bwd_kernel<true, false> : lstm_cell_bwd_kernel<false, false>);
+    launch_pdl(kern, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0, st, E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH,
+               dC, dP, dC_prev, amax16, t_ptr, t_pos, pairB_in, pairA, pairB);
     return check_launch("lstm_cell_bwd");
 }
 

@@ -64,7 +64,8 @@ int launch_lstm_sgather(int E1, int Hp, const int* b_ptr, const int* b_col, cons
                         void* s_lo, float* scale_out, cudaStream_t st);
 int launch_zero2(float* a, float* b, size_t n, cudaStream_t st);   // zero two fp32 arrays of n floats (n % 4 == 0) in one launch
 int launch_lstm_zgather(int E1, int Hp, const int* t_ptr, const int* t_row, const float* dA, const float* dP,
-                        const float* amax16, const int* deg, void* z_hi, void* z_lo, float* scale_out, cudaStream_t st);
+                        const int* t_pos, const float* pairA, const float* amax16, const int* deg, void* z_hi, void* z_lo,
+                        float* scale_out, cudaStream_t st);
 int launch_max_degree(const int* row_ptr, int rows, int* out, cudaStream_t st);   // *out = max(*out, max row length)
 // hi = rn_tf32(w), lo = rn_tf32(w - hi), element-wise over n floats (weights are split once per layer call)
 int launch_tf32_split(const float* w, long long n, float* hi, float* lo, cudaStream_t st);
@@ -79,7 +80,9 @@ int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const
                          cudaStream_t st);
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          float* gp, const float* c_prev, float* c_cur, const float* dH, const float* dC,
-                         float* dP, float* dC_prev, float* amax16, cudaStream_t st);
+                         float* dP, float* dC_prev, float* amax16, cudaStream_t st, const int* t_ptr = nullptr,
+                         const int* t_pos = nullptr, const float* pairB_in = nullptr, float* pairA = nullptr,
+                         float* pairB = nullptr, bool pairs = false);
 int launch_lstm_sgather16(int E1, int Hp, const int* b_ptr, const int* b_col, const void* h_hi, const void* h_lo, const int* deg,
                           void* s_hi, void* s_lo, float* scale_out, cudaStream_t st);
 int launch_lstm_dx_reduce(int E1, int Hp, int depth, const float* hist_gp, const float* hist_c, float* dX, cudaStream_t st);

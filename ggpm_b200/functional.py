@@ -509,6 +509,17 @@ class MessageGraph:
         return self._by_src
 
 
+_BWD_PAIRS = None
+
+
+def _bwd_pairs() -> bool:
+    global _BWD_PAIRS
+    if _BWD_PAIRS is None:
+        import os
+        _BWD_PAIRS = os.environ.get("GGPM_BWD_PAIRS", "0") == "1"
+    return _BWD_PAIRS
+
+
 def _empty(*shape, device):
     return torch.empty(*shape, dtype=torch.float32, device=device)
 
@@ -574,13 +585,21 @@ class LSTMMessages(torch.autograd.Function):
         dC, dP, dS = _empty(2, E1, Hp, device=dev), _empty(E1, Hp, device=dev), _empty(E1, Hp, device=dev)
         S, dHn = _empty(E1, Hp, device=dev), _empty(E1, Hp, device=dev)
         bt = mg.b.T
+        # per-pair stores + reverse-CSR gathers instead of atomics (fp16-plane path; see include/ggpm_b200.h)
+        bt_pos = getattr(bt, "pos", None)
+        # Opt-in (GGPM_BWD_PAIRS=1): measured neutral to slightly slower than the vector reductions (cfg4 137.7 vs 136.2 ms,
+        # cfg2 12.28 vs 12.18 ms: the stores + gathers cost what the zeroing launch did) — its value is a bit-reproducible
+        # backward pass.
+        pair_rows = mg.b.col.numel() if (_bwd_pairs() and z_planes is not None and bt_pos is not None and depth > 1) else 0
+        pair_buf = _empty(3, pair_rows, Hp, device=dev) if pair_rows else None
         call("ggpm_lstm_bwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), iptr(bt.row_ptr), iptr(bt.col),
              fptr(Yn), iptr(mg.src), fptr(T), iptr(mg.k1), None if mg.k2 is None else iptr(mg.k2), fptr(Ug), fptr(Uf),
              fptr(hist_h), fptr(hist_c), fptr(hist_gp), fptr(dH), None if dCf is None else fptr(dCf), fptr(dX), fptr(dUg),
              fptr(dUf), None, fptr(dC),
              fptr(dP), fptr(dS), fptr(S), fptr(dHn), fptr(_empty(2, Hp, 4 * Hp, device=dev)),
              None if hist_h16 is None else hist_h16.data_ptr(), None if z_planes is None else z_planes.data_ptr(),
-             int(ctx.rotate), stream_ptr(dev))
+             int(ctx.rotate), None if pair_buf is None else iptr(bt_pos), None if pair_buf is None else fptr(pair_buf),
+             pair_rows, stream_ptr(dev))
         dphi, dWx, dT = _xproj_backward(ctx, dX, phi_x, Wx, T, mg)
         return dphi, dWx, dT, dU4, None, None, None
 

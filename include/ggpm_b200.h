@@ -210,6 +210,10 @@ int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const 
  * hist_gp and hist_c are CONSUMED: every round's gate gradients overwrite that round's [G_i|G_o|G_u] block of hist_gp
  * and its forget-gate input gradient overwrites that round's slot of hist_c (each is dead once its round has been
  * back-propagated), so no [E1, 4Hp] accumulator is read and re-written per round; a second call needs a new forward.
+ * bt_pos (position of every reverse entry in b_col; ggpm_csr_transpose's t_pos) and pair_buf [3, pair_rows, Hp] with
+ * pair_rows >= nnz (both may be NULL / 0): on the fp16-plane path the scatter-adds of a round (sum_n daf_en into dP,
+ * dchat f_en into dC of the previous state) are then stored per pair and gathered over the reverse CSR where they are
+ * consumed — deterministic, no atomics, no zeroing launch; without them they are red.global.add into zeroed dP / dC.
  * Scratch: dA (unused since round 2, may be NULL), dC [2, E1, Hp], dP [E1, Hp], dS [E1, Hp], S [E1, Hp], dHn [E1, Hp];
  * w_split: optional [2, Hp, 4Hp] (may be NULL) for the tf32 planes of [Ug; Uf]^T streamed by TMA. */
 int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,
@@ -218,7 +222,7 @@ int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const 
                   const float* hist_h, float* hist_c, float* hist_gp, float* dH_final,
                   const float* dC_final, float* dX, float* dUg, float* dUf, float* dA, float* dC, float* dP, float* dS,
                   float* S, float* dHn, float* w_split, const void* hist_h16, void* z_planes, int h_rotate,
-                  void* stream);
+                  const int32_t* bt_pos, float* pair_buf, long long pair_rows, void* stream);
 
 /* Which optional buffers the two calls above will use under the current engine, so the caller can size them:
  * bit 0: f16x3 gate GEMMs; bit 1: fp16 h planes + Z planes (then hist_h may be 2 rotating slots: h_rotate = 1). */

@@ -373,7 +373,7 @@ class EmuLib:
 
     def ggpm_lstm_bwd(self, E1, H, Hp, depth, b_ptr, b_col, bt_ptr, bt_row, Yn, src, T, k1, k2, Ug, Uf, hist_h,
                       hist_c, hist_gp, dH_final, dC_final, dX, dUg, dUf, dA, dC, dP, dS, S, dHn, w_split, hist_h16, z_planes,
-                      h_rotate, stream):
+                      h_rotate, bt_pos, pair_buf, pair_rows, stream):
         self._tick("lstm_bwd")
         rp, col = _csr(b_ptr, b_col, E1)
         trp, tcol = _csr(bt_ptr, bt_row, E1)
