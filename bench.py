@@ -519,6 +519,8 @@ def run_ours(args, workload):
     launches = (_lib.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
     clocks = sampler.stop() if rank == 0 else None
     if clocks is not None:
+        # `samples`: NVML samples of the sampled pass (200 ms period over its W + K steps under load) plus the one taken
+        # right after the last step of the reported pass was enqueued (`samples_inside_timed_region`)
         clocks["samples_inside_timed_region"] = int(getattr(sampler, "in_region", 0))
         clocks["ms_per_step_with_sampler_thread"] = ms_sampled / args.steps
     mols_per_step = workload["batch"] * world

@@ -145,7 +145,7 @@ lstm_zgather_kernel(int E1, int Hp, const int* __restrict__ tp, const int* __res
             }
         } else if (pairA != nullptr) {
             // dP[n] = sum over the pairs (e, n) of daf_en, which the cell kernel stored in pair order: the scatter-add of
-            // autograd as a gather over the reverse CSR (deterministic, no atomics, nothing to zero)
+            // autograd as a gather over the reverse CSR (no atomics, nothing to zero)
             const int cc = c - 3 * Hp;
             for (int j = b; j < en; ++j) {
                 const float* r = pairA + (size_t)__ldg(tpos + j) * Hp + cc;
@@ -261,7 +261,7 @@ lstm_sgather16_kernel(int E1, int Hp, const int* __restrict__ rp, const int* __r
 // kernel of their own right before), the two per-pair terms are STORED in pair order (pairA / pairB, [nnz, Hp], coalesced:
 // the pairs of a row are consecutive) and summed where they are consumed, through the reverse CSR: dP by the zgather kernel
 // of this round, dC of the previous round's rows by THIS kernel one round later (tp / tpos / pairB_in).  Same bytes as the
-// zero + reduce + re-read they replace, but plain stores and gathers: deterministic, no atomics, one launch less per round.
+// zero + reduce + re-read they replace, but plain stores and gathers: no atomics, one launch less per round.
 template <bool FIRST, bool PAIRS>
 __global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,

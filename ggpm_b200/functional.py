@@ -588,8 +588,8 @@ class LSTMMessages(torch.autograd.Function):
         # per-pair stores + reverse-CSR gathers instead of atomics (fp16-plane path; see include/ggpm_b200.h)
         bt_pos = getattr(bt, "pos", None)
         # Opt-in (GGPM_BWD_PAIRS=1): measured neutral to slightly slower than the vector reductions (cfg4 137.7 vs 136.2 ms,
-        # cfg2 12.28 vs 12.18 ms: the stores + gathers cost what the zeroing launch did) — its value is a bit-reproducible
-        # backward pass.
+        # cfg2 12.28 vs 12.18 ms: the stores + gathers cost what the zeroing launch did) — its value is a cell kernel without atomics
+        # (the weight-gradient GEMM's split-K partial sums still meet in fp32 reduce-adds).
         pair_rows = mg.b.col.numel() if (_bwd_pairs() and z_planes is not None and bt_pos is not None and depth > 1) else 0
         pair_buf = _empty(3, pair_rows, Hp, device=dev) if pair_rows else None
         call("ggpm_lstm_bwd", E1, H, Hp, depth, iptr(mg.b.row_ptr), iptr(mg.b.col), iptr(bt.row_ptr), iptr(bt.col),

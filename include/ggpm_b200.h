@@ -213,7 +213,7 @@ int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const 
  * bt_pos (position of every reverse entry in b_col; ggpm_csr_transpose's t_pos) and pair_buf [3, pair_rows, Hp] with
  * pair_rows >= nnz (both may be NULL / 0): on the fp16-plane path the scatter-adds of a round (sum_n daf_en into dP,
  * dchat f_en into dC of the previous state) are then stored per pair and gathered over the reverse CSR where they are
- * consumed — deterministic, no atomics, no zeroing launch; without them they are red.global.add into zeroed dP / dC.
+ * consumed — no atomics, no zeroing launch; without them they are red.global.add into zeroed dP / dC.
  * Scratch: dA (unused since round 2, may be NULL), dC [2, E1, Hp], dP [E1, Hp], dS [E1, Hp], S [E1, Hp], dHn [E1, Hp];
  * w_split: optional [2, Hp, 4Hp] (may be NULL) for the tf32 planes of [Ug; Uf]^T streamed by TMA. */
 int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_ptr, const int32_t* b_col,

@@ -116,29 +116,15 @@ def test_backward_with_the_side_stream_matches_golden():
     assert " passed" in r.stdout
 
 
-def test_atomic_free_backward_matches_golden_and_is_bit_reproducible():
+def test_atomic_free_backward_matches_golden():
     """GGPM_BWD_PAIRS=1 replaces the vector reductions of the backward cell kernel (dP, dC of the previous state) by per-pair
-    stores gathered over the reverse CSR: same goldens, and two backward passes over the same batch agree bit for bit.  The
-    switch is read once per process, so the checks run in a child process."""
+    stores gathered over the reverse CSR: same goldens.  (The whole backward pass is still not bit-reproducible: the
+    split-K partial sums of the weight-gradient GEMM meet in fp32 reduce-adds.)  The switch is read once per process, so
+    the checks run in a child process."""
     import subprocess
     env = dict(os.environ, GGPM_BWD_PAIRS="1")
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider",
-                        "-k", "cfg1_matches or (forward_backward_matches and auto and lstm) or _pairs_child"], env=env,
+                        "-k", "cfg1_matches or (forward_backward_matches and auto and lstm)"], env=env,
                        capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
     assert " passed" in r.stdout
-
-
-def test_pairs_child_bit_reproducible():
-    if os.environ.get("GGPM_BWD_PAIRS") != "1":
-        pytest.skip("runs inside test_atomic_free_backward_matches_golden_and_is_bit_reproducible")
-    from conftest import load_golden
-    meta, z, tree, graph = load_golden("hier_lstm_cfg1")
-    model = C.build_model(meta, DEV)
-    grads = []
-    for _ in range(2):
-        model.zero_grad(set_to_none=True)
-        model(C.to_dev(tree, DEV), C.to_dev(graph, DEV))[0].sum().backward()
-        grads.append({k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None})
-    for k in ("graph_encoder.rnn.W_f.0.weight", "inter_encoder.rnn.W_i.0.weight", "tree_encoder.rnn.W.0.bias"):
-        assert torch.equal(grads[0][k], grads[1][k]), k
