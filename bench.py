@@ -364,7 +364,8 @@ def run_reference(args, workload):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload + ": " + workload["desc"], "hidden": workload["hidden"],
                    "depthT": workload["depthT"], "depthG": workload["depthG"], "rnn_type": "LSTM",
-                   "dropout": workload["dropout"], "batch_per_gpu": workload["batch"], "sample_molecules": sample},
+                   "dropout": workload["dropout"], "batch_per_gpu": workload["batch"]},
+        "sample_molecules": sample,
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
                          "sample": _sample_note(workload, sample, kind, dt, cores)},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
