@@ -42,7 +42,9 @@ __device__ __forceinline__ float4 xval(const XRow& r, int off) {
 // ------------------------------------------------------------------------------------------------
 // LSTM forward cell:  reads gp = [G_i|G_o|G_u|P] of this round (rows e: G, rows n: P), c_prev; writes h, c
 // ------------------------------------------------------------------------------------------------
-template <bool FIRST>
+// NC = column chunks (128 columns each) a lane works on together: with NC = 2 (Hp a multiple of 256, the shipped width) the
+// neighbour ids are loaded once for both chunks and twice as many gathered rows are in flight per warp.
+template <bool FIRST, int NC>
 __global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
                      const float* __restrict__ gp, const float* __restrict__ c_prev, float* __restrict__ h_out,
@@ -65,42 +67,64 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
     const XRow xr = xrow(xt, e);
     const int b = FIRST ? 0 : __ldg(rp + e), en = FIRST ? 0 : __ldg(rp + e + 1);
     const float* ge = gp + (size_t)e * ld4h;
-    for (int c = lane * 4; c < Hp; c += 128) {
-        float4 ai = xval(xr, c), ao = xval(xr, Hp + c), au = xval(xr, 2 * Hp + c);
-        float4 chat;
+    for (int c0 = lane * 4; c0 < Hp; c0 += 128 * NC) {
+        float4 ai[NC], ao[NC], au[NC], chat[NC];
+#pragma unroll
+        for (int k = 0; k < NC; ++k) {
+            const int c = c0 + 128 * k;
+            ai[k] = xval(xr, c); ao[k] = xval(xr, Hp + c); au[k] = xval(xr, 2 * Hp + c);
+        }
         if (FIRST) {
-            chat = sigmoid4(ai) * tanh4(au);
+#pragma unroll
+            for (int k = 0; k < NC; ++k) chat[k] = sigmoid4(ai[k]) * tanh4(au[k]);
         } else {
-            ai += ld4(ge + c);
-            ao += ld4(ge + Hp + c);
-            au += ld4(ge + 2 * Hp + c);
-            chat = sigmoid4(ai) * tanh4(au);
-            const float4 xf = xval(xr, 3 * Hp + c);
-            int j = b;
-            for (; j + 2 <= en; j += 2) {
-                const int n0 = __ldg(col + j), n1 = __ldg(col + j + 1);
-                float4 p0 = ld4(gp + (size_t)n0 * ld4h + 3 * Hp + c), p1 = ld4(gp + (size_t)n1 * ld4h + 3 * Hp + c);
-                float4 c0 = ld4(c_prev + (size_t)n0 * Hp + c), c1 = ld4(c_prev + (size_t)n1 * Hp + c);
-                chat = fma4(sigmoid4(xf + p0), c0, chat);
-                chat = fma4(sigmoid4(xf + p1), c1, chat);
+            float4 xf[NC];
+#pragma unroll
+            for (int k = 0; k < NC; ++k) {
+                const int c = c0 + 128 * k;
+                ai[k] += ld4(ge + c);
+                ao[k] += ld4(ge + Hp + c);
+                au[k] += ld4(ge + 2 * Hp + c);
+                xf[k] = xval(xr, 3 * Hp + c);
             }
-            if (j < en) {
+#pragma unroll
+            for (int k = 0; k < NC; ++k) chat[k] = sigmoid4(ai[k]) * tanh4(au[k]);
+            int j = b;
+            if (NC == 1) {
+                for (; j + 2 <= en; j += 2) {
+                    const int n0 = __ldg(col + j), n1 = __ldg(col + j + 1);
+                    float4 p0 = ld4(gp + (size_t)n0 * ld4h + 3 * Hp + c0), p1 = ld4(gp + (size_t)n1 * ld4h + 3 * Hp + c0);
+                    float4 q0 = ld4(c_prev + (size_t)n0 * Hp + c0), q1 = ld4(c_prev + (size_t)n1 * Hp + c0);
+                    chat[0] = fma4(sigmoid4(xf[0] + p0), q0, chat[0]);
+                    chat[0] = fma4(sigmoid4(xf[0] + p1), q1, chat[0]);
+                }
+            }
+            for (; j < en; ++j) {
                 const int n0 = __ldg(col + j);
-                float4 p0 = ld4(gp + (size_t)n0 * ld4h + 3 * Hp + c);
-                float4 c0 = ld4(c_prev + (size_t)n0 * Hp + c);
-                chat = fma4(sigmoid4(xf + p0), c0, chat);
+                float4 p[NC], q[NC];
+#pragma unroll
+                for (int k = 0; k < NC; ++k) {
+                    p[k] = ld4(gp + (size_t)n0 * ld4h + 3 * Hp + c0 + 128 * k);
+                    q[k] = ld4(c_prev + (size_t)n0 * Hp + c0 + 128 * k);
+                }
+#pragma unroll
+                for (int k = 0; k < NC; ++k) chat[k] = fma4(sigmoid4(xf[k] + p[k]), q[k], chat[k]);
             }
         }
-        chat = clip_cols(chat, c, H);
-        float4 h = clip_cols(sigmoid4(ao) * tanh4(chat), c, H);
-        st4(c_out + (size_t)e * Hp + c, chat);
-        if (h_out) st4(h_out + (size_t)e * Hp + c, h);      // large layers read h through the fp16 planes below only
-        if (h16_hi) {   // fp16 hi / lo planes of h * 2^13 (|h| <= 1): the B operand of the f16x3 weight-gradient GEMM
-            uint2 hi, lo;
-            tc::split2_f16(h.x * kH16Scale, h.y * kH16Scale, hi.x, lo.x);
-            tc::split2_f16(h.z * kH16Scale, h.w * kH16Scale, hi.y, lo.y);
-            h16_hi[((size_t)e * Hp + c) >> 2] = hi;
-            h16_lo[((size_t)e * Hp + c) >> 2] = lo;
+#pragma unroll
+        for (int k = 0; k < NC; ++k) {
+            const int c = c0 + 128 * k;
+            const float4 ch = clip_cols(chat[k], c, H);
+            const float4 h = clip_cols(sigmoid4(ao[k]) * tanh4(ch), c, H);
+            st4(c_out + (size_t)e * Hp + c, ch);
+            if (h_out) st4(h_out + (size_t)e * Hp + c, h);      // large layers read h through the fp16 planes below only
+            if (h16_hi) {   // fp16 hi / lo planes of h * 2^13 (|h| <= 1): the B operand of the f16x3 weight-gradient GEMM
+                uint2 hi, lo;
+                tc::split2_f16(h.x * kH16Scale, h.y * kH16Scale, hi.x, lo.x);
+                tc::split2_f16(h.z * kH16Scale, h.w * kH16Scale, hi.y, lo.y);
+                h16_hi[((size_t)e * Hp + c) >> 2] = hi;
+                h16_lo[((size_t)e * Hp + c) >> 2] = lo;
+            }
         }
     }
     }
@@ -616,12 +640,27 @@ static inline int cell_blocks_persistent(int E1) {
     return need < cap ? need : cap;
 }
 
+// GGPM_CELL_FWD_NC=2 selects the two-chunk variant.  Measured (same box, A/B/A/B): cfg4 137.6 vs 137.0 ms, cfg2 12.43 vs 12.29 ms
+// per step in favour of ONE chunk per pass (the kernel is not short of loads in flight; the second chunk costs registers),
+// so one chunk is the default.
+static int cell_fwd_chunks(int Hp) {
+    static int nc = -1;
+    if (nc < 0) {
+        const char* e = getenv("GGPM_CELL_FWD_NC");
+        nc = e != nullptr ? atoi(e) : 1;
+    }
+    return (nc == 2 && Hp % 256 == 0) ? 2 : 1;
+}
+
 int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          const float* gp, const float* c_prev, float* h_out, float* c_out, void* h16_hi, void* h16_lo,
                          cudaStream_t st) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_FWD, st, 0.0);
-    launch_pdl(first ? lstm_cell_fwd_kernel<true> : lstm_cell_fwd_kernel<false>, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0,
+    const bool two = cell_fwd_chunks(Hp) == 2;
+    auto kern = first ? (two ? lstm_cell_fwd_kernel<true, 2> : lstm_cell_fwd_kernel<true, 1>)
+                      : (two ? lstm_cell_fwd_kernel<false, 2> : lstm_cell_fwd_kernel<false, 1>);
+    launch_pdl(kern, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0,
                st, E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out, (uint2*)h16_hi, (uint2*)h16_lo);
     return check_launch("lstm_cell_fwd");
 }
