@@ -2,7 +2,7 @@
 """Benchmark of the hierarchical message-passing encoder hot path (BASELINE.json metric:
 "HierMPN encoder molecules/sec (fwd+bwd)").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg1|cfg2|cfg3s|cfg3|cfg4|cfg5|cfg5h]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg1|cfg2|cfg3s|cfg3|cfg4|cfg5|cfg5h|cfg2g]
 
 One step = HierMPNEncoder forward + backward (loss = hroot.sum(), the only output the VAEs consume,
 ggpm/property_vae.py:50) over one synthetic batch.  The default workload is BASELINE config #4, the one the
@@ -58,6 +58,8 @@ WORKLOADS = {
     "cfg5": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256, encoder="motif", latent=24,
                  desc="PropertyVAE encoder side of one pre-training step: MotifEncoder + R_mean/R_var rsample/KL "
                       "(ggpm/property_vae.py:79-99), batch 256 per GPU, decoder excluded"),
+    "cfg2g": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256, rnn="GRU",
+                  desc="cfg2 with rnn_type GRU (constructible, ggpm/encoder.py:21-22; no shipped config uses it), batch 256"),
     "cfg5h": dict(hidden=250, depthT=20, depthG=20, dropout=0.1, batch=256, latent=24,
                   desc="HierPropertyVAE ('hier-prop', ggpm/opvnet.py:7) encoder side of one pre-training step: HierMPNEncoder + "
                        "R_mean/R_var rsample/KL (ggpm/property_vae.py:48-52), batch 256 per GPU, decoder excluded"),
@@ -271,7 +273,7 @@ def _reference_step_fn(workload, sample_mols):
         ref.nnutils.device = torch.device("cpu")          # the reference pins cuda:0 when it sees a GPU (nnutils.py:9-10)
         torch.manual_seed(0)
         cls = ref.encoder.MotifEncoder if motif else ref.encoder.HierMPNEncoder
-        model = cls(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H, workload["depthT"],
+        model = cls(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), workload.get("rnn", "LSTM"), H, H, workload["depthT"],
                     workload["depthG"], workload["dropout"])
         if L:
             model.R_mean, model.R_var = torch.nn.Linear(H, L), torch.nn.Linear(H, L)
@@ -297,7 +299,7 @@ def _reference_step_fn(workload, sample_mols):
 
     from oracle import encoder_oracle as eo
     sd = {k: v.requires_grad_(True)
-          for k, v in eo.random_state("motif" if motif else "hier", "LSTM", H, H, 0, bias_std=0.0).items()}
+          for k, v in eo.random_state("motif" if motif else "hier", workload.get("rnn", "LSTM"), H, H, 0, bias_std=0.0).items()}
     if L:
         from oracle import latent_oracle as lo
         lat = [torch.randn(L, H) / H ** 0.5, torch.zeros(L), torch.randn(L, H) / H ** 0.5, torch.zeros(L)]
@@ -307,12 +309,12 @@ def _reference_step_fn(workload, sample_mols):
         for v in sd.values():
             v.grad = None
         if L:
-            root = (eo.motif_encoder(sd, "LSTM", workload["depthT"], tree)[0] if motif else
-                    eo.hier_encoder(sd, "LSTM", workload["depthT"], workload["depthG"], tree, graph)[0])
+            root = (eo.motif_encoder(sd, workload.get("rnn", "LSTM"), workload["depthT"], tree)[0] if motif else
+                    eo.hier_encoder(sd, workload.get("rnn", "LSTM"), workload["depthT"], workload["depthG"], tree, graph)[0])
             z, kl = lo.rsample(root, *lat, torch.randn(root.shape[0], L), True)
             (z.sum() + kl).backward()
         else:
-            eo.hier_encoder(sd, "LSTM", workload["depthT"], workload["depthG"], tree, graph)[0].sum().backward()
+            eo.hier_encoder(sd, workload.get("rnn", "LSTM"), workload["depthT"], workload["depthG"], tree, graph)[0].sum().backward()
     return step, "port"
 
 
@@ -363,7 +365,7 @@ def run_reference(args, workload):
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload + ": " + workload["desc"], "hidden": workload["hidden"],
-                   "depthT": workload["depthT"], "depthG": workload["depthG"], "rnn_type": "LSTM",
+                   "depthT": workload["depthT"], "depthG": workload["depthG"], "rnn_type": workload.get("rnn", "LSTM"),
                    "dropout": workload["dropout"], "batch_per_gpu": workload["batch"]},
         "sample_molecules": sample,
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
@@ -400,7 +402,7 @@ def run_ours(args, workload):
     torch.manual_seed(0)
     motif = workload.get("encoder") == "motif"
     enc_cls = ggpm_b200.MotifEncoder if motif else ggpm_b200.HierMPNEncoder
-    model = enc_cls(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H,
+    model = enc_cls(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), workload.get("rnn", "LSTM"), H, H,
                     workload["depthT"], workload["depthG"], workload["dropout"])
     if workload.get("latent"):            # the VAEs keep the latent head next to the encoder (property_vae.py:23-24, 86-87)
         model.R_mean = torch.nn.Linear(H, workload["latent"])
@@ -707,7 +709,7 @@ def run_ours(args, workload):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload + ": " + workload["desc"], "hidden": H, "depthT": workload["depthT"],
-                       "depthG": workload["depthG"], "rnn_type": "LSTM", "dropout": workload["dropout"],
+                       "depthG": workload["depthG"], "rnn_type": workload.get("rnn", "LSTM"), "dropout": workload["dropout"],
                        "batch_per_gpu": workload["batch"], "parallelism": "dp%d" % world,
                        "gemm_engine": {0: "auto (tcgen05 f16x3 + 3xtf32)", 1: "fp32-simt", 2: "tcgen05-3xtf32", 3: "tcgen05-f16x3"}[lib.ggpm_get_gemm_engine()],
                        "l2": "no explicit flush: %d distinct batches rotate and each step streams its saved "

@@ -16,7 +16,7 @@ a = ap.parse_args()
 w = bench.WORKLOADS[a.workload]
 H = w["hidden"]
 torch.manual_seed(0)
-model = ggpm_b200.HierMPNEncoder(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), "LSTM", H, H, w["depthT"], w["depthG"], w["dropout"])
+model = ggpm_b200.HierMPNEncoder(synth.SizeOnlyPairVocab(), synth.SizeOnlyAtomVocab(), w.get("rnn", "LSTM"), H, H, w["depthT"], w["depthG"], w["dropout"])
 for p in model.parameters():
     torch.nn.init.constant_(p, 0) if p.dim() == 1 else torch.nn.init.xavier_normal_(p)
 model = model.cuda().train()
