@@ -191,43 +191,10 @@ lstm_zgather_kernel(int E1, int Hp, const int* __restrict__ tp, const int* __res
 // S = gather-sum of the neighbours' h^{t-1} (index_select_ND(h, 0, bgraph).sum(1), ggpm/rnn.py:86) as scaled fp16
 // hi / lo planes [E1, Hp]: for large layers the forward gate GEMM then takes both operands by TMA (no producer
 // arithmetic, the sum is formed once per row instead of once per N tile).  |h| <= 1, so the largest neighbour count
-// bounds every row.
+// bounds every row.  The source is the pair of fp16 hi / lo planes of h^{t-1} * 2^13 that the forward cell kernel saves
+// anyway (the operands of the forget-projection and weight-gradient GEMMs): large layers never write or read an fp32
+// copy of h between rounds.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
-lstm_sgather_kernel(int E1, int Hp, const int* __restrict__ rp, const int* __restrict__ col, const float* __restrict__ h,
-                    const int* __restrict__ deg, uint4* __restrict__ s_hi, uint4* __restrict__ s_lo,
-                    float* __restrict__ scale_out) {
-    pdl_wait();
-    pdl_launch_dependents();
-    const int lane = threadIdx.x & 31;
-    const float s = tc::pow2_scale((float)max(1, __ldg(deg)));
-    if (blockIdx.x == 0 && threadIdx.x == 0) *scale_out = s;
-    const int n_warps = (gridDim.x * blockDim.x) >> 5;
-    for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < E1; e += n_warps) {
-        const int b = __ldg(rp + e), en = __ldg(rp + e + 1);
-        for (int c = lane * 8; c < Hp; c += 256) {
-            float4 a0 = f4zero(), a1 = f4zero();
-            int j = b;
-            for (; j + 2 <= en; j += 2) {
-                const float* r0 = h + (size_t)__ldg(col + j) * Hp + c;
-                const float* r1 = h + (size_t)__ldg(col + j + 1) * Hp + c;
-                const float4 x0 = ld4(r0), x1 = ld4(r0 + 4), y0 = ld4(r1), y1 = ld4(r1 + 4);
-                a0 += x0; a1 += x1; a0 += y0; a1 += y1;
-            }
-            if (j < en) {
-                const float* r0 = h + (size_t)__ldg(col + j) * Hp + c;
-                a0 += ld4(r0); a1 += ld4(r0 + 4);
-            }
-            uint4 hi, lo;
-            tc::split8_f16(a0, a1, s, hi, lo);
-            s_hi[((size_t)e * Hp + c) >> 3] = hi;
-            s_lo[((size_t)e * Hp + c) >> 3] = lo;
-        }
-    }
-}
-
-// The same from the fp16 hi / lo planes of h^{t-1} * 2^13 that the forward cell kernel saves anyway (the operands of the
-// forget-projection and weight-gradient GEMMs): large layers then never write or read an fp32 copy of h between rounds.
 __device__ __forceinline__ void add_h16(uint4 hi, uint4 lo, float4& a0, float4& a1) {
     const __half2* ph = reinterpret_cast<const __half2*>(&hi);
     const __half2* pl = reinterpret_cast<const __half2*>(&lo);
@@ -672,14 +639,6 @@ int launch_lstm_zgather(int E1, int Hp, const int* t_ptr, const int* t_row, cons
     launch_pdl(lstm_zgather_kernel, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0, st, E1, Hp, t_ptr, t_row, dA, dP,
                t_pos, pairA, amax16, deg, (uint4*)z_hi, (uint4*)z_lo, scale_out);
     return check_launch("lstm_zgather");
-}
-
-int launch_lstm_sgather(int E1, int Hp, const int* b_ptr, const int* b_col, const float* h, const int* deg, void* s_hi,
-                        void* s_lo, float* scale_out, cudaStream_t st) {
-    ProfScope prof(PROF_GATHER, st, 0.0);
-    launch_pdl(lstm_sgather_kernel, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0, st, E1, Hp, b_ptr, b_col, h, deg,
-               (uint4*)s_hi, (uint4*)s_lo, scale_out);
-    return check_launch("lstm_sgather");
 }
 
 int launch_lstm_sgather16(int E1, int Hp, const int* b_ptr, const int* b_col, const void* h_hi, const void* h_lo, const int* deg,

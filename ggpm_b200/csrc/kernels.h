@@ -60,8 +60,6 @@ int launch_f16_split_transpose(const float* w, int rows, int cols, const float* 
                                cudaStream_t st);
 // Z = [gather^T(dA[:, :3Hp]) | dP] as fp16 hi / lo planes [E1, 4Hp] scaled by the power of two derived from
 // max(amax16[0..16)) * max(1, *deg); the scale is stored to *scale_out.  Z[n, :3Hp] = sum_{e in T(n)} dA[e, :3Hp].
-int launch_lstm_sgather(int E1, int Hp, const int* b_ptr, const int* b_col, const float* h, const int* deg, void* s_hi,
-                        void* s_lo, float* scale_out, cudaStream_t st);
 int launch_zero2(float* a, float* b, size_t n, cudaStream_t st);   // zero two fp32 arrays of n floats (n % 4 == 0) in one launch
 int launch_lstm_zgather(int E1, int Hp, const int* t_ptr, const int* t_row, const float* dA, const float* dP,
                         const int* t_pos, const float* pairA, const float* amax16, const int* deg, void* z_hi, void* z_lo,
