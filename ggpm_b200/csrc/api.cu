@@ -176,6 +176,17 @@ static int sgather_min_rows() {
     }
     return v;
 }
+// GGPM_FUSED_GATES=1: on the plane-fed path the forward gate GEMM applies the x-projection, the gate non-linearities and the
+// row-0 mask in its epilogue (GGPM_ACT_LSTM_GATES) and the history keeps the activated gates; the cell kernels then only
+// evaluate the per-neighbour forget gate.  Read by the forward and the backward call alike.
+static bool fused_gates() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("GGPM_FUSED_GATES");
+        v = (e != nullptr && e[0] == '1') ? 1 : 0;
+    }
+    return v != 0;
+}
 static bool f16_engine_on() {
     const int e = gemm_engine();
     return e == GGPM_ENGINE_AUTO || e == GGPM_ENGINE_TCGEN05_F16X3;
@@ -387,6 +398,10 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
                     a.Ah_hi = s_hi; a.Ah_lo = s_lo; a.lda_h = Hp; a.a_scale = s_scale;
                     a.Bh_hi = fw.hi; a.Bh_lo = fw.lo; a.sbn = Hp; a.b_scale = fw.scal + 1;
                     a.C = gp; a.ldc = 4 * Hp; a.M = E1; a.N = 3 * Hp; a.K = Hp;
+                    if (fused_gates()) {
+                        a.act = GGPM_ACT_LSTM_GATES;
+                        a.gx_Yn = Yn; a.gx_src = src; a.gx_T = T; a.gx_k1 = k1; a.gx_k2 = k2; a.gx_ld = 4 * Hp; a.gx_hp = Hp;
+                    }
                     GGPM_TRY(launch_gemm_f16(a, st));
                     GemmArgs q;
                     q.Ah_hi = hp_hi; q.Ah_lo = hp_hi + 2 * row; q.lda_h = Hp; q.a_scale = fw.scal + 6;      // = 2^13
@@ -412,7 +427,8 @@ extern "C" int ggpm_lstm_fwd(int E1, int H, int Hp, int depth, const int32_t* b_
             GGPM_TRY(gemm_nt(s_scratch, Hp, Ug, Hp, gp, 4 * Hp, E1, 3 * Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
             GGPM_TRY(gemm_nt(h_prev, Hp, Uf, Hp, gp + 3 * Hp, 4 * Hp, E1, Hp, Hp, 0.f, nullptr, GGPM_ACT_NONE, 0, st));
         }
-        GGPM_TRY(launch_lstm_cell_fwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, h_out, c_cur, h16_hi, h16_lo, st));
+        GGPM_TRY(launch_lstm_cell_fwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, h_out, c_cur, h16_hi, h16_lo, st,
+                                      planes_only && fused_gates()));
     }
     return 0;
 }
@@ -460,6 +476,8 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
     // pair mode (plane path only): the two per-pair terms of a round are stored in pair order and gathered over the
     // reverse CSR where they are consumed, instead of being reduced into zeroed tables with atomics
     // pair_buf: [3, pair_rows, Hp] = daf pairs | dchat * f pairs of even rounds | of odd rounds; pair_rows >= nnz
+    // the forward kept ACTIVATED gates in hist_gp on the plane-fed path when GGPM_FUSED_GATES is on (same predicate as there)
+    const bool gates_act = fused_gates() && zmode && fused_w && tc_ok && E1 >= sgather_min_rows() && Hp % 64 == 0;
     const bool pairs = zmode && bt_pos != nullptr && pair_buf != nullptr && pair_rows > 0 && ((uintptr_t)pair_buf & 15) == 0;
     const size_t pair_slot = (size_t)(pair_rows > 0 ? pair_rows : 0) * Hp;
     SideStream* side = zmode ? side_stream() : nullptr;
@@ -484,7 +502,7 @@ extern "C" int ggpm_lstm_bwd(int E1, int H, int Hp, int depth, const int32_t* b_
         // the cell kernel also records max |gate-gradient term| of this round (16 slots): the scale of the f16x3 GEMM
         float* amax_t = f16 ? fw.scal + 16 + 16 * (size_t)t : nullptr;
         GGPM_TRY(launch_lstm_cell_bwd(false, E1, H, Hp, b_ptr, b_col, x, gp, c_prev, c_cur, dH, dC_dense, dP, dC_prev, amax_t, st,
-                                      bt_ptr, bt_pos, pairB_in, pairA, pairB, pairs));
+                                      bt_ptr, bt_pos, pairB_in, pairA, pairB, pairs, gates_act));
         if (zmode) {
             // Z = [gather^T(dA[:, :3Hp]) | dP] as scaled fp16 planes; then dH^{t-1} = Z [Ug; Uf] and
             // [dUg; dUf] += Z^T h^{t-1}: two plain GEMMs whose operands all arrive by TMA

@@ -44,7 +44,9 @@ __device__ __forceinline__ float4 xval(const XRow& r, int off) {
 // ------------------------------------------------------------------------------------------------
 // NC = column chunks (128 columns each) a lane works on together: with NC = 2 (Hp a multiple of 256, the shipped width) the
 // neighbour ids are loaded once for both chunks and twice as many gathered rows are in flight per warp.
-template <bool FIRST, int NC>
+// ACT: the round's gate block of gp already holds the ACTIVATED gates [i|o|u] (the gate GEMM applied the x-projection, the
+// non-linearities and the row-0 mask in its epilogue): only the per-neighbour forget gate is evaluated here.
+template <bool FIRST, int NC, bool ACT>
 __global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
                      const float* __restrict__ gp, const float* __restrict__ c_prev, float* __restrict__ h_out,
@@ -69,26 +71,35 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
     const float* ge = gp + (size_t)e * ld4h;
     for (int c0 = lane * 4; c0 < Hp; c0 += 128 * NC) {
         float4 ai[NC], ao[NC], au[NC], chat[NC];
+        if (!(ACT && !FIRST)) {
 #pragma unroll
-        for (int k = 0; k < NC; ++k) {
-            const int c = c0 + 128 * k;
-            ai[k] = xval(xr, c); ao[k] = xval(xr, Hp + c); au[k] = xval(xr, 2 * Hp + c);
+            for (int k = 0; k < NC; ++k) {
+                const int c = c0 + 128 * k;
+                ai[k] = xval(xr, c); ao[k] = xval(xr, Hp + c); au[k] = xval(xr, 2 * Hp + c);
+            }
         }
         if (FIRST) {
 #pragma unroll
-            for (int k = 0; k < NC; ++k) chat[k] = sigmoid4(ai[k]) * tanh4(au[k]);
+            for (int k = 0; k < NC; ++k) { chat[k] = sigmoid4(ai[k]) * tanh4(au[k]); ao[k] = sigmoid4(ao[k]); }
         } else {
             float4 xf[NC];
 #pragma unroll
             for (int k = 0; k < NC; ++k) {
                 const int c = c0 + 128 * k;
-                ai[k] += ld4(ge + c);
-                ao[k] += ld4(ge + Hp + c);
-                au[k] += ld4(ge + 2 * Hp + c);
+                if (ACT) {
+                    chat[k] = ld4(ge + c) * ld4(ge + 2 * Hp + c);        // i * u, both activated by the GEMM epilogue
+                    ao[k] = ld4(ge + Hp + c);                             // o
+                } else {
+                    ai[k] += ld4(ge + c);
+                    ao[k] += ld4(ge + Hp + c);
+                    au[k] += ld4(ge + 2 * Hp + c);
+                }
                 xf[k] = xval(xr, 3 * Hp + c);
             }
+            if (!ACT) {
 #pragma unroll
-            for (int k = 0; k < NC; ++k) chat[k] = sigmoid4(ai[k]) * tanh4(au[k]);
+                for (int k = 0; k < NC; ++k) { chat[k] = sigmoid4(ai[k]) * tanh4(au[k]); ao[k] = sigmoid4(ao[k]); }
+            }
             int j = b;
             if (NC == 1) {
                 for (; j + 2 <= en; j += 2) {
@@ -115,7 +126,7 @@ lstm_cell_fwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
         for (int k = 0; k < NC; ++k) {
             const int c = c0 + 128 * k;
             const float4 ch = clip_cols(chat[k], c, H);
-            const float4 h = clip_cols(sigmoid4(ao[k]) * tanh4(ch), c, H);
+            const float4 h = clip_cols(ao[k] * tanh4(ch), c, H);       // ao holds the activated output gate here
             st4(c_out + (size_t)e * Hp + c, ch);
             if (h_out) st4(h_out + (size_t)e * Hp + c, h);      // large layers read h through the fp16 planes below only
             if (h16_hi) {   // fp16 hi / lo planes of h * 2^13 (|h| <= 1): the B operand of the f16x3 weight-gradient GEMM
@@ -253,7 +264,8 @@ lstm_sgather16_kernel(int E1, int Hp, const int* __restrict__ rp, const int* __r
 // the pairs of a row are consecutive) and summed where they are consumed, through the reverse CSR: dP by the zgather kernel
 // of this round, dC of the previous round's rows by THIS kernel one round later (tp / tpos / pairB_in).  Same bytes as the
 // zero + reduce + re-read they replace, but plain stores and gathers: no atomics, one launch less per round.
-template <bool FIRST, bool PAIRS>
+// ACT: the gate block of gp holds the activated gates (see the forward kernel): nothing to recompute for i, o, u.
+template <bool FIRST, bool PAIRS, bool ACT>
 __global__ void __launch_bounds__(kCellWarps * 32, kCellMinBlocks)
 lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const int* __restrict__ col, XTab xt,
                      float* gp, const float* __restrict__ c_prev, float* c_cur,
@@ -280,13 +292,18 @@ lstm_cell_bwd_kernel(int E1, int H, int Hp, const int* __restrict__ rp, const in
     const int tb = (PAIRS && pairB_in != nullptr) ? __ldg(tp + e) : 0, te = (PAIRS && pairB_in != nullptr) ? __ldg(tp + e + 1) : 0;
     const float4 one = make_float4(1.f, 1.f, 1.f, 1.f);
     for (int c = lane * 4; c < Hp; c += 128) {
-        float4 ai = xval(xr, c), ao = xval(xr, Hp + c), au = xval(xr, 2 * Hp + c);
-        if (!FIRST) {
-            ai += ld4(ge + c);
-            ao += ld4(ge + Hp + c);
-            au += ld4(ge + 2 * Hp + c);
+        float4 gi, go, gu;
+        if (ACT && !FIRST) {
+            gi = ld4(ge + c); go = ld4(ge + Hp + c); gu = ld4(ge + 2 * Hp + c);
+        } else {
+            float4 ai = xval(xr, c), ao = xval(xr, Hp + c), au = xval(xr, 2 * Hp + c);
+            if (!FIRST) {
+                ai += ld4(ge + c);
+                ao += ld4(ge + Hp + c);
+                au += ld4(ge + 2 * Hp + c);
+            }
+            gi = sigmoid4(ai); go = sigmoid4(ao); gu = tanh4(au);
         }
-        const float4 gi = sigmoid4(ai), go = sigmoid4(ao), gu = tanh4(au);
         const float4 th = tanh4(ld4(ce + c));
         const float4 dh = clip_cols(ld4(dH + (size_t)e * Hp + c), c, H);
         float4 dchat = dh * go * (one - th * th);
@@ -621,12 +638,13 @@ static int cell_fwd_chunks(int Hp) {
 
 int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          const float* gp, const float* c_prev, float* h_out, float* c_out, void* h16_hi, void* h16_lo,
-                         cudaStream_t st) {
+                         cudaStream_t st, bool gates_activated) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_FWD, st, 0.0);
-    const bool two = cell_fwd_chunks(Hp) == 2;
-    auto kern = first ? (two ? lstm_cell_fwd_kernel<true, 2> : lstm_cell_fwd_kernel<true, 1>)
-                      : (two ? lstm_cell_fwd_kernel<false, 2> : lstm_cell_fwd_kernel<false, 1>);
+    const bool two = cell_fwd_chunks(Hp) == 2 && !gates_activated;
+    auto kern = first ? (two ? lstm_cell_fwd_kernel<true, 2, false> : lstm_cell_fwd_kernel<true, 1, false>)
+                      : (gates_activated ? lstm_cell_fwd_kernel<false, 1, true>
+                                         : (two ? lstm_cell_fwd_kernel<false, 2, false> : lstm_cell_fwd_kernel<false, 1, false>));
     launch_pdl(kern, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0,
                st, E1, H, Hp, rp, col, xt, gp, c_prev, h_out, c_out, (uint2*)h16_hi, (uint2*)h16_lo);
     return check_launch("lstm_cell_fwd");
@@ -652,11 +670,13 @@ int launch_lstm_sgather16(int E1, int Hp, const int* b_ptr, const int* b_col, co
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          float* gp, const float* c_prev, float* c_cur, const float* dH, const float* dC,
                          float* dP, float* dC_prev, float* amax16, cudaStream_t st, const int* t_ptr, const int* t_pos,
-                         const float* pairB_in, float* pairA, float* pairB, bool pairs) {
+                         const float* pairB_in, float* pairA, float* pairB, bool pairs, bool gates_activated) {
     XTab xt{x.Yn, x.src, x.T, x.k1, x.k2, 4 * Hp};
     ProfScope prof(PROF_CELL_BWD, st, 0.0);
-    auto kern = pairs ? (first ? lstm_cell_bwd_kernel<true, true> : lstm_cell_bwd_kernel<false, true>)
-                      : (first ? lstm_cell_bwd_kernel<true, false> : lstm_cell_bwd_kernel<false, false>);
+    auto kern = lstm_cell_bwd_kernel<false, false, false>;
+    if (first) kern = pairs ? lstm_cell_bwd_kernel<true, true, false> : lstm_cell_bwd_kernel<true, false, false>;
+    else if (gates_activated) kern = pairs ? lstm_cell_bwd_kernel<false, true, true> : lstm_cell_bwd_kernel<false, false, true>;
+    else if (pairs) kern = lstm_cell_bwd_kernel<false, true, false>;
     launch_pdl(kern, dim3(cell_blocks_persistent(E1)), dim3(kCellWarps * 32), 0, st, E1, H, Hp, rp, col, xt, gp, c_prev, c_cur, dH,
                dC, dP, dC_prev, amax16, t_ptr, t_pos, pairB_in, pairA, pairB);
     return check_launch("lstm_cell_bwd");

@@ -529,6 +529,8 @@ struct F16Params {
     const int* a_deg;
     const float* a_scale;                  // when given: the A scale itself (A already is fp16 planes)
     const float* b_scale; float b_scale_const;
+    // GGPM_ACT_LSTM_GATES epilogue: the hoisted x-projection tables (see GemmArgs)
+    const float* gx_Yn; const int* gx_src; const float* gx_T; const int* gx_k1; const int* gx_k2; int gx_ld, gx_hp;
 #ifdef GGPM_TRACE
     unsigned long long* dbg;               // [gridDim.x][8] globaltimer stamps; only in -DGGPM_TRACE builds (tools/f16_trace.py)
 #endif
@@ -921,7 +923,19 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_f16_kernel(const F16Params fp
                                 x.x += p.beta * o.x; x.y += p.beta * o.y; x.z += p.beta * o.z; x.w += p.beta * o.w;
                             }
                             x += bias4;
-                            if (p.act == GGPM_ACT_RELU) x = make_float4(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f), fmaxf(x.z, 0.f), fmaxf(x.w, 0.f));
+                            if (p.act == GGPM_ACT_LSTM_GATES) {
+                                // gate non-linearities and padding mask of the graph LSTM in the GEMM epilogue
+                                // (ggpm/rnn.py:88-89, 91, 106): add the hoisted x-projection of this message, sigmoid
+                                // for the input / output gates, tanh for the candidate
+                                const int row = row_base + rr;
+                                float4 xv = ldg4(fp.gx_Yn + (size_t)__ldg(fp.gx_src + row) * fp.gx_ld + n) +
+                                            ldg4(fp.gx_T + (size_t)__ldg(fp.gx_k1 + row) * fp.gx_ld + n);
+                                if (fp.gx_k2 != nullptr) xv += ldg4(fp.gx_T + (size_t)__ldg(fp.gx_k2 + row) * fp.gx_ld + n);
+                                x = xv + x;
+                                x = n < 2 * fp.gx_hp ? sigmoid4(x) : tanh4(x);
+                                if (row == 0) x = f4zero();
+                            }
+                            else if (p.act == GGPM_ACT_RELU) x = make_float4(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f), fmaxf(x.z, 0.f), fmaxf(x.w, 0.f));
                             else if (p.act == GGPM_ACT_TANH) x = tanh4(x);
                             else if (p.act == GGPM_ACT_SIGMOID) x = sigmoid4(x);
                             if (p.zero_row0 && row_base + rr == 0) x = f4zero();
@@ -1226,6 +1240,11 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
     p.beta = g.beta; p.bias = g.bias; p.act = g.act; p.zero_row0 = g.zero_row0;
     fp.a_amax = g.a_amax; fp.a_amax_n = g.a_amax_n; fp.a_amax_const = g.a_amax_const; fp.a_deg = g.a_deg;
     fp.a_scale = g.a_scale; fp.b_scale = g.b_scale; fp.b_scale_const = g.b_scale_const;
+    fp.gx_Yn = g.gx_Yn; fp.gx_src = g.gx_src; fp.gx_T = g.gx_T; fp.gx_k1 = g.gx_k1; fp.gx_k2 = g.gx_k2;
+    fp.gx_ld = g.gx_ld; fp.gx_hp = g.gx_hp;
+    GGPM_REQUIRE(g.act != GGPM_ACT_LSTM_GATES || (g.gx_Yn && g.gx_src && g.gx_T && g.gx_k1 && g.gx_hp > 0 && g.gx_hp % 4 == 0 &&
+                                                 g.gx_ld % 4 == 0 && g.beta == 0.f && g.N <= 3 * g.gx_hp),
+                 "gemm_f16x3: the LSTM-gate epilogue needs the x-projection tables");
 #ifdef GGPM_TRACE
     fp.dbg = nullptr;
     if (const char* tr = getenv("GGPM_F16_TRACE")) fp.dbg = (unsigned long long*)strtoull(tr, nullptr, 0);

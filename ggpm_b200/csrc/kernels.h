@@ -43,7 +43,13 @@ struct GemmArgs {
     const float* a_scale = nullptr;
     float b_scale_const = 1.f;   // used when b_scale is NULL
     int f16_tn = 0;
+    // act = GGPM_ACT_LSTM_GATES (f16x3 engine, fused epilogue): C[e, n] = s(acc + X[e, n]) for n < 2 * gx_hp (input and
+    // output gates, sigmoid) and tanh(...) for the candidate block, row 0 forced to zero, with the hoisted x-projection
+    // X[e, n] = gx_Yn[gx_src[e], n] + gx_T[gx_k1[e], n] (+ gx_T[gx_k2[e], n]), row stride gx_ld (ggpm/rnn.py:88-89,91,106)
+    const float* gx_Yn = nullptr; const int* gx_src = nullptr; const float* gx_T = nullptr;
+    const int* gx_k1 = nullptr; const int* gx_k2 = nullptr; int gx_ld = 0, gx_hp = 0;
 };
+constexpr int GGPM_ACT_LSTM_GATES = 4;   // internal to the library (not a public activation code)
 
 int launch_gemm_simt(const GemmArgs& g, cudaStream_t st);
 // generic entry: tcgen05 3xTF32 kernel when the operand layout allows it, else the fp32 CUDA-core kernel
@@ -75,12 +81,12 @@ struct XTabArgs {   // hoisted x-projection: X_g[e] = Yn[src[e], g] + T[k1[e], g
 
 int launch_lstm_cell_fwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          const float* gp, const float* c_prev, float* h_out, float* c_out, void* h16_hi, void* h16_lo,
-                         cudaStream_t st);
+                         cudaStream_t st, bool gates_activated = false);
 int launch_lstm_cell_bwd(bool first, int E1, int H, int Hp, const int* rp, const int* col, const XTabArgs& x,
                          float* gp, const float* c_prev, float* c_cur, const float* dH, const float* dC,
                          float* dP, float* dC_prev, float* amax16, cudaStream_t st, const int* t_ptr = nullptr,
                          const int* t_pos = nullptr, const float* pairB_in = nullptr, float* pairA = nullptr,
-                         float* pairB = nullptr, bool pairs = false);
+                         float* pairB = nullptr, bool pairs = false, bool gates_activated = false);
 int launch_lstm_sgather16(int E1, int Hp, const int* b_ptr, const int* b_col, const void* h_hi, const void* h_lo, const int* deg,
                           void* s_hi, void* s_lo, float* scale_out, cudaStream_t st);
 int launch_lstm_dx_reduce(int E1, int Hp, int depth, const float* hist_gp, const float* hist_c, float* dX, cudaStream_t st);

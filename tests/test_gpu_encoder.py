@@ -128,3 +128,17 @@ def test_atomic_free_backward_matches_golden():
                        capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
     assert " passed" in r.stdout
+
+
+def test_gate_nonlinearities_in_the_gemm_epilogue_match_golden():
+    """GGPM_FUSED_GATES=1: on the plane-fed path the forward gate GEMM applies the x-projection, sigmoid / tanh and the row-0
+    mask in its tcgen05 epilogue and the cell kernels only evaluate the per-neighbour forget gate (forward and backward read
+    the activated gates from the history).  With GGPM_SGATHER_MIN_ROWS=0 every golden takes that path; both switches are
+    read once per process, so the checks run in a child process."""
+    import subprocess
+    env = dict(os.environ, GGPM_FUSED_GATES="1", GGPM_SGATHER_MIN_ROWS="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider",
+                        "-k", "cfg1_matches or (forward_backward_matches and auto and lstm) or (fixed_dropout and lstm)"], env=env,
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
+    assert " passed" in r.stdout
