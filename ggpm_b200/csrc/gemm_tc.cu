@@ -60,6 +60,9 @@ struct TcParams {
     int m_tiles, n_tiles, total_tiles, tiles_full;
     int split_s;       // > 0 (fewer tiles than SMs): every tile is cut along K into split_s equal parts, one CTA each
     int epi_mode;
+    int seg_cap;       // stream-K segments are at most this many K chunks long (0: unbounded).  A tensor-core accumulator
+                       // truncates every partial sum it holds, so its error grows with the number of MMA steps chained into it;
+                       // capping the chain and adding the pieces in fp32 (the reduce-add epilogue) bounds it — DESIGN.md 4.2
 };
 
 template <int BN> struct Cfg {
@@ -259,6 +262,7 @@ struct SegIter {
             t = p.tiles_full + u / p.nk;
             c0 = u % p.nk;
             c1 = min(p.nk, c0 + (u_end - u));
+            if (p.seg_cap > 0) c1 = min(c1, c0 + p.seg_cap);
             u += c1 - c0;
             sg.partial = true;
         } else {
@@ -1119,6 +1123,17 @@ bool gemm_tc_eligible(const GemmArgs& g) {
     return true;
 }
 
+// GGPM_SEG_CAP: longest accumulation chain, in K chunks, a stream-K segment may hold (default 16; 0 = unbounded)
+static int seg_cap_chunks() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("GGPM_SEG_CAP");
+        int c = e != nullptr ? atoi(e) : 16;
+        v = c < 0 ? 0 : c;
+    }
+    return v;
+}
+
 int launch_gemm_tc(const GemmArgs& g, cudaStream_t st) {
     GGPM_REQUIRE(gemm_tc_eligible(g), "gemm_tcgen05: operand layout not supported (alignment / strides)");
     const bool a_kc = (g.sak == 1), b_kc = (g.sbk == 1);
@@ -1148,6 +1163,7 @@ int launch_gemm_tc(const GemmArgs& g, cudaStream_t st) {
     const int bnf = wide ? 256 : 128;
     p.split_s = 0;
     p.nk = ceil_div(g.K, BK);
+    p.seg_cap = seg_cap_chunks();
     p.m_tiles = ceil_div(g.M, BM);
     p.n_tiles = ceil_div(g.N, bnf);
     p.total_tiles = p.m_tiles * p.n_tiles;
@@ -1274,6 +1290,7 @@ int launch_gemm_f16(const GemmArgs& g, cudaStream_t st) {
     if (g.split_dim == SPLIT_N && g.split_at % 256 != 0) wide = false;
     const int bnf = wide ? 256 : 128;
     p.nk = ceil_div(g.K, BK16);
+    p.seg_cap = seg_cap_chunks();
     p.m_tiles = ceil_div(g.M, BM);
     p.n_tiles = ceil_div(g.N, bnf);
     p.total_tiles = p.m_tiles * p.n_tiles;

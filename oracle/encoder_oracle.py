@@ -60,8 +60,21 @@ def _affine(sd: Dict[str, Tensor], name: str, x: Tensor) -> Tensor:
     return y if b is None else y + b
 
 
+# Full-size comparisons (tests/test_gpu_parity_full.py) evaluate the oracle in fp64 on the GPU, where the padded [E, K, H]
+# intermediates of every depth round would not fit if autograd kept them all: with this flag each round is recomputed
+# in the backward pass (torch.utils.checkpoint) — same arithmetic, same results (tests/test_oracle_golden.py).
+CHECKPOINT_ROUNDS = False
+
+
+def _round(fn, *state):
+    if CHECKPOINT_ROUNDS and torch.is_grad_enabled():
+        from torch.utils.checkpoint import checkpoint
+        return checkpoint(fn, *state, use_reentrant=False)
+    return fn(*state)
+
+
 def _row0_mask(rows: int, like: Tensor) -> Tensor:
-    m = torch.ones(rows, 1, dtype=like.dtype)
+    m = torch.ones(rows, 1, dtype=like.dtype, device=like.device)
     m[0, 0] = 0
     return m
 
@@ -69,10 +82,11 @@ def _row0_mask(rows: int, like: Tensor) -> Tensor:
 def lstm_messages(sd, prefix: str, x: Tensor, bgraph: Tensor, depth: int) -> Tuple[Tensor, Tensor]:
     """ggpm/rnn.py:96-108 with the cell of ggpm/rnn.py:85-94.  Keys: prefix + W_i.0 / W_o.0 / W_f.0 / W.0"""
     hidden = sd[prefix + "W_i.0.weight"].shape[0]
-    h = torch.zeros(x.shape[0], hidden, dtype=x.dtype)
+    h = torch.zeros(x.shape[0], hidden, dtype=x.dtype, device=x.device)
     c = torch.zeros_like(h)
     mask = _row0_mask(x.shape[0], x)
-    for _ in range(depth):
+
+    def one_round(h, c):
         h_nb = gather_padded(h, bgraph)                   # [E, K, H]
         c_nb = gather_padded(c, bgraph)
         xs = torch.cat([x, h_nb.sum(1)], dim=-1)          # [E, IN + H]
@@ -83,17 +97,20 @@ def lstm_messages(sd, prefix: str, x: Tensor, bgraph: Tensor, depth: int) -> Tup
         gate_f = torch.sigmoid(_affine(sd, prefix + "W_f.0", torch.cat([x_rep, h_nb], dim=-1)))
         c = gate_i * cand + (gate_f * c_nb).sum(1)
         h = gate_o * torch.tanh(c)
-        h = h * mask
-        c = c * mask
+        return h * mask, c * mask
+
+    for _ in range(depth):
+        h, c = _round(one_round, h, c)
     return h, c
 
 
 def gru_messages(sd, prefix: str, x: Tensor, bgraph: Tensor, depth: int) -> Tensor:
     """ggpm/rnn.py:41-50 with the cell of ggpm/rnn.py:25-39.  Keys: prefix + W_z / W_r / U_r / W_h"""
     hidden = sd[prefix + "W_z.weight"].shape[0]
-    h = torch.zeros(x.shape[0], hidden, dtype=x.dtype)
+    h = torch.zeros(x.shape[0], hidden, dtype=x.dtype, device=x.device)
     mask = _row0_mask(x.shape[0], x)
-    for _ in range(depth):
+
+    def one_round(h):
         h_nb = gather_padded(h, bgraph)
         s = h_nb.sum(1)
         z = torch.sigmoid(_affine(sd, prefix + "W_z", torch.cat([x, s], dim=-1)))
@@ -101,7 +118,10 @@ def gru_messages(sd, prefix: str, x: Tensor, bgraph: Tensor, depth: int) -> Tens
         sg = (r * h_nb).sum(1)
         cand = torch.tanh(_affine(sd, prefix + "W_h", torch.cat([x, sg], dim=-1)))
         h = (1.0 - z) * s + z * cand
-        h = h * mask
+        return h * mask
+
+    for _ in range(depth):
+        h = _round(one_round, h)
     return h
 
 
@@ -133,12 +153,12 @@ def mpn_layer(sd, prefix: str, rnn_type: str, fnode: Tensor, fmess: Tensor, agra
 
 
 def _onehot(index: Tensor, width: int, dtype) -> Tensor:
-    return torch.eye(width, dtype=dtype).index_select(0, index)
+    return torch.eye(width, dtype=dtype, device=index.device).index_select(0, index)
 
 
 def _root_vectors(sd, node_feat: Tensor, hmess: Tensor, agraph: Tensor, scope) -> Tensor:
     """ggpm/encoder.py:128-138 (and 319-328): W_root([feat[root] | sum of messages into root]), tanh."""
-    roots = torch.tensor([st for st, _ in scope], dtype=torch.long)
+    roots = torch.tensor([st for st, _ in scope], dtype=torch.long, device=agraph.device)
     feat = node_feat.index_select(0, roots)
     incoming = gather_padded(hmess, agraph.index_select(0, roots)).sum(1)
     return torch.tanh(_affine(sd, "W_root.0", torch.cat([feat, incoming], dim=-1)))

@@ -65,6 +65,32 @@ def test_oracle_cfg1_outputs():
         assert abs(float(p.grad.norm()) - float(z["gnorm_" + k])) <= 1e-10 * max(1.0, float(z["gnorm_" + k]))
 
 
+@pytest.mark.parametrize("name", ["hier_lstm_deep", "hier_gru_small"])
+def test_checkpointed_rounds_give_the_same_oracle(name):
+    """CHECKPOINT_ROUNDS (used by the GPU-evaluated full-size comparisons) recomputes each depth round in the backward
+    pass: same arithmetic, so outputs are identical and gradients agree to fp64 rounding"""
+    if name not in golden_names():
+        pytest.skip("no such golden case")
+    meta, z, tree, graph = load_golden(name)
+    names = OUT_NAMES[meta["kind"]]
+    res = []
+    for flag in (False, True):
+        eo.CHECKPOINT_ROUNDS = flag
+        try:
+            sd, outs = _oracle_run(meta, tree, graph, torch.float64)
+            sum((o * torch.from_numpy(z["cot_" + n])).sum() for n, o in zip(names, outs)).backward()
+        finally:
+            eo.CHECKPOINT_ROUNDS = False
+        res.append(([o.detach() for o in outs], {k: p.grad for k, p in sd.items()}))
+    for a, b in zip(res[0][0], res[1][0]):
+        assert torch.equal(a, b)
+    for k, g in res[0][1].items():
+        if g is None:
+            assert res[1][1][k] is None
+        else:
+            assert _rel(res[1][1][k].numpy(), g.numpy()) <= 1e-13, k
+
+
 def test_oracle_fp32_close_to_fp64():
     meta, z, tree, graph = load_golden("hier_lstm_deep")
     _, outs = _oracle_run(meta, tree, graph, torch.float32)
