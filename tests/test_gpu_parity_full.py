@@ -20,7 +20,9 @@ both recorded in gpurun_out/parity_report.json:
     has an fp64 pre-activation below 1e-5 of the site's scale, and that there are at most max(16, units / 250 000)
     of them, and (3) re-runs
     the fp64 oracle on the product's pattern (`relu=` of oracle/encoder_oracle.py: gradient of a prescribed linear
-    branch) and holds every gradient to 1e-5 against THAT.  A wrong kernel fails (2) or (3); a kink passes both.
+    branch) and holds every gradient to 1e-5 against THAT (relaxed, as above, to twice the gap of the reference's fp32
+    arithmetic evaluated on the same branch where that gap exceeds 5e-6).  A wrong kernel fails (2) or (3); a kink
+    passes both.
 """
 import os
 import sys
@@ -129,7 +131,7 @@ def _compare(tag, kind, rnn, H, depth, B, seed, loss, min_atom_rows=0, oracle_de
                                 raise_on_bad=False)
     out_names = set(C.OUT_NAMES[kind])
     assert not [b for b in bad if b[0] in out_names], bad             # outputs are continuous across a kink: no excuse
-    if bad:
+    if bad or oracle_device != "cpu":          # sweep-size batches: always also record the kink-free comparison
         _kink_analysis(tag, kind, rnn, depth, sd, tree_np, graph_np, loss, masks, trace, outs, ref_outs, grads, bad,
                        oracle_device)
 
@@ -149,13 +151,17 @@ def _kink_analysis(tag, kind, rnn, depth, sd, tree_np, graph_np, loss, masks, tr
             worst_pre = max(worst_pre, float(pre[diff].abs().max() / pre.abs().max()))
     max_flips = max(16, n_units // 250000)            # units within fp32 rounding of zero scale with the unit count
     C.record(tag, "kink:flipped_relu_units", flips, max_flips, relu_units=n_units, max_flipped_preactivation_rel=worst_pre,
-             first_mismatch=str(bad[0]))
-    assert 0 < flips <= max_flips, ("gradient mismatch without a ReLU pattern difference" if flips == 0 else "too many flips", flips, bad)
+             first_mismatch=str(bad[0]) if bad else None)
+    assert (0 if not bad else 1) <= flips <= max_flips, ("gradient mismatch without a ReLU pattern difference" if flips == 0 else "too many flips", flips, bad)
     assert worst_pre <= 1e-5, ("a unit far from its kink took the other branch", worst_pre, bad)
     _, branch_grads, _ = _oracle(kind, rnn, depth, depth, sd, tree_np, graph_np, torch.float64, loss,
                                  relu={k: v.double() for k, v in masks.items()}, device=oracle_device)
+    # the reference arithmetic in fp32 on the SAME branch: its gap to fp64 is the measured fp32 noise of this tensor
+    # (tests/_checks.py grad_tolerance), free of kink effects
+    _, branch_grads32, _ = _oracle(kind, rnn, depth, depth, sd, tree_np, graph_np, torch.float32, loss,
+                                   relu={k: v.float() for k, v in masks.items()}, device=oracle_device)
     C.compare_with_oracle(tag + ":on_product_relu_pattern", C.OUT_NAMES[kind], outs, ref_outs, grads, branch_grads,
-                          skip_outputs=True)
+                          branch_grads32, skip_outputs=True)
 
 
 def test_hidden_500_depth_20_matches_fp64_oracle():
