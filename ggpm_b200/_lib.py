@@ -54,6 +54,7 @@ SIGNATURES = {
     "ggpm_gru_fwd": (I, [I, I, I, I] + [P] * 13 + [I, P]),
     "ggpm_gru_bwd": (I, [I, I, I, I] + [P] * 24),
     "ggpm_rsample_fwd": (I, [P, I, I, P, I, I, I, P, I, P, P, P]),
+    "ggpm_rsample_fwd_noalloc": (I, [P, I, I, P, I, I, I, P, I, P, P]),
     "ggpm_rsample_bwd": (I, [P, I, I, P, I, I, I, P, I, P, P, I, I, P]),
     "ggpm_mlp_heads_fwd": (I, [P, I, I, I, I, I, I, P]),
     "ggpm_mlp_heads_bwd": (I, [P, P, I, I, I, I, I, I, I, P]),

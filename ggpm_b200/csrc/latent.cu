@@ -79,6 +79,49 @@ extern "C" int ggpm_rsample_fwd(const float* Y, int ldy, int var_off, const floa
     return check_launch("rsample_fwd", 2);
 }
 
+// ---- allocation-free variant ----------------------------------------------------------------------------------------
+// Same two kernels as ggpm_rsample_fwd, with the per-row KL scratch in a file-scope device array instead of a caller
+// buffer, for callers that cannot allocate (CUDA graph capture, serving loops).  No counterpart in the reference.
+// The array is part of the module image: every GPU that loads the library holds kRowKlMax floats (256 KiB) until exit.
+// All calls on a device share it and it keeps the last call's contents; every element a call reads (rows [0, B)) is
+// written by that call's first kernel before its second kernel reads it, so nothing needs clearing — but two calls
+// whose kernels overlap on the GPU (different streams, no ordering) race on it.
+constexpr int kRowKlMax = 65536;
+static __device__ __align__(256) float g_row_kl_scratch[kRowKlMax];
+
+constexpr int kMaxDevices = 64;
+static float* g_row_kl_addr[kMaxDevices];          // device address of the array, per device (0: not looked up yet)
+
+// In host code `g_row_kl_scratch` is only a handle: the device address comes from cudaGetSymbolAddress, asked once per
+// device with that device current.
+static int row_kl_scratch(float** out) {
+    int dev = -1;
+    GGPM_CUDA(cudaGetDevice(&dev));
+    GGPM_REQUIRE(dev >= 0 && dev < kMaxDevices, "rsample_fwd_noalloc: device ordinal %d out of range", dev);
+    float* p = __atomic_load_n(&g_row_kl_addr[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        GGPM_CUDA(cudaGetSymbolAddress((void**)&p, g_row_kl_scratch));
+        GGPM_REQUIRE(p != nullptr, "rsample_fwd_noalloc: no device address for the scratch array");
+        __atomic_store_n(&g_row_kl_addr[dev], p, __ATOMIC_RELEASE);      // same value from every thread
+    }
+    *out = p;
+    return 0;
+}
+
+extern "C" int ggpm_rsample_fwd_noalloc(const float* Y, int ldy, int var_off, const float* eps, int ld_eps, int B, int L,
+                                        float* z, int ldz, float* kl, void* stream) {
+    GGPM_REQUIRE(Y && z && kl, "rsample_fwd_noalloc: null pointer");
+    GGPM_REQUIRE(B >= 1 && L >= 1 && var_off >= L && ldy >= var_off + L && ldz >= L, "rsample_fwd_noalloc: bad sizes");
+    GGPM_REQUIRE(B <= kRowKlMax, "rsample_fwd_noalloc: %d rows exceed the built-in scratch (at most %d); use ggpm_rsample_fwd "
+                 "with a caller-provided row_kl buffer", B, kRowKlMax);
+    float* row_kl = nullptr;
+    GGPM_TRY(row_kl_scratch(&row_kl));
+    cudaStream_t st = (cudaStream_t)stream;
+    rsample_fwd_kernel<<<ceil_div(B, 8), 256, 0, st>>>(Y, ldy, var_off, eps, ld_eps, B, L, z, ldz, row_kl);
+    rsample_kl_kernel<<<1, 256, 0, st>>>(row_kl, B, kl);
+    return check_launch("rsample_fwd_noalloc", 2);
+}
+
 extern "C" int ggpm_rsample_bwd(const float* Y, int ldy, int var_off, const float* eps, int ld_eps, int B, int L,
                                 const float* dz, int ld_dz, const float* dkl, float* dY, int ld_dy, int width, void* stream) {
     GGPM_REQUIRE(Y && dY, "rsample_bwd: null pointer");

@@ -265,6 +265,18 @@ int ggpm_rsample_fwd(const float* Y, int ldy, int var_off, const float* eps, int
 int ggpm_rsample_bwd(const float* Y, int ldy, int var_off, const float* eps, int ld_eps, int B, int L, const float* dz,
                      int ld_dz, const float* dkl, float* dY, int ld_dy, int width, void* stream);
 
+/* Allocation-free variant of ggpm_rsample_fwd.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid allocation).  Same arguments and results as ggpm_rsample_fwd minus row_kl: the per-row KL scratch is a
+ * file-scope `static __device__` array of 65 536 floats (256 KiB, held by every GPU that loads the library until exit),
+ * whose device address the library obtains once per device with cudaGetSymbolAddress.  B > 65 536 is rejected with an
+ * error (use ggpm_rsample_fwd with a caller buffer).  The call makes no cudaMalloc / cudaFree / allocating library
+ * call.  All calls on a device share the array: calls whose kernels may overlap on the GPU (different streams without
+ * ordering) race on it; calls ordered on one stream are safe, and nothing has to be cleared between them (each call
+ * writes rows [0, B) before reading them). */
+int ggpm_rsample_fwd_noalloc(const float* Y, int ldy, int var_off, const float* eps, int ld_eps, int B, int L, float* z,
+                             int ldz, float* kl, void* stream);
+
 /* ---- property heads behind the latent head ---------------------------------------------------
  * PropertyOptimizer of ggpm/property_optimizer.py:5-51 in its shipped shape: two one-hidden-layer regressors (HOMO,
  * LUMO; PropertyRegressor :54-66) on [B, In] inputs,  a = relu(W1 x + b1),  y = w2 . (a * mult) + b2,  loss = mean
