@@ -1478,8 +1478,57 @@ int launch_tf32_split_transpose(const float* w, int rows, int cols, float* hi, f
 }
 
 // generic entry: tensor cores when the layout allows, else the fp32 CUDA-core kernel
+// GGPM_GLUE_KSLICE: K-slice length of the generic tcgen05 GEMMs (default 256; 0 = unsliced);
+// GGPM_GLUE_KSLICE_MIN_ROWS: only GEMMs with at least this many rows are sliced (default 4096)
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    const int c = e != nullptr ? atoi(e) : dflt;
+    return c < 0 ? 0 : c;
+}
+static int glue_kslice() {
+    static int v = -1;
+    if (v < 0) v = (env_int("GGPM_GLUE_KSLICE", 256) / 32) * 32;
+    return v;
+}
+static int glue_kslice_min_rows() {
+    static int v = -1;
+    if (v < 0) v = env_int("GGPM_GLUE_KSLICE_MIN_ROWS", 4096);
+    return v;
+}
+
 int launch_gemm_nt(const GemmArgs& g, cudaStream_t st) {
-    if (gemm_tc_eligible(g)) return launch_gemm_tc(g, st);
+    static int glue_simt = -1;          // diagnosis knob: generic GEMMs (glue linears, x-projections) on the fp32 CUDA-core engine
+    if (glue_simt < 0) glue_simt = env_int("GGPM_GLUE_SIMT", 0) != 0 ? 1 : 0;
+    if (glue_simt && !g.a_row_ptr && !g.b_row_ptr) return launch_gemm_simt(g, st);
+    if (gemm_tc_eligible(g)) {
+        // Long-K products of the generic path (glue linears: K up to 2H, non-negative post-ReLU inputs) run as K-slices that
+        // the epilogue accumulates in fp32: a 3xTF32 accumulator takes K / 8 MMA steps per tile, each rounding toward zero,
+        // and the loss grows with that chain and is coherent across rows (measured at K = 1000: rms error
+        // 2.3e-6 unsliced, 5.6e-7 with 256-deep slices, cuBLAS fp32 4.0e-7).  Slices are multiples of 32; bias, activation
+        // and the row-0 mask run in the last slice only.
+        const int ks = glue_kslice();
+        if (ks > 0 && g.K > ks + ks / 2 && g.split_k <= 1 && !g.a_row_ptr && !g.b_row_ptr && g.split_dim == SPLIT_NONE &&
+            g.M >= glue_kslice_min_rows()) {
+            for (int k0 = 0; k0 < g.K;) {
+                const int len = g.K - k0 > ks + ks / 2 ? ks : g.K - k0;
+                GemmArgs q = g;
+                q.A = g.A + (long long)k0 * g.sak;
+                q.B = g.B + (long long)k0 * g.sbk;
+                q.K = len;
+                const bool first = k0 == 0, last = k0 + len >= g.K;
+                if (!first) q.beta = 1.f;
+                if (!last) { q.bias = nullptr; q.act = GGPM_ACT_NONE; q.zero_row0 = 0; }
+                if (!gemm_tc_eligible(q)) {
+                    GGPM_REQUIRE(first, "gemm: K-slice %d of a sliced product is not eligible for the tcgen05 engine", k0);
+                    return launch_gemm_tc(g, st);
+                }
+                GGPM_TRY(launch_gemm_tc(q, st));
+                k0 += len;
+            }
+            return 0;
+        }
+        return launch_gemm_tc(g, st);
+    }
     GGPM_REQUIRE(!g.a_row_ptr && !g.b_row_ptr, "gemm: fused gather needs the tcgen05 engine");
     return launch_gemm_simt(g, st);
 }

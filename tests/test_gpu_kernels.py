@@ -122,6 +122,31 @@ def test_gemm_nt_with_epilogue(engine, M, N, K):
         assert rel(out, ref) <= 1e-5, (act, rel(out, ref))
 
 
+@pytest.mark.parametrize("M,N,K", [(4096, 256, 1000), (5000, 512, 520), (4200, 250, 538), (6000, 128, 388)])
+def test_gemm_nt_long_k_runs_as_fp32_accumulated_slices(engine, M, N, K):
+    """generic GEMMs with >= 4096 rows and K > 384 run as 256-deep K-slices (gemm_tc.cu launch_gemm_nt): every epilogue
+    (accumulate, bias, activation, row-0 mask) gives the unsliced result, and the post-ReLU (non-negative) operand that
+    makes the tensor core's round-toward-zero accumulation coherent stays at fp32-level error"""
+    g = torch.Generator().manual_seed(M + K)
+    A = torch.relu(torch.randn(M, K, generator=g, dtype=torch.float64))
+    W = torch.randn(N, K, generator=g, dtype=torch.float64) / K ** 0.5
+    b = torch.randn(N, generator=g, dtype=torch.float64) * 0.1
+    C0 = torch.randn(M, N, generator=g, dtype=torch.float64)
+    Af, Wf, bf = A.float().to(DEV), W.float().to(DEV), b.float().to(DEV)
+    lin = Af.double().cpu() @ Wf.double().cpu().t()
+    for beta, bias, act, z0 in ((0.0, None, 0, False), (1.0, bf, 1, True), (0.0, bf, 2, False), (1.0, None, 0, False)):
+        out = C0.float().to(DEV)
+        Fn.gemm_nt(Af, Wf, out=out, beta=beta, bias=bias, act=act, zero_row0=z0)
+        ref = lin + beta * C0.float().double() + (0 if bias is None else bf.double().cpu())
+        ref = (lambda x: x, torch.relu, torch.tanh)[act](ref)
+        if z0:
+            ref[0] = 0
+        assert rel(out, ref) <= 1e-5, (beta, act, rel(out, ref))
+    out = Fn.gemm_nt(Af, Wf)
+    err = out.double().cpu() - lin
+    assert float(err.pow(2).mean().sqrt() / lin.pow(2).mean().sqrt()) <= (1.2e-6 if engine != 1 else 6e-7)
+
+
 def test_gemm_strided_views_and_padded_output(engine):
     g = torch.Generator().manual_seed(5)
     big = torch.randn(500, 300, generator=g).to(DEV)
